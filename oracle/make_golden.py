@@ -1,0 +1,236 @@
+"""Generate tests/golden/*.pt by running the UNMODIFIED reference (imported read-only from
+/root/reference through oracle/ref_harness.py) on seeded synthetic inputs.
+
+Run in the build container only:   python oracle/make_golden.py
+The fixtures travel to the GPU box; the reference does not.  TEST INFRASTRUCTURE ONLY.
+"""
+import contextlib
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from oracle import ref_harness  # noqa: E402
+import synthetic_scene as syn  # noqa: E402
+
+OUT = os.path.join(ROOT, "tests", "golden")
+
+
+@contextlib.contextmanager
+def injected_draws(noise=None, perm=None):
+    """Replace torch.rand / torch.randperm for the duration of one reference call so that the
+    reference consumes OUR jitter (model/rendering.py:190) and OUR ray choice (model/training.py:277)."""
+    o_rand, o_perm = torch.rand, torch.randperm
+
+    def rand(*shape, **kw):
+        assert noise is not None and tuple(shape) == tuple(noise.shape), (shape, None if noise is None else noise.shape)
+        return noise.clone()
+
+    def randperm(n, **kw):
+        assert perm is not None
+        return perm.clone()
+
+    torch.rand, torch.randperm = rand, randperm
+    try:
+        yield
+    finally:
+        torch.rand, torch.randperm = o_rand, o_perm
+
+
+def build_ref_model(ref, cfg, sd):
+    nerf = ref.model.OfficialStaticNerf(cfg)
+    nerf.load_state_dict(sd)
+    renderer = ref.model.Renderer(nerf, cfg["rendering"], device=torch.device("cpu"))
+    net = ref.network.nope_nerf(cfg, renderer, None, torch.device("cpu"))
+    return nerf, renderer, net
+
+
+def stage_vectors(ref, cfg):
+    g = torch.Generator().manual_seed(5)
+    out = {"torch_version": torch.__version__}
+    # --- SE(3) exp / pose / distortion (model/common.py:277-310, model/poses.py, model/distortions.py)
+    rs = torch.cat([torch.zeros(1, 3), 1e-2 * torch.randn(3, 3, generator=g), torch.randn(2, 3, generator=g),
+                    torch.tensor([[3.0, 0.1, -0.2]])])
+    ts = torch.randn(rs.shape[0], 3, generator=g)
+    init = syn.make_poses(rs.shape[0])
+    c2w, c2w_init, g_r, g_t = [], [], [], []
+    probe = torch.randn(4, 4, generator=g)
+    for r, t, ini in zip(rs, ts, init):
+        r = r.clone().requires_grad_(True)
+        t = t.clone().requires_grad_(True)
+        m = ref.common.make_c2w(r, t)
+        mi = m @ ini
+        (mi * probe).sum().backward()
+        c2w.append(m.detach())
+        c2w_init.append(mi.detach())
+        g_r.append(r.grad.clone())
+        g_t.append(t.grad.clone())
+    out["pose"] = {"r": rs, "t": ts, "init": init, "probe": probe, "c2w": torch.stack(c2w),
+                   "c2w_init": torch.stack(c2w_init), "grad_r": torch.stack(g_r), "grad_t": torch.stack(g_t)}
+    dn = ref.model.Learn_Distortion(4, True, True, cfg)
+    with torch.no_grad():
+        dn.global_scales.copy_(torch.tensor([[1.3], [0.005], [0.7], [2.0]]))
+        dn.global_shifts.copy_(torch.tensor([[0.1], [-0.2], [0.3], [0.4]]))
+    out["distortion"] = {"scales": dn.global_scales.detach().clone(), "shifts": dn.global_shifts.detach().clone(),
+                         "out": [tuple(float(v) for v in dn(i)) for i in range(4)]}
+    # --- pixel grid (model/common.py:13-40)
+    loc, scaled = ref.common.arange_pixels((5, 7))
+    out["pixel_grid"] = {"h": 5, "w": 7, "loc": loc, "scaled": scaled}
+    # --- positional encoding (model/official_nerf.py:99-119): far-plane-sized arguments included
+    x = torch.cat([torch.randn(64, 3, generator=g), 10.0 * (torch.rand(64, 3, generator=g) - 0.5) * 2])
+    out["posenc"] = {"x": x, "enc10": ref.official_nerf.encode_position(x, 10, True),
+                     "enc4": ref.official_nerf.encode_position(x, 4, True)}
+    # --- compositing semantics probes (model/rendering.py:116-126)
+    a = torch.rand(16, 128, generator=g) * 0.2
+    a[0, 5] = 1.0
+    a[1] = 0.0
+    c = torch.rand(16, 128, 3, generator=g)
+    z = torch.sort(torch.rand(16, 128, generator=g) * 10)[0]
+    a_ = a.clone().requires_grad_(True)
+    c_ = c.clone().requires_grad_(True)
+    w = a_ * torch.cumprod(torch.cat([torch.ones(16, 1), 1. - a_ + 1e-6], -1), -1)[:, :-1]
+    rgb = torch.sum(w.unsqueeze(-1) * c_, dim=-2)
+    dist = torch.sum(w * z, dim=-1)
+    pr, pd = torch.randn(16, 3, generator=g), torch.randn(16, generator=g)
+    ((rgb * pr).sum() + (dist * pd).sum()).backward()
+    out["composite"] = {"alpha": a, "rgb_s": c, "z": z, "weights": w.detach(), "rgb": rgb.detach(), "dist": dist.detach(),
+                        "probe_rgb": pr, "probe_dist": pd, "grad_alpha": a_.grad.clone(), "grad_rgb_s": c_.grad.clone()}
+    return out
+
+
+def loss_vectors(ref, cfg):
+    g = torch.Generator().manual_seed(6)
+    L = ref.losses.Loss(cfg["training"])
+    out = {}
+    pred = torch.rand(1, 50, 3, generator=g)
+    gt = torch.rand(1, 50, 3, generator=g)
+    out["rgb"] = {"pred": pred, "gt": gt, "l1": L.get_rgb_full_loss(pred, gt, "l1"), "l2": L.get_rgb_full_loss(pred, gt, "l2"),
+                  "mse": torch.nn.functional.mse_loss(pred, gt)}
+    for n in (50, 51):  # even (lower median) and odd counts
+        dp = (torch.rand(n, generator=g) * 5 + 0.5).requires_grad_(True)
+        dg = (torch.rand(n, generator=g) * 5 + 0.5).requires_grad_(True)
+        L.depth_loss_type = "l1"
+        l1 = L.get_depth_loss(dp, dg)
+        L.depth_loss_type = "invariant"
+        inv = L.get_depth_loss(dp, dg)
+        inv.backward()
+        out["depth_%d" % n] = {"pred": dp.detach().clone(), "gt": dg.detach().clone(), "l1": l1.detach(), "inv": inv.detach(),
+                               "inv_grad_pred": dp.grad.clone(), "inv_grad_gt": dg.grad.clone()}
+    # Chamfer: random clouds, a lattice (exact ties -> first index), a coincident point (zero subgradient)
+    X = torch.rand(3, 300, generator=g) * 2 - 1
+    Y = torch.rand(3, 257, generator=g) * 2 - 1
+    Y[:, 7] = X[:, 11]
+    lat = torch.stack(torch.meshgrid(torch.arange(4.), torch.arange(4.), torch.arange(4.), indexing="ij")).reshape(3, -1)
+    latq = lat[:, ::3] + 0.5
+    Xr = X.clone().requires_grad_(True)
+    Yr = Y.clone().requires_grad_(True)
+    e = L.get_pc_loss(Xr.t().unsqueeze(0), Yr.t().unsqueeze(0))
+    e.backward()
+    out["chamfer"] = {"X": X, "Y": Y, "idx_xy": L.comp_closest_pts_idx_with_split(X, Y), "idx_yx": L.comp_closest_pts_idx_with_split(Y, X),
+                      "loss": e.detach(), "grad_X": Xr.grad.clone(), "grad_Y": Yr.grad.clone(),
+                      "lat_src": latq, "lat_dst": lat, "lat_idx": L.comp_closest_pts_idx_with_split(latq, lat)}
+    r1 = torch.rand(1, 6, 8, 3, generator=g)
+    r2 = torch.rand(1, 6, 8, 3, generator=g) * 2.5
+    vm = torch.rand(1, 6, 8, 1, generator=g) > 0.3
+    out["rgb_s"] = {"rgb1": r1, "rgb2": r2, "valid": vm, "loss": L.get_rgb_s_loss(r1, r2, vm),
+                    "loss_empty": torch.tensor(0.0)}
+    return out
+
+
+def flat_stats(t):
+    return torch.stack([t.sum(), t.abs().sum(), (t * t).sum()])
+
+
+def render_and_step_vectors(ref, cfg):
+    out = {}
+    scene = syn.make_scene("tiny")
+    n, h, w, R = scene["n"], scene["h"], scene["w"], syn.SHAPES["tiny"][3]
+    sd = syn.init_mlp_state(42)
+    nerf, renderer, net = build_ref_model(ref, cfg, sd)
+    out["mlp_checksum"] = {k: flat_stats(v) for k, v in sd.items()}
+    ray_idx = syn.ray_choice(h, w, R)
+    noise = syn.jitter(R, 128)
+    r0, t0 = syn.init_pose_params(n)
+    # --- MLP forward alone (model/official_nerf.py:69-96)
+    g = torch.Generator().manual_seed(9)
+    pts = (torch.rand(256, 3, generator=g) - 0.5) * 8
+    vd = torch.nn.functional.normalize(torch.randn(256, 3, generator=g), dim=-1)
+    with torch.no_grad():
+        rgb, alpha = nerf(pts, vd, return_addocc=True)
+    out["mlp"] = {"pts": pts, "viewdir": vd, "rgb": rgb, "alpha": alpha}
+    # --- Renderer.forward train (jitter injected) and eval (no jitter) (model/rendering.py:22-168)
+    pose_net = ref.model.LearnPose(n, True, True, cfg, init_c2w=scene["poses_gt"].clone())
+    with torch.no_grad():
+        pose_net.r.copy_(r0)
+        pose_net.t.copy_(t0)
+    c2w = pose_net(1)
+    world_mat = torch.inverse(c2w).unsqueeze(0).detach()
+    _, p_full = ref.common.arange_pixels((h, w))
+    p = p_full[:, ray_idx]
+    depth_sel = scene["depths"][1].reshape(1, -1, 1)[:, ray_idx].clone()
+    depth_sel[0, 3, 0] = 0.0  # one invalid-depth ray exercises the mask path
+    with injected_draws(noise=noise):
+        o_tr = renderer(p, depth_sel, scene["camera_mat"], world_mat, scene["scale_mat"], "nope_nerf", add_noise=True, eval_=False)
+    with torch.no_grad():
+        o_ev = renderer(p, depth_sel, scene["camera_mat"], world_mat, scene["scale_mat"], "nope_nerf", add_noise=False, eval_=True)
+    out["render"] = {"ray_idx": ray_idx, "noise": noise, "pixels": p, "depth": depth_sel, "world_mat": world_mat,
+                     "train": {k: (v.detach() if torch.is_tensor(v) else v) for k, v in o_tr.items()},
+                     "eval": {k: (v.detach() if torch.is_tensor(v) else v) for k, v in o_ev.items()}}
+    # --- full Trainer.compute_loss + backward (model/training.py:214-416), several branches
+    cases = {
+        "l1_mid": dict(idx=1, ref=2, depth_loss_type="l1", epoch=0),
+        "inv_mid": dict(idx=1, ref=2, depth_loss_type="invariant", epoch=0),
+        "l1_last": dict(idx=n - 1, ref=n - 2, depth_loss_type="l1", epoch=0),
+        "l2_rgb_only": dict(idx=0, ref=1, depth_loss_type="l1", epoch=10 ** 6),
+    }
+    out["step"] = {}
+    for name, c in cases.items():
+        tcfg = dict(cfg["training"])
+        tcfg["depth_loss_type"] = c["depth_loss_type"]
+        tcfg["n_training_points"] = R
+        nerf, renderer, net = build_ref_model(ref, cfg, sd)
+        pose_net = ref.model.LearnPose(n, True, True, cfg, init_c2w=scene["poses_gt"].clone())
+        dist_net = ref.model.Learn_Distortion(n, True, True, cfg)
+        with torch.no_grad():
+            pose_net.r.copy_(r0)
+            pose_net.t.copy_(t0)
+            dist_net.global_scales.copy_(1.0 + 0.05 * torch.arange(n, dtype=torch.float32).view(n, 1))
+            dist_net.global_shifts.copy_(0.01 * torch.arange(n, dtype=torch.float32).view(n, 1))
+        trainer = ref.model.Trainer(net, None, tcfg, device=torch.device("cpu"), pose_param_net=pose_net,
+                                    distortion_net=dist_net)
+        batch = syn.make_batch(scene, c["idx"], c["ref"])
+        with injected_draws(noise=noise, perm=torch.cat([ray_idx, torch.zeros(h * w - R, dtype=torch.long)])):
+            ld = trainer.compute_loss(batch, it=1, epoch=c["epoch"], scheduling_start=tcfg["scheduling_start"],
+                                      out_render_path="/tmp")
+        ld["loss"].backward()
+        rec = {"case": c, "loss_dict": {k: v.detach().clone().reshape(-1) for k, v in ld.items()},
+               "grad_r": pose_net.r.grad.clone(), "grad_t": pose_net.t.grad.clone(),
+               "grad_scales": dist_net.global_scales.grad.clone() if dist_net.global_scales.grad is not None else None,
+               "grad_shifts": dist_net.global_shifts.grad.clone() if dist_net.global_shifts.grad is not None else None,
+               "mlp_grad_stats": {k: flat_stats(v.grad) for k, v in nerf.named_parameters()}}
+        if name == "l1_mid":
+            rec["mlp_grads"] = {k: v.grad.clone() for k, v in nerf.named_parameters()}
+        out["step"][name] = rec
+        print(name, {k: float(v.reshape(-1)[0]) for k, v in ld.items()})
+    out["step_setup"] = {"scales": 1.0 + 0.05 * torch.arange(n, dtype=torch.float32).view(n, 1),
+                         "shifts": 0.01 * torch.arange(n, dtype=torch.float32).view(n, 1), "r": r0, "t": t0}
+    return out
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    ref = ref_harness.load_reference()
+    cfg = syn.default_cfg()
+    torch.set_num_threads(max(1, os.cpu_count() or 1))
+    torch.save(stage_vectors(ref, cfg), os.path.join(OUT, "stages.pt"))
+    torch.save(loss_vectors(ref, cfg), os.path.join(OUT, "losses.pt"))
+    torch.save(render_and_step_vectors(ref, cfg), os.path.join(OUT, "render_step.pt"))
+    for f in sorted(os.listdir(OUT)):
+        print(f, os.path.getsize(os.path.join(OUT, f)))
+
+
+if __name__ == "__main__":
+    main()
