@@ -1,0 +1,494 @@
+"""torch.autograd.Function wrappers: one per C-ABI stage, forward and hand-written backward both
+call into libnope_nerf_b200.so on torch's current CUDA stream.  No torch math on the data path."""
+import ctypes as C
+
+import torch
+
+from . import _cabi as K
+from ._cabi import call, f32, ptr, stream
+
+
+def _new(ref, *shape, dtype=torch.float32):
+    return torch.empty(shape, dtype=dtype, device=ref.device)
+
+
+# ------------------------------------------------------------------------------------------------
+# Stage 1
+# ------------------------------------------------------------------------------------------------
+class PoseC2W(torch.autograd.Function):
+    """LearnPose.forward (model/poses.py:23-31)."""
+
+    @staticmethod
+    def forward(ctx, r, t, init_c2w, cam_id):
+        r, t = f32(r), f32(t)
+        init = f32(init_c2w) if init_c2w is not None else None
+        out = _new(r, 4, 4)
+        call("nnb_pose_fwd", ptr(r), ptr(t), ptr(init), int(cam_id), ptr(out), stream())
+        ctx.save_for_backward(r, t, init if init is not None else torch.empty(0, device=r.device))
+        ctx.cam_id, ctx.has_init = int(cam_id), init is not None
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        r, t, init = ctx.saved_tensors
+        dr, dt = torch.zeros_like(r), torch.zeros_like(t)
+        rows = _new(r, 6)
+        call("nnb_pose_bwd", ptr(r), ptr(t), ptr(init) if ctx.has_init else None, ctx.cam_id, ptr(f32(g)),
+             C.c_void_p(rows.data_ptr()), C.c_void_p(rows.data_ptr() + 12), stream())
+        dr[ctx.cam_id] = rows[:3]
+        dt[ctx.cam_id] = rows[3:]
+        return dr, dt, None, None
+
+
+class Mat4Inverse(torch.autograd.Function):
+    """torch.inverse on one 4x4 (model/training.py:257 and friends)."""
+
+    @staticmethod
+    def forward(ctx, m):
+        shape = m.shape
+        m = f32(m).reshape(4, 4)
+        out = torch.empty_like(m)
+        call("nnb_mat4_inv_fwd", ptr(m), ptr(out), stream())
+        ctx.save_for_backward(out)
+        ctx.shape = shape
+        return out.reshape(shape)
+
+    @staticmethod
+    def backward(ctx, g):
+        (inv,) = ctx.saved_tensors
+        dm = torch.empty_like(inv)
+        call("nnb_mat4_inv_bwd", ptr(inv), ptr(f32(g).reshape(4, 4)), ptr(dm), stream())
+        return dm.reshape(ctx.shape)
+
+
+class Distortion(torch.autograd.Function):
+    """Learn_Distortion.forward (model/distortions.py:19-27) -> tensor [scale, shift]."""
+
+    @staticmethod
+    def forward(ctx, scales, shifts, cam_id, fix_scaleN):
+        scales, shifts = f32(scales), f32(shifts)
+        out = _new(scales, 2)
+        n = scales.shape[0]
+        call("nnb_distortion_fwd", ptr(scales), ptr(shifts), int(cam_id), n, int(bool(fix_scaleN)), ptr(out), stream())
+        ctx.save_for_backward(scales)
+        ctx.args = (int(cam_id), n, int(bool(fix_scaleN)))
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        (scales,) = ctx.saved_tensors
+        cam, n, fix = ctx.args
+        ds, dsh = torch.zeros_like(scales), torch.zeros_like(scales)
+        row = _new(scales, 2)
+        call("nnb_distortion_bwd", ptr(scales), cam, n, fix, ptr(f32(g)), C.c_void_p(row.data_ptr()),
+             C.c_void_p(row.data_ptr() + 4), stream())
+        ds[cam, 0] = row[0]
+        dsh[cam, 0] = row[1]
+        return ds, dsh, None, None
+
+
+def pixel_grid(h, w, device):
+    loc = torch.empty(h * w, 2, dtype=torch.int64, device=device)
+    scaled = torch.empty(h * w, 2, dtype=torch.float32, device=device)
+    call("nnb_pixel_grid", h, w, ptr(loc), ptr(scaled), stream())
+    return loc, scaled
+
+
+class GatherRays(torch.autograd.Function):
+    """pixels / rgb_gt / depth*scale+shift at ray_idx (model/training.py:264,285-288; model/network.py:21-24).
+    scale_shift: tensor [scale, shift] on device or None."""
+
+    @staticmethod
+    def forward(ctx, ray_idx, img, depth_img, scale_shift, h, w):
+        ray_idx = ray_idx.contiguous()
+        n = ray_idx.numel()
+        img = f32(img) if img is not None else None
+        depth_img = f32(depth_img) if depth_img is not None else None
+        ss = f32(scale_shift) if scale_shift is not None else None
+        pixels = _new(ray_idx, n, 2)
+        rgb = _new(ray_idx, n, 3) if img is not None else None
+        depth = _new(ray_idx, n) if depth_img is not None else None
+        call("nnb_gather_rays_fwd", ptr(ray_idx), n, int(h), int(w), ptr(img), ptr(depth_img), ptr(ss), ptr(pixels), ptr(rgb),
+             ptr(depth), stream())
+        ctx.save_for_backward(ray_idx, depth_img if depth_img is not None else torch.empty(0, device=ray_idx.device))
+        ctx.has_ss = ss is not None
+        ctx.mark_non_differentiable(pixels)
+        if rgb is not None:
+            ctx.mark_non_differentiable(rgb)
+        return pixels, rgb, depth
+
+    @staticmethod
+    def backward(ctx, gp, gr, gd):
+        ray_idx, depth_img = ctx.saved_tensors
+        dss = None
+        if ctx.has_ss and gd is not None:
+            dss = _new(depth_img, 2)
+            call("nnb_gather_rays_bwd", ptr(ray_idx), ray_idx.numel(), ptr(depth_img), ptr(f32(gd)), ptr(dss), stream())
+        return None, None, None, dss, None, None
+
+
+class RayGen(torch.autograd.Function):
+    """model/common.py:112-237 + model/rendering.py:53-80."""
+
+    @staticmethod
+    def forward(ctx, pixels, depth, camera_mat, world_mat, scale_mat, normalise):
+        ctx.depth_shape = depth.shape if depth is not None else None
+        pixels = f32(pixels).reshape(-1, 2)
+        n = pixels.shape[0]
+        depth = f32(depth).reshape(-1) if depth is not None else None
+        Km, Wm, Sm = f32(camera_mat).reshape(4, 4), f32(world_mat).reshape(4, 4), f32(scale_mat).reshape(4, 4)
+        A, origin = _new(pixels, 4, 4), _new(pixels, 3)
+        dirs, nrm, dgt = _new(pixels, n, 3), _new(pixels, n), _new(pixels, n)
+        mask = _new(pixels, n, dtype=torch.bool)
+        call("nnb_raygen_fwd", ptr(pixels), ptr(depth), ptr(Km), ptr(Wm), ptr(Sm), n, int(bool(normalise)), ptr(A), ptr(origin),
+             ptr(dirs), ptr(nrm), ptr(dgt), ptr(mask), stream())
+        ctx.save_for_backward(pixels, depth if depth is not None else torch.empty(0, device=pixels.device), Km, Wm, Sm, A)
+        ctx.has_depth, ctx.normalise = depth is not None, int(bool(normalise))
+        ctx.shapes = (camera_mat.shape, world_mat.shape, scale_mat.shape, None)
+        ctx.mark_non_differentiable(mask, nrm)
+        return origin, dirs, nrm, dgt, mask
+
+    @staticmethod
+    def backward(ctx, g_origin, g_dirs, g_nrm, g_dgt, g_mask):
+        pixels, depth, Km, Wm, Sm, A = ctx.saved_tensors
+        n = pixels.shape[0]
+        d_depth = _new(pixels, n) if ctx.has_depth else None
+        dK, dW, dS = _new(pixels, 4, 4), _new(pixels, 4, 4), _new(pixels, 4, 4)
+        scratch = _new(pixels, 16)
+        call("nnb_raygen_bwd", ptr(pixels), ptr(depth) if ctx.has_depth else None, ptr(Km), ptr(Wm), ptr(Sm), ptr(A), n, ctx.normalise,
+             ptr(f32(g_dirs)) if g_dirs is not None else None, ptr(f32(g_origin)) if g_origin is not None else None,
+             ptr(f32(g_dgt)) if g_dgt is not None else None, ptr(d_depth), ptr(dK), ptr(dW), ptr(dS), ptr(scratch), stream())
+        sk, sw, ss, _ = ctx.shapes
+        if d_depth is not None:
+            d_depth = d_depth.reshape(ctx.depth_shape)
+        return None, d_depth, dK.reshape(sk), dW.reshape(sw), dS.reshape(ss), None
+
+
+# ------------------------------------------------------------------------------------------------
+# Stages 2+3
+# ------------------------------------------------------------------------------------------------
+def make_cfg(n_rays, n_samples, near, far, occ_softplus, dist_alpha, white_bkgd, use_dir, precision):
+    return K.RenderCfg(int(n_rays), int(n_samples), float(near), float(far), int(occ_softplus), int(dist_alpha),
+                       int(white_bkgd), int(use_dir), int(precision))
+
+
+def workspace_bytes(cfg, save):
+    return int(K.lib().nnb_render_workspace_bytes(C.byref(cfg), int(save)))
+
+
+_ws_cache = {}
+
+
+def _workspace(device, nbytes, tag):
+    """Reused scratch buffer per (device, tag): the library never allocates."""
+    key = (str(device), tag)
+    buf = _ws_cache.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=device)
+        _ws_cache[key] = buf
+    return buf
+
+
+def render_nograd(cfg, params, packed, origin, dirs, noise, want_aux=True):
+    """Forward only (eval / render loops).  Returns rgb, dist, weights, alpha, z (aux None if not wanted)."""
+    R, S = cfg.n_rays, cfg.n_samples
+    dev = dirs.device
+    rgb, dist = torch.empty(R, 3, device=dev), torch.empty(R, device=dev)
+    w = torch.empty(R, S, device=dev) if want_aux else None
+    a = torch.empty(R, S, device=dev) if want_aux else None
+    z = torch.empty(R, S, device=dev) if want_aux else None
+    nbytes = workspace_bytes(cfg, 0)
+    ws = _workspace(dev, nbytes, "render_eval")
+    parr = K.param_ptr_array(params)
+    call("nnb_render_fwd", C.byref(cfg), parr, ptr(packed), ptr(origin), ptr(dirs), ptr(noise), ptr(rgb), ptr(dist), ptr(w), ptr(a),
+         ptr(z), ptr(ws), nbytes, 0, stream())
+    return rgb, dist, w, a, z
+
+
+class RenderRays(torch.autograd.Function):
+    """Stratified sampling + positional encoding + MLP + compositing (model/rendering.py:89-126,
+    model/official_nerf.py:60-119).  Inputs after the fixed ones are the 24 parameter tensors."""
+
+    @staticmethod
+    def forward(ctx, cfg, packed, origin, dirs, noise, *params):
+        R, S = cfg.n_rays, cfg.n_samples
+        dev = dirs.device
+        origin, dirs = f32(origin), f32(dirs)
+        noise = f32(noise).reshape(R, S) if noise is not None else None
+        params = [f32(p) for p in params]
+        rgb, dist = torch.empty(R, 3, device=dev), torch.empty(R, device=dev)
+        w, a, z = torch.empty(R, S, device=dev), torch.empty(R, S, device=dev), torch.empty(R, S, device=dev)
+        nbytes = workspace_bytes(cfg, 1)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)  # owned by this graph node until backward
+        parr = K.param_ptr_array(params)
+        call("nnb_render_fwd", C.byref(cfg), parr, ptr(packed), ptr(origin), ptr(dirs), ptr(noise), ptr(rgb), ptr(dist), ptr(w),
+             ptr(a), ptr(z), ptr(ws), nbytes, 1, stream())
+        ctx.cfg, ctx.packed, ctx.ws, ctx.nbytes = cfg, packed, ws, nbytes
+        ctx.save_for_backward(origin, dirs, w, a, z, *params)
+        ctx.mark_non_differentiable(z)
+        return rgb, dist, w, a, z
+
+    @staticmethod
+    def backward(ctx, g_rgb, g_dist, g_w, g_a, g_z):
+        origin, dirs, w, a, z, *params = ctx.saved_tensors
+        cfg = ctx.cfg
+        dev = dirs.device
+        grads = [torch.zeros_like(p) for p in params]
+        d_origin, d_dirs = torch.empty(3, device=dev), torch.empty_like(dirs)
+        parr, garr = K.param_ptr_array(params), K.param_ptr_array(grads)
+
+        def opt(g):
+            return ptr(f32(g)) if g is not None else None
+        call("nnb_render_bwd", C.byref(cfg), parr, ptr(ctx.packed), ptr(origin), ptr(dirs), ptr(w), ptr(a), ptr(z), opt(g_rgb),
+             opt(g_dist), opt(g_a), opt(g_w), garr, ptr(d_origin), ptr(d_dirs), ptr(ctx.ws), ctx.nbytes, stream())
+        ctx.ws = None
+        return (None, None, d_origin, d_dirs, None) + tuple(grads)
+
+
+class Composite(torch.autograd.Function):
+    """Stand-alone stage 3 (model/rendering.py:116-126)."""
+
+    @staticmethod
+    def forward(ctx, alpha, rgb_s, z, dist_alpha, white):
+        alpha, rgb_s, z = f32(alpha), f32(rgb_s), f32(z)
+        R, S = alpha.shape
+        rgb, dist, w, a = _new(alpha, R, 3), _new(alpha, R), _new(alpha, R, S), _new(alpha, R, S)
+        call("nnb_composite_fwd", ptr(alpha), ptr(rgb_s), ptr(z), R, S, int(dist_alpha), int(white), ptr(rgb), ptr(dist), ptr(w),
+             ptr(a), stream())
+        ctx.save_for_backward(alpha, rgb_s, z, w)
+        ctx.flags = (int(dist_alpha), int(white))
+        return rgb, dist, w
+
+    @staticmethod
+    def backward(ctx, g_rgb, g_dist, g_w):
+        alpha, rgb_s, z, w = ctx.saved_tensors
+        R, S = alpha.shape
+        da, dc = torch.empty_like(alpha), torch.empty_like(rgb_s)
+        call("nnb_composite_bwd", ptr(alpha), ptr(rgb_s), ptr(z), ptr(w), R, S, ctx.flags[0], ctx.flags[1],
+             ptr(f32(g_rgb)) if g_rgb is not None else None, ptr(f32(g_dist)) if g_dist is not None else None,
+             ptr(f32(g_w)) if g_w is not None else None, ptr(da), ptr(dc), stream())
+        return da, dc, None, None, None
+
+
+# ------------------------------------------------------------------------------------------------
+# Stage 4
+# ------------------------------------------------------------------------------------------------
+class RgbLoss(torch.autograd.Function):
+    """-> tensor [l1_sum/R, l2_sum/R, mse_mean] (model/losses.py:28-33,200)."""
+
+    @staticmethod
+    def forward(ctx, pred, gt):
+        ctx.shp = pred.shape
+        pred, gt = f32(pred).reshape(-1, 3), f32(gt).reshape(-1, 3)
+        out = _new(pred, 3)
+        call("nnb_rgb_loss_fwd", ptr(pred), ptr(gt), pred.shape[0], ptr(out), stream())
+        ctx.save_for_backward(pred, gt)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        pred, gt = ctx.saved_tensors
+        d = torch.empty_like(pred)
+        call("nnb_rgb_loss_bwd", ptr(pred), ptr(gt), pred.shape[0], ptr(f32(g)), ptr(d), stream())
+        return d.reshape(ctx.shp), None
+
+
+class DepthL1(torch.autograd.Function):
+    """Masked mean |pred-gt| on dense tensors (model/losses.py:60-63)."""
+
+    @staticmethod
+    def forward(ctx, pred, gt, mask):
+        ctx.shp = (pred.shape, gt.shape)
+        pred, gt = f32(pred).reshape(-1), f32(gt).reshape(-1)
+        mask = mask.contiguous() if mask is not None else None
+        out = _new(pred, 2)
+        call("nnb_depth_l1_fwd", ptr(pred), ptr(gt), ptr(mask), pred.numel(), ptr(out), stream())
+        ctx.save_for_backward(pred, gt, out, mask if mask is not None else torch.empty(0, device=pred.device))
+        ctx.has_mask = mask is not None
+        return out[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        pred, gt, out, mask = ctx.saved_tensors
+        dp, dg = torch.empty_like(pred), torch.empty_like(gt)
+        call("nnb_depth_l1_bwd", ptr(pred), ptr(gt), ptr(mask) if ctx.has_mask else None, pred.numel(), ptr(out),
+             ptr(f32(g).reshape(1)), ptr(dp), ptr(dg), stream())
+        return dp.reshape(ctx.shp[0]), dg.reshape(ctx.shp[1]), None
+
+
+def median_select(x, mask=None):
+    x = f32(x).reshape(-1)
+    val, idx = _new(x, 1), _new(x, 1, dtype=torch.int64)
+    call("nnb_median_select", ptr(x), ptr(mask.contiguous()) if mask is not None else None, x.numel(), ptr(val), ptr(idx), stream())
+    return val, idx
+
+
+class DepthInvariant(torch.autograd.Function):
+    """Scale/shift-invariant depth loss (model/losses.py:35-58)."""
+
+    @staticmethod
+    def forward(ctx, pred, gt, mask):
+        ctx.shp = (pred.shape, gt.shape)
+        pred, gt = f32(pred).reshape(-1), f32(gt).reshape(-1)
+        mask = mask.contiguous() if mask is not None else None
+        loss, stats, med = _new(pred, 1), _new(pred, 8), _new(pred, 2, dtype=torch.int64)
+        call("nnb_depth_invariant_fwd", ptr(pred), ptr(gt), ptr(mask), pred.numel(), ptr(loss), ptr(stats), ptr(med), stream())
+        ctx.save_for_backward(pred, gt, stats, med, mask if mask is not None else torch.empty(0, device=pred.device))
+        ctx.has_mask = mask is not None
+        return loss[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        pred, gt, stats, med, mask = ctx.saved_tensors
+        dp, dg = torch.empty_like(pred), torch.empty_like(gt)
+        call("nnb_depth_invariant_bwd", ptr(pred), ptr(gt), ptr(mask) if ctx.has_mask else None, pred.numel(), ptr(stats), ptr(med),
+             ptr(f32(g).reshape(1)), ptr(dp), ptr(dg), stream())
+        return dp.reshape(ctx.shp[0]), dg.reshape(ctx.shp[1]), None
+
+
+class Backproject(torch.autograd.Function):
+    """Depth map -> (h4*w4, 3) cloud (model/training.py:354-362)."""
+
+    @staticmethod
+    def forward(ctx, depth_img, scale_shift, camera_mat, h4, w4, nl):
+        depth_img = f32(depth_img)
+        h, w = depth_img.shape[-2:]
+        depth_img = depth_img.reshape(h, w)
+        ss = f32(scale_shift) if scale_shift is not None else None
+        Km = f32(camera_mat).reshape(4, 4)
+        pc = _new(depth_img, h4 * w4, 3)
+        clamped = _new(depth_img, h4 * w4, dtype=torch.uint8)
+        call("nnb_backproject_fwd", ptr(depth_img), h, w, int(h4), int(w4), ptr(ss), ptr(Km), float(nl), ptr(pc), ptr(clamped), stream())
+        ctx.save_for_backward(depth_img, Km, clamped)
+        ctx.dims, ctx.has_ss = (h, w, int(h4), int(w4)), ss is not None
+        return pc
+
+    @staticmethod
+    def backward(ctx, g):
+        depth_img, Km, clamped = ctx.saved_tensors
+        h, w, h4, w4 = ctx.dims
+        dss = None
+        if ctx.has_ss:
+            dss = _new(depth_img, 2)
+            call("nnb_backproject_bwd", ptr(depth_img), h, w, h4, w4, ptr(Km), ptr(clamped), ptr(f32(g)), ptr(dss), stream())
+        return None, dss, None, None, None, None
+
+
+def resize_bilinear(img, h4, w4):
+    img = f32(img)
+    c, h, w = img.shape[-3:]
+    out = _new(img, c, h4, w4)
+    call("nnb_resize_bilinear", ptr(img.reshape(c, h, w)), c, h, w, int(h4), int(w4), ptr(out), stream())
+    return out
+
+
+class Reproject(torch.autograd.Function):
+    """model/training.py:367-382.  Returns rgb_pc1 (P,3), rgb_pc1_proj (P,3), valid (P,) bool."""
+
+    @staticmethod
+    def forward(ctx, img1r, img2r, pc1, R_rel, t_rel, camera_mat, nl):
+        ctx.pc_shape = pc1.shape
+        img1r, img2r, pc1 = f32(img1r), f32(img2r), f32(pc1).reshape(-1, 3)
+        Rm, tv, Km = f32(R_rel).reshape(3, 3), f32(t_rel).reshape(3), f32(camera_mat).reshape(4, 4)
+        h4, w4 = img2r.shape[-2:]
+        P = pc1.shape[0]
+        rgb1, rgb2, valid = _new(pc1, P, 3), _new(pc1, P, 3), _new(pc1, P, dtype=torch.bool)
+        call("nnb_reproj_fwd", ptr(img1r), ptr(img2r), h4, w4, ptr(pc1), ptr(Rm), ptr(tv), ptr(Km), float(nl), ptr(rgb1), ptr(rgb2),
+             ptr(valid), stream())
+        ctx.save_for_backward(img2r, pc1, Rm, tv, Km)
+        ctx.nl, ctx.rshape, ctx.tshape = float(nl), R_rel.shape, t_rel.shape
+        ctx.mark_non_differentiable(rgb1, valid)
+        return rgb1, rgb2, valid
+
+    @staticmethod
+    def backward(ctx, g1, g2, gv):
+        img2r, pc1, Rm, tv, Km = ctx.saved_tensors
+        h4, w4 = img2r.shape[-2:]
+        d_pc1 = torch.empty_like(pc1)
+        acc = _new(pc1, 12)
+        call("nnb_reproj_bwd", ptr(img2r), h4, w4, ptr(pc1), ptr(Rm), ptr(tv), ptr(Km), ctx.nl, ptr(f32(g2).reshape(-1, 3)), ptr(d_pc1),
+             C.c_void_p(acc.data_ptr()), C.c_void_p(acc.data_ptr() + 36), stream())
+        return None, None, d_pc1.reshape(ctx.pc_shape), acc[:9].reshape(ctx.rshape), acc[9:].reshape(ctx.tshape), None, None
+
+
+class Photometric(torch.autograd.Function):
+    """model/losses.py:79-87,152-159."""
+
+    @staticmethod
+    def forward(ctx, rgb1, rgb2, valid):
+        ctx.shp = (rgb1.shape, rgb2.shape)
+        rgb1, rgb2 = f32(rgb1).reshape(-1, 3), f32(rgb2).reshape(-1, 3)
+        valid = valid.reshape(-1).contiguous()
+        out = _new(rgb1, 2)
+        call("nnb_photometric_fwd", ptr(rgb1), ptr(rgb2), ptr(valid), rgb1.shape[0], ptr(out), stream())
+        ctx.save_for_backward(rgb1, rgb2, valid, out)
+        return out[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        rgb1, rgb2, valid, out = ctx.saved_tensors
+        d1, d2 = torch.empty_like(rgb1), torch.empty_like(rgb2)
+        call("nnb_photometric_bwd", ptr(rgb1), ptr(rgb2), ptr(valid), rgb1.shape[0], ptr(out), ptr(f32(g).reshape(1)), ptr(d1), ptr(d2),
+             stream())
+        return d1.reshape(ctx.shp[0]), d2.reshape(ctx.shp[1]), None
+
+
+# ------------------------------------------------------------------------------------------------
+# Stage 5
+# ------------------------------------------------------------------------------------------------
+def chamfer_nn(src, dst, want_dist=False):
+    """First-argmin nearest neighbour of every src point in dst (model/losses.py:129-144).  (n,3),(m,3) -> (n,) int64."""
+    src, dst = f32(src.detach()).reshape(-1, 3), f32(dst.detach()).reshape(-1, 3)
+    idx = _new(src, src.shape[0], dtype=torch.int64)
+    dist = _new(src, src.shape[0]) if want_dist else None
+    call("nnb_chamfer_nn", ptr(src), src.shape[0], ptr(dst), dst.shape[0], ptr(idx), ptr(dist), stream())
+    return (idx, dist) if want_dist else idx
+
+
+class ChamferErr(torch.autograd.Function):
+    """mean_i ||X_i - Y[idx_i]|| (model/losses.py:145-150)."""
+
+    @staticmethod
+    def forward(ctx, X, Y, idx):
+        ctx.shp = (X.shape, Y.shape)
+        X, Y = f32(X).reshape(-1, 3), f32(Y).reshape(-1, 3)
+        loss = _new(X, 1)
+        call("nnb_chamfer_err_fwd", ptr(X), X.shape[0], ptr(Y), ptr(idx), ptr(loss), stream())
+        ctx.save_for_backward(X, Y, idx)
+        return loss[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        X, Y, idx = ctx.saved_tensors
+        dX, dY = torch.empty_like(X), torch.zeros_like(Y)
+        call("nnb_chamfer_err_bwd", ptr(X), X.shape[0], ptr(Y), ptr(idx), ptr(f32(g).reshape(1)), ptr(dX), ptr(dY), stream())
+        return dX.reshape(ctx.shp[0]), dY.reshape(ctx.shp[1]), None
+
+
+def adam_step(param, grad, exp_avg, exp_avg_sq, lr, beta1, beta2, eps, step):
+    call("nnb_adam_step", ptr(param), ptr(grad), ptr(exp_avg), ptr(exp_avg_sq), param.numel(), float(lr), float(beta1), float(beta2),
+         float(eps), int(step), stream())
+
+
+def mlp_points(params, pts, viewdirs, occ_softplus, dist_alpha):
+    """OfficialStaticNerf.forward at explicit points (forward only).  -> rgb (M,3) or None, dens (M,1)."""
+    pts = f32(pts)
+    M = pts.shape[0]
+    viewdirs = f32(viewdirs) if viewdirs is not None else None
+    rgb = _new(pts, M, 3) if viewdirs is not None else None
+    dens = _new(pts, M)
+    nbytes = int(K.lib().nnb_mlp_points_workspace_bytes(M))
+    ws = _workspace(pts.device, nbytes, "points")
+    parr = K.param_ptr_array([f32(p.detach()) for p in params])
+    call("nnb_mlp_points_fwd", parr, ptr(pts), ptr(viewdirs), M, int(bool(occ_softplus)), int(bool(dist_alpha)), ptr(rgb), ptr(dens),
+         ptr(ws), nbytes, stream())
+    return rgb, dens.reshape(M, 1)
+
+
+def pack_weights(params):
+    """bf16 tile images of the 24 tensors for the tcgen05 path (refreshed whenever the fp32 masters change)."""
+    nbytes = int(K.lib().nnb_pack_weights_bytes())
+    packed = torch.empty(nbytes, dtype=torch.uint8, device=params[0].device)
+    parr = K.param_ptr_array([f32(p.detach()) for p in params])
+    call("nnb_pack_weights", parr, ptr(packed), stream())
+    return packed

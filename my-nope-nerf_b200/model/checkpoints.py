@@ -1,0 +1,50 @@
+"""CheckpointIO -- same on-disk format as the reference's model/checkpoints.py: torch.save of
+{module_name: state_dict, **scalars}; strict load_state_dict, so files are interchangeable with the reference."""
+import os
+
+import torch
+
+
+class CheckpointIO(object):
+    def __init__(self, checkpoint_dir='./chkpts', **kwargs):
+        self.module_dict = kwargs
+        self.checkpoint_dir = checkpoint_dir
+        if not os.path.exists(checkpoint_dir):
+            os.makedirs(checkpoint_dir)
+
+    def register_modules(self, **kwargs):
+        self.module_dict.update(kwargs)
+
+    def save(self, filename, **kwargs):
+        if not os.path.isabs(filename):
+            filename = os.path.join(self.checkpoint_dir, filename)
+        outdict = dict(kwargs)
+        for k, v in self.module_dict.items():
+            outdict[k] = v.state_dict()
+        torch.save(outdict, filename)
+
+    def backup_model_best(self, filename, **kwargs):
+        if not os.path.isabs(filename):
+            filename = os.path.join(self.checkpoint_dir, filename)
+        if os.path.exists(filename):
+            backup_dir = os.path.join(self.checkpoint_dir, 'backup_model_best')
+            if not os.path.exists(backup_dir):
+                os.makedirs(backup_dir)
+            ts = len(os.listdir(backup_dir))
+            os.replace(filename, os.path.join(backup_dir, '%s_%d.pt' % (os.path.basename(filename)[:-3], ts)))
+
+    def load(self, filename, device=None, load_model_only=False):
+        if not os.path.isabs(filename):
+            filename = os.path.join(self.checkpoint_dir, filename)
+        if not os.path.exists(filename):
+            raise FileExistsError
+        state_dict = torch.load(filename, map_location=device if device is not None else 'cpu', weights_only=False)
+        return self.parse_state_dict(state_dict, load_model_only)
+
+    def parse_state_dict(self, state_dict, load_model_only=False):
+        for k, v in self.module_dict.items():
+            if k in state_dict:
+                if load_model_only and k != 'model':
+                    continue
+                v.load_state_dict(state_dict[k])
+        return {k: v for k, v in state_dict.items() if k not in self.module_dict}

@@ -1,0 +1,114 @@
+"""Renderer -- drop-in for the reference's model/rendering.py (`nope_nerf` technique, `uniform` sampling).
+
+forward(pixels, depth, camera_mat, world_mat, scale_mat, rendering_technique, add_noise=True, eval_=False, it=...)
+returns the reference's dict: rgb (1,R,3), z_vals (R,S), normal, depth_pred, depth_gt, alpha (R,S).
+Two launches replace the ~60 the reference issues: ray generation, then the fused
+sampling + encoding + MLP + compositing render.  Extra keys (`depth_pred_dense`, `depth_gt_dense`, `mask`) let the
+loss stack consume the dense tensors + mask without the reference's boolean-index host sync.
+"""
+import torch
+import torch.nn as nn
+
+from . import _cabi, _ops
+
+# rays per fused-render call when saving for backward (bounds the activation workspace)
+MAX_TRAIN_RAYS_FP32 = 8192
+
+
+class Renderer(nn.Module):
+    def __init__(self, model, cfg, device=None, **kwargs):
+        super().__init__()
+        self._device = device
+        self.depth_range = cfg['depth_range']
+        self.n_max_network_queries = cfg['n_max_network_queries']  # kept for parity; the fused kernels do not chunk
+        self.white_background = cfg['white_background']
+        self.cfg = cfg
+        self.model = model.to(device)
+        # 'fp32' (CUDA cores, tight tolerance) or 'bf16' (tcgen05 tensor cores); not a reference option
+        self.precision = kwargs.get('precision', cfg.get('precision', 'fp32'))
+        self._packed = None
+        self._packed_version = None
+
+    # -- reference API -------------------------------------------------------------------------
+    def forward(self, pixels, depth, camera_mat, world_mat, scale_mat, rendering_technique, add_noise=True,
+                eval_=False, it=1000000, noise=None, lazy_mask=False):
+        if rendering_technique == 'nope_nerf':
+            return self.nope_nerf(pixels, depth, camera_mat, world_mat, scale_mat, it=it, add_noise=add_noise,
+                                  eval_=eval_, noise=noise, lazy_mask=lazy_mask)
+        if rendering_technique == 'phong_renderer':
+            raise NotImplementedError("phong_renderer is a 'next' row (SURVEY.md 8f rank 3), off the hot path")
+        raise ValueError("unknown rendering technique %r" % (rendering_technique,))
+
+    def to(self, device):
+        new = super().to(device)
+        new._device = device
+        return new
+
+    # -- implementation --------------------------------------------------------------------------
+    def _prec(self):
+        return _cabi.PREC_BF16 if self.precision == 'bf16' else _cabi.PREC_FP32
+
+    def _cfg(self, n_rays, n_samples):
+        c = self.cfg
+        return _ops.make_cfg(n_rays, n_samples, c['depth_range'][0], c['depth_range'][1],
+                             self.model.occ_activation == 'softplus', c['dist_alpha'], c['white_background'],
+                             c['use_ray_dir'], self._prec())
+
+    def _packed_weights(self, params):
+        if self._prec() != _cabi.PREC_BF16:
+            return None
+        version = tuple(p._version for p in params) + tuple(p.data_ptr() for p in params)
+        if self._packed is None or self._packed_version != version:
+            self._packed = _ops.pack_weights(params)
+            self._packed_version = version
+        return self._packed
+
+    def nope_nerf(self, pixels, depth, camera_mat, world_mat, scale_mat, add_noise=False, it=100000, eval_=False,
+                  noise=None, lazy_mask=False):
+        cfg = self.cfg
+        if cfg['sample_option'] != 'uniform':
+            raise NotImplementedError("sample_option=%r: the NDC branch is a 'next' row (SURVEY.md 8f rank 2)" % cfg['sample_option'])
+        if cfg['normal_loss'] and not eval_:
+            raise NotImplementedError("normal_loss needs the second-order path ('next' row, SURVEY.md 8f rank 3)")
+        batch_size, n_points, _ = pixels.shape
+        if batch_size != 1:
+            raise ValueError("batch size 1 only (as the reference: model/rendering.py:80 takes element 0)")
+        S = cfg['num_points'] - cfg['outside_steps']
+        origin, dirs, nrm, d_gt, mask = _ops.RayGen.apply(pixels, depth, camera_mat, world_mat, scale_mat,
+                                                          cfg['normalise_ray'])
+        if add_noise and noise is None:
+            # same draw, shape and generator as the reference (model/rendering.py:190)
+            noise = torch.rand(batch_size, n_points, S, device=pixels.device)
+        if not add_noise:
+            noise = None
+        params = self.model.param_list()
+        packed = self._packed_weights(params)
+        need_grad = torch.is_grad_enabled() and (any(p.requires_grad for p in params) or dirs.requires_grad
+                                                 or origin.requires_grad)
+        if need_grad:
+            outs = []
+            step = MAX_TRAIN_RAYS_FP32 if self._prec() == _cabi.PREC_FP32 else n_points
+            for r0 in range(0, n_points, step):
+                r1 = min(n_points, r0 + step)
+                rc = self._cfg(r1 - r0, S)
+                nz = None if noise is None else noise.reshape(n_points, S)[r0:r1]
+                outs.append(_ops.RenderRays.apply(rc, packed, origin, dirs[r0:r1], nz, *params))
+            rgb, dist, w, alpha, z = [torch.cat(t, 0) if len(outs) > 1 else t[0] for t in zip(*outs)]
+        else:
+            rc = self._cfg(n_points, S)
+            rgb, dist, w, alpha, z = _ops.render_nograd(rc, [p.detach() for p in params], packed, origin.detach(),
+                                                        dirs.detach(), None if noise is None else noise.reshape(n_points, S))
+        if eval_ and cfg['normalise_ray']:  # model/rendering.py:144-148
+            dist = dist / nrm
+            d_gt = d_gt / nrm
+        if not eval_ and not lazy_mask:
+            # the reference's boolean indexing (model/rendering.py:151-153): data-dependent size => host sync.
+            # Callers that want to stay asynchronous pass lazy_mask=True and use the dense tensors + `mask`.
+            depth_pred, depth_gt = dist[mask], d_gt[mask]
+        else:
+            depth_pred, depth_gt = dist, d_gt
+        return {
+            'rgb': rgb.reshape(batch_size, -1, 3), 'z_vals': z, 'normal': None,
+            'depth_pred': depth_pred, 'depth_gt': depth_gt, 'alpha': alpha,
+            'depth_pred_dense': dist, 'depth_gt_dense': d_gt, 'mask': mask, 'weights': w,
+        }

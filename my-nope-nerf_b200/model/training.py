@@ -1,0 +1,266 @@
+"""Trainer -- drop-in for the reference's model/training.py (same constructor, train_step, compute_loss,
+process_data_dict, anneal; same loss_dict keys plus `scale`, `shift`).
+
+compute_loss keeps the reference's control flow (weight annealing, reference-frame pairing, zero-weight skipping,
+RNG draw order: randperm for the rays, then rand for the stratified jitter) and replaces its tensor math with the
+C-ABI kernels:  pose exp-map, 4x4 inverse, distortion, fused ray gather, ray generation, fused render,
+point-cloud back-projection, reprojection sampling and the loss kernels.  Multi-GPU: every rank draws the same
+global ray batch and takes its contiguous shard; gradients are averaged with ONE flat NCCL allreduce (parallel.py).
+"""
+import logging
+
+import torch
+
+from . import _ops, parallel
+from .losses import Loss
+
+logger_py = logging.getLogger(__name__)
+
+WEIGHT_NAMES = ['rgb_weight', 'depth_weight', 'pc_weight', 'rgb_s_weight', 'depth_consistency_weight',
+                'weight_dist_2nd_loss', 'weight_dist_1st_loss', 't_cycle_weight']
+
+
+class Trainer(object):
+    def __init__(self, model, optimizer, cfg, device=None, optimizer_pose=None, pose_param_net=None,
+                 optimizer_focal=None, focal_net=None, optimizer_distortion=None, distortion_net=None, **kwargs):
+        self.model = model
+        self.optimizer = optimizer
+        self.device = device
+        self.optimizer_pose = optimizer_pose
+        self.pose_param_net = pose_param_net
+        self.focal_net = focal_net
+        self.optimizer_focal = optimizer_focal
+        self.distortion_net = distortion_net
+        self.optimizer_distortion = optimizer_distortion
+
+        self.n_training_points = cfg['n_training_points']
+        self.rendering_technique = cfg['type']
+        self.vis_geo = cfg['vis_geo']
+        self.detach_gt_depth = cfg['detach_gt_depth']
+        self.pc_ratio = cfg['pc_ratio']
+        self.match_method = cfg['match_method']
+        self.shift_first = cfg['shift_first']
+        self.detach_ref_img = cfg['detach_ref_img']
+        self.scale_pcs = cfg['scale_pcs']
+        self.detach_rgbs_scale = cfg['detach_rgbs_scale']
+        self.vis_reprojection_every = cfg['vis_reprojection_every']
+        self.nearest_limit = cfg['nearest_limit']
+        self.annealing_epochs = cfg['annealing_epochs']
+        for w in WEIGHT_NAMES:
+            setattr(self, w, cfg[w])
+        self.loss = Loss(cfg)
+        # data-parallel context (world size 1 unless torch.distributed is initialised)
+        self.dp = kwargs.get('dp') or parallel.DataParallelContext.from_env()
+        # test hooks: inject the ray choice / jitter instead of drawing them (parity tests)
+        self.fixed_ray_idx = None
+        self.fixed_noise = None
+
+    # -- reference API -------------------------------------------------------------------------
+    def train_step(self, data, it=None, epoch=None, scheduling_start=None, render_path=None):
+        self.model.train()
+        self.optimizer.zero_grad()
+        if self.pose_param_net:
+            self.pose_param_net.train()
+            self.optimizer_pose.zero_grad()
+        if self.focal_net:
+            self.focal_net.train()
+            self.optimizer_focal.zero_grad()
+        if self.distortion_net:
+            self.distortion_net.train()
+            self.optimizer_distortion.zero_grad()
+        loss_dict = self.compute_loss(data, it=it, epoch=epoch, scheduling_start=scheduling_start,
+                                      out_render_path=render_path)
+        loss_dict['loss'].backward()
+        if self.dp.world_size > 1:
+            nets = [self.model, self.pose_param_net, self.distortion_net, self.focal_net]
+            self.dp.allreduce_grads([p for n in nets if n is not None for p in n.parameters()])
+        self.optimizer.step()
+        if self.optimizer_pose:
+            self.optimizer_pose.step()
+        if self.optimizer_focal:
+            self.optimizer_focal.step()
+        if self.optimizer_distortion:
+            self.optimizer_distortion.step()
+        return loss_dict
+
+    def process_data_dict(self, data):
+        device = self.device
+        img = data.get('img').to(device)
+        img_idx = data.get('img.idx')
+        depth = data.get('img.dpt')
+        if depth is None:
+            depth = data.get('img.depth')
+        depth = depth.to(device).unsqueeze(1)
+        depth_mask = data.get('img.depth_mask').to(device).unsqueeze(1)
+        camera_mat = data.get('img.camera_mat').to(device)
+        scale_mat = data.get('img.scale_mat').to(device)
+        pose_gt = data.get('img.pose_gt').to(device)
+        return (img, depth, camera_mat, scale_mat, img_idx, pose_gt, depth_mask)
+
+    def process_data_reference(self, data):
+        device = self.device
+        ref_imgs = data.get('img.ref_imgs').to(device)
+        ref_depths = data.get('img.ref_dpts')
+        if ref_depths is None:
+            ref_depths = data.get('img.ref_depths')
+        ref_depths = ref_depths.to(device).unsqueeze(1)
+        ref_pose_gt = data.get('img.ref_pose_gt').to(device)
+        ref_idxs = data.get('img.ref_idxs')
+        return (ref_imgs, ref_depths, ref_idxs, ref_pose_gt)
+
+    def anneal(self, start_weight, end_weight, anneal_start_epoch, anneal_epoches, current):
+        if current <= anneal_start_epoch:
+            return start_weight
+        elif current >= anneal_start_epoch + anneal_epoches:
+            return end_weight
+        return start_weight + (end_weight - start_weight) * (current - anneal_start_epoch) / anneal_epoches
+
+    # -- the step ---------------------------------------------------------------------------------
+    def compute_loss(self, data, eval_mode=False, it=None, epoch=None, scheduling_start=None, out_render_path=None):
+        weights = {w: self.anneal(getattr(self, w)[0], getattr(self, w)[1], scheduling_start, self.annealing_epochs, epoch)
+                   for w in WEIGHT_NAMES}
+        rgb_loss_type = 'l1' if epoch < self.annealing_epochs + scheduling_start else 'l2'
+        render_model = (weights['rgb_weight'] != 0.0) or (weights['depth_weight'] != 0.0)
+        use_ref_imgs = (weights['pc_weight'] != 0.0) or (weights['rgb_s_weight'] != 0.0) or (weights['t_cycle_weight'] != 0.0)
+        if self.shift_first:
+            raise NotImplementedError("shift_first=True is not used by any shipped config ('next' row)")
+
+        n_points = self.n_training_points
+        nl = self.nearest_limit
+        (img, depth_raw, camera_mat_gt, scale_mat, img_idx, pose_gt, depth_mask) = self.process_data_dict(data)
+        if use_ref_imgs:
+            (ref_img, depth_ref_raw, ref_idx, ref_pose_gt) = self.process_data_reference(data)
+        device = self.device
+        batch_size, _, h, w = img.shape
+        _, _, h_depth, w_depth = depth_raw.shape
+        kwargs = dict()
+        kwargs['t_list'] = self.pose_param_net.get_t()
+        kwargs['weights'] = weights
+        kwargs['rgb_loss_type'] = rgb_loss_type
+        img_idx_i = int(img_idx)
+
+        num_cams = self.pose_param_net.num_cams
+        c2w = self.pose_param_net(img_idx_i)                       # exp-map kernel
+        world_mat = _ops.Mat4Inverse.apply(c2w).unsqueeze(0)       # model/training.py:257
+
+        ss_in = None
+        if self.distortion_net is not None:
+            ss_in = self.distortion_net.scale_shift(img_idx_i)     # [scale, shift] on device, no host sync
+        if self.optimizer_focal:
+            fxfy = self.focal_net(0)
+            pad = torch.zeros(4, device=device)
+            one = torch.ones(1, device=device)
+            camera_mat = torch.cat([fxfy[0:1], pad, -fxfy[1:2], pad, -one, pad, one]).view(1, 4, 4)
+        else:
+            camera_mat = camera_mat_gt
+
+        # ray choice: same draw as the reference (model/training.py:277); ranks draw the SAME global batch
+        if self.fixed_ray_idx is not None:
+            ray_idx = self.fixed_ray_idx.to(device)
+        else:
+            ray_idx = torch.randperm(h * w, device=device)[:n_points]
+            if data.get('img.dpt') is None:
+                depth_mask_flat = torch.flatten(depth_mask)
+                while not depth_mask_flat[ray_idx].any():
+                    print('No valid depths found, resampling...')
+                    ray_idx = torch.randperm(h * w, device=device)[:n_points]
+        n_global = ray_idx.numel()
+        lo, hi = self.dp.shard(n_global)
+        ray_idx_local = ray_idx[lo:hi].contiguous()
+
+        # fused gather: pixels, rgb_gt and depth*scale+shift for the selected rays only
+        pixels, rgb_gt, depth_sel = _ops.GatherRays.apply(ray_idx_local, img[0], depth_raw[0, 0], ss_in, h, w)
+        rgb_gt = rgb_gt.unsqueeze(0)
+
+        out_dict = None
+        if render_model:
+            renderer = self.model.renderer
+            S = renderer.cfg['num_points'] - renderer.cfg['outside_steps']
+            if self.fixed_noise is not None:
+                noise = self.fixed_noise.to(device).reshape(n_global, S)[lo:hi]
+            elif not eval_mode:
+                # the reference draws (1, R, S) inside the renderer (model/rendering.py:190)
+                noise = torch.rand(1, n_global, S, device=device).reshape(n_global, S)[lo:hi]
+            else:
+                noise = None
+            out_dict = renderer(pixels.unsqueeze(0), depth_sel.reshape(1, -1, 1), camera_mat, world_mat, scale_mat,
+                                self.rendering_technique, add_noise=noise is not None, eval_=eval_mode, it=it, noise=noise,
+                                lazy_mask=True)
+            rendered_rgb = out_dict['rgb']
+            rendered_depth = out_dict['depth_pred_dense']
+            gt_depth = out_dict['depth_gt_dense']
+            kwargs['depth_mask'] = out_dict['mask']
+        else:
+            rendered_rgb = rendered_depth = gt_depth = None
+
+        if use_ref_imgs:
+            ref_idx_i = int(ref_idx)
+            c2w_ref = self.pose_param_net(ref_idx_i)
+            ss_ref = self.distortion_net.scale_shift(ref_idx_i) if self.distortion_net is not None else None
+            if self.detach_ref_img:
+                c2w_ref = c2w_ref.detach()
+                ss_ref = ss_ref.detach() if ss_ref is not None else None
+            if img_idx_i < (num_cams - 1):
+                d1_raw, d2_raw, ss1, ss2 = depth_raw, depth_ref_raw, ss_in, ss_ref
+                img1, img2 = img, ref_img
+                # ref_Rt @ inverse(world_mat) with inverse(world_mat) == c2w (model/training.py:329)
+                Rt_rel_12 = _ops.Mat4Inverse.apply(c2w_ref) @ c2w
+            else:
+                d1_raw, d2_raw, ss1, ss2 = depth_ref_raw, depth_raw, ss_ref, ss_in
+                img1, img2 = ref_img, img
+                Rt_rel_12 = world_mat[0] @ c2w_ref                 # world_mat @ inverse(ref_Rt) (model/training.py:344)
+            R_rel_12 = Rt_rel_12[:3, :3]
+            t_rel_12 = Rt_rel_12[:3, 3]
+            scale1 = ss1[0] if ss1 is not None else None
+
+            ratio = self.pc_ratio
+            h4, w4 = int(h_depth / ratio), int(w_depth / ratio)
+            pc1 = _ops.Backproject.apply(d1_raw, ss1, camera_mat, h4, w4, nl)   # (P,3)
+            pc2 = _ops.Backproject.apply(d2_raw, ss2, camera_mat, h4, w4, nl)
+
+            if weights['rgb_s_weight'] != 0.0:
+                img1r = _ops.resize_bilinear(img1[0], h4, w4)
+                img2r = _ops.resize_bilinear(img2[0], h4, w4)
+                pc1_in = pc1.detach() if self.detach_rgbs_scale else pc1
+                rgb_pc1, rgb_pc1_proj, valid = _ops.Reproject.apply(img1r, img2r, pc1_in, R_rel_12, t_rel_12, camera_mat, nl)
+                kwargs['rgb_pc1'] = rgb_pc1.view(batch_size, h4, w4, 3)
+                kwargs['rgb_pc1_proj'] = rgb_pc1_proj.view(batch_size, h4, w4, 3)
+                kwargs['valid_points'] = valid.view(batch_size, h4, w4, 1)
+            if self.scale_pcs and scale1 is not None:
+                pc1 = pc1 / scale1
+                pc2 = pc2 / scale1
+            kwargs['X'] = (pc1 @ R_rel_12.transpose(0, 1) + t_rel_12).unsqueeze(0)
+            kwargs['Y'] = pc2.unsqueeze(0)
+            kwargs['sample_resolution'] = (h4, w4)
+            kwargs['rt_12'] = Rt_rel_12.unsqueeze(0)
+            if weights['t_cycle_weight'] != 0.0:
+                world_mat_gt = torch.inverse(pose_gt).unsqueeze(0)
+                ref_Rt_gt = torch.inverse(ref_pose_gt).unsqueeze(0)
+                if img_idx_i < (num_cams - 1):
+                    kwargs['rt_12_gt'] = ref_Rt_gt @ torch.inverse(world_mat_gt)
+                else:
+                    kwargs['rt_12_gt'] = world_mat_gt @ torch.inverse(ref_Rt_gt)
+
+        if render_model and self.detach_gt_depth:
+            gt_depth = gt_depth.detach()
+        loss_dict = self.loss(rendered_rgb, rgb_gt, rendered_depth, gt_depth, **kwargs)
+        if self.optimizer_focal:
+            loss_dict['focalx'] = fxfy[0] / camera_mat_gt[0, 0, 0]
+            loss_dict['focaly'] = fxfy[1] / camera_mat_gt[0, 1, 1]
+        if ss_in is not None:
+            loss_dict['scale'] = ss_in[0:1]
+            loss_dict['shift'] = ss_in[1:2]
+        return loss_dict
+
+    def render_visdata(self, data, resolution, it, out_render_path):
+        """Full-frame preview render (model/training.py:103-165) -> uint8 (h,w,3) image; file output is left to the caller."""
+        (img, depth_input, camera_mat, scale_mat, img_idx, *other) = self.process_data_dict(data)
+        h, w = resolution
+        c2w = self.pose_param_net(int(img_idx))
+        world_mat = _ops.Mat4Inverse.apply(c2w.detach()).unsqueeze(0)
+        _, pixels = _ops.pixel_grid(h, w, self.device)
+        with torch.no_grad():
+            out = self.model.renderer(pixels.unsqueeze(0), torch.ones(1, h * w, 1, device=self.device), camera_mat, world_mat,
+                                      scale_mat, self.rendering_technique, add_noise=False, eval_=True, it=it)
+        rgb = out['rgb'].view(h, w, 3)
+        return (rgb * 255).to(torch.uint8).cpu().numpy()

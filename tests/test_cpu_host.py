@@ -1,0 +1,178 @@
+"""CPU-side checks: the C-ABI library builds, loads and exports every symbol the header declares; host logic
+(annealing, sharding, flat gradient buffers); drop-in surface parity with the reference (when it is present);
+multi-process data-parallel plumbing over gloo (world size 2)."""
+import ctypes
+import inspect
+import os
+import re
+import subprocess
+import sys
+
+import pytest
+import torch
+
+from util import PKG, ROOT, syn
+
+
+def _header_functions():
+    txt = open(os.path.join(ROOT, "include", "nope_nerf_b200.h")).read()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    return sorted(set(re.findall(r"\b(nnb_[a-z0-9_]+)\s*\(", txt)))
+
+
+def test_library_builds_and_exports_every_declared_symbol():
+    sys.path.insert(0, PKG)
+    import build as nnb_build
+    so = nnb_build.build()
+    assert os.path.exists(so)
+    lib = ctypes.CDLL(so)
+    names = _header_functions()
+    assert len(names) >= 40
+    for n in names:
+        assert hasattr(lib, n), "missing export %s" % n
+    from model import _cabi
+    assert sorted(_cabi.SIGNATURES.keys()) == names, set(names) ^ set(_cabi.SIGNATURES.keys())
+    lib.nnb_version.restype = ctypes.c_int
+    assert lib.nnb_version() >= 100
+    lib.nnb_error_string.restype = ctypes.c_char_p
+    assert b"workspace" in lib.nnb_error_string(-2)
+
+
+def test_sass_is_sm100a():
+    so = os.path.join(PKG, "libnope_nerf_b200.so")
+    if not os.path.exists(so):
+        pytest.skip("library not built")
+    out = subprocess.run(["cuobjdump", "-lelf", so], capture_output=True, text=True).stdout
+    assert "sm_100a" in out, out[:500]
+
+
+def test_product_refuses_cpu_tensors():
+    from model import _ops
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        _ops.RgbLoss.apply(torch.zeros(1, 4, 3), torch.zeros(1, 4, 3))
+
+
+def test_product_never_imports_oracle():
+    for root, _, files in os.walk(PKG):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                txt = open(os.path.join(root, f)).read()
+                assert "nope_oracle" not in txt and "from oracle" not in txt and "import oracle" not in txt, f
+
+
+def test_state_dict_layout():
+    import model as mdl
+    cfg = syn.default_cfg()
+    nerf = mdl.OfficialStaticNerf(cfg)
+    net = mdl.get_model(mdl.Renderer(nerf, cfg["rendering"], device="cpu"), cfg, device="cpu")
+    sd = net.state_dict()
+    want = {"renderer.model.layers0.0.weight": (256, 63), "renderer.model.layers1.0.weight": (256, 319),
+            "renderer.model.fc_density.weight": (1, 256), "renderer.model.fc_feature.weight": (256, 256),
+            "renderer.model.rgb_layers.0.weight": (128, 283), "renderer.model.fc_rgb.weight": (3, 128)}
+    for k, shp in want.items():
+        assert tuple(sd[k].shape) == shp
+    assert len(sd) == 24 and sum(v.numel() for v in sd.values()) == 595844
+    assert float(sd["renderer.model.fc_density.bias"]) == pytest.approx(0.1)
+    assert len([m for m in net.modules() if isinstance(m, torch.nn.Linear)]) == 12  # train.py:347-350 'reset' mode
+    pose = mdl.LearnPose(5, True, False, cfg, init_c2w=torch.eye(4).repeat(5, 1, 1))
+    assert list(pose.state_dict().keys()) == ["init_c2w", "r", "t"] and not pose.t.requires_grad
+    assert list(mdl.LearnPose(5, True, True, cfg).state_dict().keys()) == ["r", "t"]
+    assert list(mdl.Learn_Distortion(5, True, True, cfg).state_dict().keys()) == ["global_scales", "global_shifts"]
+
+
+def test_surface_matches_reference():
+    """Constructor / forward signatures and exported names equal the reference's (only where it is mounted)."""
+    from oracle import ref_harness
+    if not ref_harness.reference_available():
+        pytest.skip("reference tree not mounted")
+    code = r'''
+import sys, inspect, json
+sys.path.insert(0, %r)
+from oracle import ref_harness
+ref = ref_harness.load_reference().model
+names = ["OfficialStaticNerf", "Renderer", "nope_nerf", "LearnPose", "Learn_Distortion", "LearnFocal", "Trainer", "Trainer_pose", "CheckpointIO"]
+out = {}
+for n in names:
+    c = getattr(ref, n)
+    out[n] = {m: list(inspect.signature(getattr(c, m)).parameters) for m in ("__init__", "forward", "train_step", "compute_loss", "save", "load", "get_t")
+              if hasattr(c, m) and callable(getattr(c, m))}
+out["get_model"] = list(inspect.signature(ref.get_model).parameters)
+import yaml
+cfg = yaml.safe_load(open(ref_harness.REFERENCE_ROOT + "/configs/default.yaml"))
+net = ref.get_model(ref.Renderer(ref.OfficialStaticNerf(cfg), cfg["rendering"], device="cpu"), cfg, device="cpu")
+out["state"] = {k: list(v.shape) for k, v in net.state_dict().items()}
+print(json.dumps(out))
+''' % ROOT
+    import json
+    res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stderr[-2000:]
+    ref = json.loads(res.stdout.strip().splitlines()[-1])
+    import model as mdl
+    for n, methods in ref.items():
+        if n in ("get_model", "state"):
+            continue
+        c = getattr(mdl, n)
+        for m, params in methods.items():
+            mine = list(inspect.signature(getattr(c, m)).parameters)
+            assert mine[:len(params)] == params or set(params) <= set(mine), (n, m, params, mine)
+    assert list(inspect.signature(mdl.get_model).parameters) == ref["get_model"]
+    cfg = syn.default_cfg()
+    net = mdl.get_model(mdl.Renderer(mdl.OfficialStaticNerf(cfg), cfg["rendering"], device="cpu"), cfg, device="cpu")
+    assert {k: list(v.shape) for k, v in net.state_dict().items()} == ref["state"]
+
+
+def test_anneal_and_weights_match_oracle():
+    import model as mdl
+    from oracle import nope_oracle as O
+    cfg = syn.default_cfg()["training"]
+    tr = mdl.Trainer(None, None, cfg, device="cpu")
+    for epoch in (0, 9999, 10000, 10500, 11999, 12000, 20000):
+        w, kind = O.step_weights(cfg, epoch, cfg["scheduling_start"])
+        for k in w:
+            assert tr.anneal(cfg[k][0], cfg[k][1], cfg["scheduling_start"], cfg["annealing_epochs"], epoch) == w[k]
+
+
+def test_shard_ranges_partition():
+    from model.parallel import shard_range
+    for n in (0, 1, 7, 4096, 65536, 465750):
+        for world in (1, 2, 3, 4, 8):
+            spans = [shard_range(n, r, world) for r in range(world)]
+            assert spans[0][0] == 0 and spans[-1][1] == n
+            assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+            sizes = [b - a for a, b in spans]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def _gloo_worker(rank, world, port, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    sys.path.insert(0, PKG)
+    import torch.distributed as dist
+    from model import parallel
+    dp = parallel.init_from_env(backend="gloo")
+    assert dp.world_size == world and dp.rank == rank
+    # every rank draws the same global batch and takes its shard: the union is the 1-rank batch
+    idx = syn.ray_choice(24, 32, 100, seed=42)
+    lo, hi = dp.shard(idx.numel())
+    got = dp.gather_rows(idx[lo:hi].reshape(-1, 1).float(), idx.numel()).reshape(-1).long()
+    assert torch.equal(got, idx)
+    # gradient averaging over one flat buffer; a param without grad on one rank contributes zeros
+    torch.manual_seed(0)
+    ps = [torch.nn.Parameter(torch.randn(3, 5)), torch.nn.Parameter(torch.randn(7)), torch.nn.Parameter(torch.randn(2))]
+    ps[0].grad = torch.full((3, 5), float(rank + 1))
+    ps[1].grad = torch.arange(7.0) * (rank + 1)
+    if rank == 0:
+        ps[2].grad = torch.ones(2)
+    dp.allreduce_grads(ps)
+    mean = sum(r + 1 for r in range(world)) / world
+    assert torch.allclose(ps[0].grad, torch.full((3, 5), mean))
+    assert torch.allclose(ps[1].grad, torch.arange(7.0) * mean)
+    assert torch.allclose(ps[2].grad, torch.ones(2) / world)
+    open(os.path.join(out_dir, "ok%d" % rank), "w").write("ok")
+    dist.destroy_process_group()
+
+
+def test_data_parallel_plumbing_gloo_world2(tmp_path):
+    import torch.multiprocessing as mp
+    port = 29500 + (os.getpid() % 2000)
+    mp.spawn(_gloo_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    assert os.path.exists(tmp_path / "ok0") and os.path.exists(tmp_path / "ok1")

@@ -1,0 +1,115 @@
+"""GPU parity of the whole training step (Trainer.compute_loss + backward) against the fixtures produced by the
+reference's own Trainer on the same scene, weights, ray choice and jitter; plus optimiser and API checks."""
+import pytest
+import torch
+
+from util import assert_close, build_models, dev, max_err, syn, to_dev
+
+pytestmark = pytest.mark.gpu
+
+LOSS_KEYS = ("loss", "loss_rgb", "loss_depth", "l2_mean", "loss_dist_1st", "loss_dist_2nd", "loss_pc", "loss_rgb_s",
+             "loss_depth_consistency", "loss_t_cycle")
+
+
+def _trainer(cfg, scene, setup, depth_loss_type, n_rays):
+    import model as mdl
+    tcfg = dict(cfg["training"])
+    tcfg["depth_loss_type"] = depth_loss_type
+    tcfg["n_training_points"] = n_rays
+    nerf, renderer, net, pose, dist = build_models(cfg, scene["n"], scene, r0=setup["r"], t0=setup["t"],
+                                                   scales=setup["scales"], shifts=setup["shifts"])
+    opt = torch.optim.Adam(net.parameters(), lr=1e-3)
+    opt_p = torch.optim.Adam(pose.parameters(), lr=5e-4)
+    opt_d = torch.optim.Adam(dist.parameters(), lr=5e-4)
+    tr = mdl.Trainer(net, opt, tcfg, device=dev(), optimizer_pose=opt_p, pose_param_net=pose, optimizer_distortion=opt_d,
+                     distortion_net=dist)
+    return tr, nerf, pose, dist
+
+
+def test_compute_loss_and_grads_vs_reference(golden):
+    g = golden("render_step")
+    cfg = syn.default_cfg()
+    scene = syn.make_scene("tiny")
+    R = syn.SHAPES["tiny"][3]
+    for name, rec in g["step"].items():
+        c = rec["case"]
+        tr, nerf, pose, dist = _trainer(cfg, scene, g["step_setup"], c["depth_loss_type"], R)
+        tr.fixed_ray_idx = g["render"]["ray_idx"]
+        tr.fixed_noise = g["render"]["noise"]
+        batch = syn.make_batch(scene, c["idx"], c["ref"])
+        ld = tr.compute_loss(batch, it=1, epoch=c["epoch"], scheduling_start=cfg["training"]["scheduling_start"])
+        assert set(LOSS_KEYS) <= set(ld.keys())
+        for k in LOSS_KEYS + ("scale", "shift"):
+            assert torch.is_tensor(ld[k]), k
+            print(name, k, "got %.7f want %.7f" % (float(ld[k].reshape(-1)[0]), float(rec["loss_dict"][k].reshape(-1)[0])))
+            assert_close(ld[k].reshape(-1).float(), rec["loss_dict"][k].float(), 2e-4, 2e-5, "%s/%s" % (name, k))
+        ld["loss"].backward()
+        assert_close(pose.r.grad, rec["grad_r"], 5e-3, 5e-3 * float(rec["grad_r"].abs().max()), name + "/grad_r")
+        assert_close(pose.t.grad, rec["grad_t"], 5e-3, 5e-3 * float(rec["grad_t"].abs().max()), name + "/grad_t")
+        if rec["grad_scales"] is not None:
+            assert_close(dist.global_scales.grad, rec["grad_scales"], 5e-3, 5e-3 * float(rec["grad_scales"].abs().max()), name + "/grad_scales")
+            assert_close(dist.global_shifts.grad, rec["grad_shifts"], 5e-3, 5e-3 * float(rec["grad_shifts"].abs().max()), name + "/grad_shifts")
+        if "mlp_grads" in rec:
+            worst = 0.0
+            for k, p in nerf.named_parameters():
+                ref = rec["mlp_grads"][k]
+                e = float((p.grad.cpu() - ref).abs().max() / ref.abs().max().clamp_min(1e-12))
+                worst = max(worst, e)
+                assert e < 5e-3, "%s grad %s scale-relative err %.3e" % (name, k, e)
+            print(name, "worst MLP grad scale-relative err %.3e" % worst)
+
+
+def test_train_step_runs_and_decreases_loss():
+    cfg = syn.default_cfg()
+    scene = syn.make_scene("tiny")
+    r0, t0 = syn.init_pose_params(scene["n"])
+    setup = {"r": r0, "t": t0, "scales": torch.ones(scene["n"], 1), "shifts": torch.zeros(scene["n"], 1)}
+    tr, nerf, pose, dist = _trainer(cfg, scene, setup, "l1", 256)
+    torch.manual_seed(0)
+    batch = syn.make_batch(scene, 1, 2)
+    first = last = None
+    for it in range(30):
+        ld = tr.train_step(batch, it=it, epoch=0, scheduling_start=cfg["training"]["scheduling_start"])
+        v = float(ld["loss_rgb"])
+        first = v if first is None else first
+        last = v
+    assert last < first, (first, last)
+
+
+def test_fused_adam_matches_torch():
+    from model import _ops
+    g = torch.Generator().manual_seed(3)
+    p = torch.randn(10007, generator=g)
+    ref = p.clone().requires_grad_(True)
+    opt = torch.optim.Adam([ref], lr=1e-3)
+    pd = p.to(dev())
+    m, v = torch.zeros_like(pd), torch.zeros_like(pd)
+    for step in range(1, 6):
+        gr = torch.randn(10007, generator=g)
+        ref.grad = gr.clone()
+        opt.step()
+        _ops.adam_step(pd, gr.to(dev()), m, v, 1e-3, 0.9, 0.999, 1e-8, step)
+    assert_close(pd, ref.detach(), 1e-5, 1e-6, "adam")
+
+
+def test_checkpoint_roundtrip_keys(tmp_path):
+    import model as mdl
+    cfg = syn.default_cfg()
+    _, _, net, pose, dist = build_models(cfg, 4, syn.make_scene("tiny"))
+    io = mdl.CheckpointIO(str(tmp_path), model=net)
+    io.save("model.pt", epoch_it=3, it=7)
+    _, _, net2, _, _ = build_models(cfg, 4, syn.make_scene("tiny"), state=syn.init_mlp_state(7))
+    io2 = mdl.CheckpointIO(str(tmp_path), model=net2)
+    scalars = io2.load("model.pt")
+    assert scalars["epoch_it"] == 3 and scalars["it"] == 7
+    for (k1, v1), (k2, v2) in zip(net.state_dict().items(), net2.state_dict().items()):
+        assert k1 == k2 and torch.equal(v1.cpu(), v2.cpu())
+    assert list(pose.state_dict().keys()) == ["init_c2w", "r", "t"]
+    assert list(dist.state_dict().keys()) == ["global_scales", "global_shifts"]
+
+
+def test_no_cpu_fallback():
+    """Product ops must refuse CPU tensors instead of silently computing somewhere else."""
+    from model import _ops
+    with pytest.raises(RuntimeError):
+        _ops.RgbLoss.apply(torch.zeros(1, 4, 3), torch.zeros(1, 4, 3))
