@@ -193,6 +193,9 @@ def render_nograd(cfg, params, packed, origin, dirs, noise, want_aux=True):
     """Forward only (eval / render loops).  Returns rgb, dist, weights, alpha, z (aux None if not wanted)."""
     R, S = cfg.n_rays, cfg.n_samples
     dev = dirs.device
+    origin, dirs = f32(origin), f32(dirs)
+    noise = f32(noise).reshape(R, S) if noise is not None else None
+    params = [f32(p) for p in params]
     rgb, dist = torch.empty(R, 3, device=dev), torch.empty(R, device=dev)
     w = torch.empty(R, S, device=dev) if want_aux else None
     a = torch.empty(R, S, device=dev) if want_aux else None
