@@ -28,7 +28,8 @@ constexpr int TC_MAX_STAGES = 512;
 constexpr int TC_RING = 5;               // weight ring slots
 constexpr uint32_t TC_SLOT = 8192;       // bytes per slot (256 rows x 16 k x bf16)
 
-enum ASrc : uint8_t { A_ACT = 0, A_ENC = 1, A_AUX = 2 };
+enum ASrc : uint8_t { A_ACT = 0, A_ENC = 1, A_AUX = 2, A_ACT128 = 3, A_DSMALL = 4 };
+enum Epi : uint8_t { EPI_DIR = 0, EPI_FEAT = 1, EPI_MASK = 2, EPI_ENC = 3 };
 
 // One k-step (K = 16) of one layer.
 struct TcStage {
@@ -50,10 +51,13 @@ struct TcPack {
   int32_t col0, col_end;
   int32_t row0;
   int32_t transposed;
+  int32_t n_valid;  // rows n >= n_valid are zero (0 = all rows valid)
 };
 
 __constant__ TcStage c_fwd_stages[TC_MAX_STAGES];
 __constant__ TcPack c_fwd_pack[TC_MAX_STAGES];
+__constant__ TcStage c_bwd_stages[TC_MAX_STAGES];
+__constant__ TcPack c_bwd_pack[TC_MAX_STAGES];
 
 struct Schedule {
   std::vector<TcStage> st;
@@ -90,6 +94,32 @@ Schedule build_fwd_schedule() {
   return S;
 }
 
+// backward (data-gradient) schedule: B operand = W^T stage images; `layer` = Epi kind, `pad` = saved-activation slot
+Schedule build_bwd_schedule() {
+  Schedule S;
+  auto add_step = [&](int n, ASrc src, int ksteps, int wparam, int ld, int row0, int n_valid, int epi, int slot, bool den_extra) {
+    const size_t first = S.st.size();
+    for (int j = 0; j < ksteps; ++j)
+      S.add(epi, n, src, j, j == 0, (j == ksteps - 1) && !den_extra, TcPack{(int16_t)wparam, -1, ld, 16 * j, 16 * ksteps, row0, 1, n_valid});
+    if (den_extra) S.add(epi, n, A_DSMALL, 0, false, true, TcPack{P_DEN, -1, 256, -3, 1, 0, 1, 0});
+    for (size_t i = first; i < S.st.size(); ++i) S.st[i].pad = (uint8_t)slot;
+  };
+  add_step(32, A_ACT128, 8, P_RGB0, 283, 256, 27, EPI_DIR, 0, false);
+  add_step(256, A_ACT128, 8, P_RGB0, 283, 0, 0, EPI_FEAT, 0, false);
+  add_step(256, A_ACT, 16, P_FEAT, 256, 0, 0, EPI_MASK, 7, true);
+  for (int L = 7; L >= 5; --L) add_step(256, A_ACT, 16, P_L0 + 2 * L, 256, 0, 0, EPI_MASK, L - 1, false);
+  add_step(64, A_ACT, 16, P_L0 + 8, 319, 256, 63, EPI_ENC, 0, false);
+  add_step(256, A_ACT, 16, P_L0 + 8, 319, 0, 0, EPI_MASK, 3, false);
+  for (int L = 3; L >= 1; --L) add_step(256, A_ACT, 16, P_L0 + 2 * L, 256, 0, 0, EPI_MASK, L - 1, false);
+  add_step(64, A_ACT, 16, P_L0, 63, 0, 63, EPI_ENC, 1, false);
+  return S;
+}
+
+const Schedule &bwd_schedule() {
+  static Schedule s = build_bwd_schedule();
+  return s;
+}
+
 const Schedule &fwd_schedule() {
   static Schedule s = build_fwd_schedule();
   return s;
@@ -101,15 +131,14 @@ struct PackPtrs { const float *p[NNB_NUM_PARAMS]; };
 __global__ void tc_pack_kernel(PackPtrs P, uint8_t *out, int n_stages, int which) {
   const int i = blockIdx.x;
   if (i >= n_stages) return;
-  const TcStage st = c_fwd_stages[i];
-  const TcPack pk = c_fwd_pack[i];
-  (void)which;
+  const TcStage st = which ? c_bwd_stages[i] : c_fwd_stages[i];
+  const TcPack pk = which ? c_bwd_pack[i] : c_fwd_pack[i];
   for (int n = threadIdx.x; n < st.n; n += blockDim.x) {
     __nv_bfloat16 row[16];
 #pragma unroll
     for (int kk = 0; kk < 16; ++kk) {
       float v = 0.f;
-      if (pk.wparam >= 0 && pk.col0 + kk < pk.col_end) {
+      if (pk.wparam >= 0 && pk.col0 + kk >= 0 && pk.col0 + kk < pk.col_end && (pk.n_valid == 0 || n < pk.n_valid)) {
         const float *W = P.p[pk.wparam];
         v = pk.transposed ? W[(size_t)(pk.col0 + kk) * pk.ld + pk.row0 + n] : W[(size_t)n * pk.ld + pk.col0 + kk];
       }
@@ -154,7 +183,34 @@ struct FwdArgs {
   int n_rays, S, n_stages;
   float near_, far_;
   int softplus, white, use_dir;
+  uint8_t *ws_fwd;   // SAVE: per-ray activation images (FWD_TILE_BYTES each)
+  float4 *ws_s;      // SAVE: per-sample {rgb_s, raw density}
 };
+
+// saved-activation images of one ray (bf16, operand-image layout), written by the forward when SAVE, read by the
+// backward (relu masks) and by the weight-gradient kernel (X operands)
+constexpr uint32_t FW_H = 0;                 // H0..H7: 8 x 65536 (layer l at l*65536)
+constexpr uint32_t FW_FEAT = 8 * 65536;      // fc_feature output (no activation)
+constexpr uint32_t FW_HC = 9 * 65536;        // relu(rgb_layers.0), 128 cols (gs 2048)
+constexpr uint32_t FW_ENC = FW_HC + 32768;   // positional encoding, 64 cols
+constexpr uint32_t FW_AUX = FW_ENC + 16384;  // view-direction encoding + ones, 32 cols
+constexpr uint32_t FWD_TILE_BYTES = FW_AUX + 8192;
+// gradient images written by the backward, read by the weight-gradient kernel
+constexpr uint32_t BW_DY = 0;                // dY0..dY7
+constexpr uint32_t BW_DYFEAT = 8 * 65536;
+constexpr uint32_t BW_DYRGB0 = 9 * 65536;    // 128 cols
+constexpr uint32_t BW_DSMALL = BW_DYRGB0 + 32768;  // 16 cols: d_raw rgb (3), d_raw density (1)
+constexpr uint32_t BWD_TILE_BYTES = BW_DSMALL + 4096;
+
+__device__ __forceinline__ void st_global_v4(void *p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.global.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+// one 16-byte chunk (8 bf16) of an operand image: shared-memory copy (MMA operand) and optional global copy
+template <bool SAVE>
+__device__ __forceinline__ void put_chunk(uint32_t saddr, uint8_t *gaddr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  st_shared_v4(saddr, a, b, c, d);
+  if (SAVE) st_global_v4(gaddr, a, b, c, d);
+}
 
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
 
@@ -169,7 +225,9 @@ __device__ __forceinline__ float warp_incl_prod(float v, int lane) {
 
 // Sampling + positional encoding of one sample -> its rows of the enc (64 cols) and aux (32 cols) operand images.
 // Column order follows encode_position (model/official_nerf.py:99-119): [x, sin(2^l x), cos(2^l x)]_l, 3 wide each.
-__device__ __forceinline__ void write_encodings(uint32_t enc_row, uint32_t aux_row, const float p[3], const float v[3]) {
+template <bool SAVE>
+__device__ __forceinline__ void write_encodings(uint32_t enc_row, uint32_t aux_row, uint8_t *genc, uint8_t *gaux, const float p[3],
+                                                const float v[3]) {
   float e[64];
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
@@ -187,8 +245,8 @@ __device__ __forceinline__ void write_encodings(uint32_t enc_row, uint32_t aux_r
   e[63] = 0.f;
 #pragma unroll
   for (int g = 0; g < 8; ++g)
-    st_shared_v4(enc_row + g * 128, pack_bf16(e[8 * g], e[8 * g + 1]), pack_bf16(e[8 * g + 2], e[8 * g + 3]),
-                 pack_bf16(e[8 * g + 4], e[8 * g + 5]), pack_bf16(e[8 * g + 6], e[8 * g + 7]));
+    put_chunk<SAVE>(enc_row + g * 128, genc + g * 128, pack_bf16(e[8 * g], e[8 * g + 1]), pack_bf16(e[8 * g + 2], e[8 * g + 3]),
+                    pack_bf16(e[8 * g + 4], e[8 * g + 5]), pack_bf16(e[8 * g + 6], e[8 * g + 7]));
   float a[32];
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
@@ -206,10 +264,26 @@ __device__ __forceinline__ void write_encodings(uint32_t enc_row, uint32_t aux_r
   a[27] = 1.f; a[28] = 1.f; a[29] = 0.f; a[30] = 0.f; a[31] = 0.f;
 #pragma unroll
   for (int g = 0; g < 4; ++g)
-    st_shared_v4(aux_row + g * 128, pack_bf16(a[8 * g], a[8 * g + 1]), pack_bf16(a[8 * g + 2], a[8 * g + 3]),
-                 pack_bf16(a[8 * g + 4], a[8 * g + 5]), pack_bf16(a[8 * g + 6], a[8 * g + 7]));
+    put_chunk<SAVE>(aux_row + g * 128, gaux + g * 128, pack_bf16(a[8 * g], a[8 * g + 1]), pack_bf16(a[8 * g + 2], a[8 * g + 3]),
+                    pack_bf16(a[8 * g + 4], a[8 * g + 5]), pack_bf16(a[8 * g + 6], a[8 * g + 7]));
 }
 
+// 32 fp32 accumulator columns -> 4 chunks of 8 bf16 (optionally relu) into the operand image (+ global copy)
+template <bool RELU, bool SAVE>
+__device__ __forceinline__ void store32(uint32_t saddr, uint8_t *gaddr, const uint32_t (&v)[32]) {
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    uint32_t w[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float a = __uint_as_float(v[8 * g + 2 * k]), b = __uint_as_float(v[8 * g + 2 * k + 1]);
+      w[k] = RELU ? pack_bf16_relu(a, b) : pack_bf16(a, b);
+    }
+    put_chunk<SAVE>(saddr + g * 128, gaddr + g * 128, w[0], w[1], w[2], w[3]);
+  }
+}
+
+template <bool SAVE>
 __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const uint32_t sbase = smem_u32(smem);
@@ -290,6 +364,8 @@ __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
       const int ray_raw = 2 * pair + t;
       const bool valid = ray_raw < A.n_rays;
       const int ray = valid ? ray_raw : A.n_rays - 1;
+      uint8_t *gtile = SAVE ? A.ws_fwd + (size_t)ray * FWD_TILE_BYTES : nullptr;
+      const bool sv = SAVE && valid;
       // ---- prologue: stratified depth, sample position, encodings
       const float z = z_sample(row, A.S, A.near_, A.far_, A.noise ? A.noise + (size_t)ray * A.S : nullptr);
       {
@@ -300,13 +376,15 @@ __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
           p[c] = __fadd_rn(A.origin[c], __fmul_rn(d, z));
           v[c] = A.use_dir ? -d : 1.0f;
         }
-        write_encodings(enc_row, aux_row, p, v);
+        if (SAVE && valid) write_encodings<true>(enc_row, aux_row, gtile + FW_ENC + (row >> 3) * GS_ENC + (row & 7) * 16,
+                                                 gtile + FW_AUX + (row >> 3) * GS_AUX + (row & 7) * 16, p, v);
+        else write_encodings<false>(enc_row, aux_row, nullptr, nullptr, p, v);
       }
       fence_async_smem();
       tc_fence_before();
       mbar_arrive(bar_act);
 
-      float alpha = 0.f, r_s = 0.f, g_s = 0.f, b_s = 0.f;
+      float alpha = 0.f, r_s = 0.f, g_s = 0.f, b_s = 0.f, raw_den = 0.f;
       for (int L = 0; L < 10; ++L) {
         mbar_wait(bar_acc, acc_par);
         acc_par ^= 1;
@@ -339,37 +417,19 @@ __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
               }
             }
             const uint32_t dst = act_row + (c0 >> 3) * 128;
+            uint8_t *gdst = sv ? gtile + (uint32_t)L * 65536u + (row >> 3) * GS_ACT + (row & 7) * 16 + (c0 >> 3) * 128 : nullptr;
             if (L != 8) {
-#pragma unroll
-              for (int g = 0; g < 4; ++g)
-                st_shared_v4(dst + g * 128, pack_bf16_relu(__uint_as_float(v0[8 * g]), __uint_as_float(v0[8 * g + 1])),
-                             pack_bf16_relu(__uint_as_float(v0[8 * g + 2]), __uint_as_float(v0[8 * g + 3])),
-                             pack_bf16_relu(__uint_as_float(v0[8 * g + 4]), __uint_as_float(v0[8 * g + 5])),
-                             pack_bf16_relu(__uint_as_float(v0[8 * g + 6]), __uint_as_float(v0[8 * g + 7])));
-#pragma unroll
-              for (int g = 0; g < 4; ++g)
-                st_shared_v4(dst + (4 + g) * 128, pack_bf16_relu(__uint_as_float(v1[8 * g]), __uint_as_float(v1[8 * g + 1])),
-                             pack_bf16_relu(__uint_as_float(v1[8 * g + 2]), __uint_as_float(v1[8 * g + 3])),
-                             pack_bf16_relu(__uint_as_float(v1[8 * g + 4]), __uint_as_float(v1[8 * g + 5])),
-                             pack_bf16_relu(__uint_as_float(v1[8 * g + 6]), __uint_as_float(v1[8 * g + 7])));
+              if (sv) { store32<true, true>(dst, gdst, v0); store32<true, true>(dst + 512, gdst + 512, v1); }
+              else { store32<true, false>(dst, nullptr, v0); store32<true, false>(dst + 512, nullptr, v1); }
             } else {
-#pragma unroll
-              for (int g = 0; g < 4; ++g)
-                st_shared_v4(dst + g * 128, pack_bf16(__uint_as_float(v0[8 * g]), __uint_as_float(v0[8 * g + 1])),
-                             pack_bf16(__uint_as_float(v0[8 * g + 2]), __uint_as_float(v0[8 * g + 3])),
-                             pack_bf16(__uint_as_float(v0[8 * g + 4]), __uint_as_float(v0[8 * g + 5])),
-                             pack_bf16(__uint_as_float(v0[8 * g + 6]), __uint_as_float(v0[8 * g + 7])));
-#pragma unroll
-              for (int g = 0; g < 4; ++g)
-                st_shared_v4(dst + (4 + g) * 128, pack_bf16(__uint_as_float(v1[8 * g]), __uint_as_float(v1[8 * g + 1])),
-                             pack_bf16(__uint_as_float(v1[8 * g + 2]), __uint_as_float(v1[8 * g + 3])),
-                             pack_bf16(__uint_as_float(v1[8 * g + 4]), __uint_as_float(v1[8 * g + 5])),
-                             pack_bf16(__uint_as_float(v1[8 * g + 6]), __uint_as_float(v1[8 * g + 7])));
+              if (sv) { store32<false, true>(dst, gdst, v0); store32<false, true>(dst + 512, gdst + 512, v1); }
+              else { store32<false, false>(dst, nullptr, v0); store32<false, false>(dst + 512, nullptr, v1); }
             }
           }
           if (L == 7) {
             // density head (model/official_nerf.py:66,77-83): softplus(beta 1, threshold 20) or relu, then 1 - exp(-d)
             const float raw = dsum + sm_small[640];
+            raw_den = raw;
             const float d = A.softplus ? (raw > 20.f ? raw : log1pf(expf(raw))) : fmaxf(raw, 0.f);
             alpha = 1.f - expf(-d);
           }
@@ -385,6 +445,15 @@ __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
             tmem_ld32(tacc + c0, v0);
             tmem_ld_wait();
             const float *w0 = sm_small + 256 + c0, *w1 = w0 + 128, *w2 = w0 + 256;
+            if (sv) {
+              uint8_t *ghc = gtile + FW_HC + (row >> 3) * 2048 + (row & 7) * 16 + (c0 >> 3) * 128;
+#pragma unroll
+              for (int g = 0; g < 4; ++g)
+                st_global_v4(ghc + g * 128, pack_bf16_relu(__uint_as_float(v0[8 * g]), __uint_as_float(v0[8 * g + 1])),
+                             pack_bf16_relu(__uint_as_float(v0[8 * g + 2]), __uint_as_float(v0[8 * g + 3])),
+                             pack_bf16_relu(__uint_as_float(v0[8 * g + 4]), __uint_as_float(v0[8 * g + 5])),
+                             pack_bf16_relu(__uint_as_float(v0[8 * g + 6]), __uint_as_float(v0[8 * g + 7])));
+            }
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
               const float h = fmaxf(__uint_as_float(v0[j]), 0.f);
@@ -396,6 +465,7 @@ __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
           r_s = 1.f / (1.f + expf(-s0));
           g_s = 1.f / (1.f + expf(-s1));
           b_s = 1.f / (1.f + expf(-s2));
+          if (sv) A.ws_s[(size_t)ray * 128 + row] = make_float4(r_s, g_s, b_s, raw_den);
         }
       }
       // ---- compositing over the ray (model/rendering.py:124-126): T = exclusive cumprod(1 - alpha + 1e-6)
@@ -434,6 +504,531 @@ __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
 }  // namespace
 
 // =====================================================================================================================
+// backward (data-gradient chain) kernel
+// =====================================================================================================================
+namespace {
+
+constexpr int BW_RING = 8;
+constexpr uint32_t SB_ACT = 0;                         // 2 x 65536: dY operand image, updated in place layer by layer
+constexpr uint32_t SB_DSMALL = 131072;                 // 2 x 4096 : [128 x 16] d_raw {r,g,b,density}
+constexpr uint32_t SB_RING = SB_DSMALL + 8192;         // BW_RING x 8192
+constexpr uint32_t SB_SMALL = SB_RING + BW_RING * TC_SLOT;  // fp32 w_rgb[384]
+constexpr uint32_t SB_SCAN = SB_SMALL + 384 * 4;       // 2 tiles x 64 floats
+constexpr uint32_t SB_BARS = SB_SCAN + 2 * 64 * 4;
+constexpr uint32_t SB_TOTAL = SB_BARS + 24 * 8 + 16;
+static_assert(SB_TOTAL <= 232448, "shared memory budget");
+
+struct BwdArgs {
+  const uint8_t *wimg;       // backward stage images
+  const uint8_t *ws_fwd;     // saved activations
+  uint8_t *ws_bwd;           // dY images (output)
+  const float4 *ws_s;        // per-sample {rgb_s, raw}
+  const float *origin, *dirs, *alpha, *z_vals;
+  const float *d_rgb, *d_dist, *d_alpha_out, *d_weights_out;
+  const float *w_rgb;
+  float *d_origin, *d_dirs, *d_b_den, *d_b_rgb;   // d_origin / d_b_*: atomically accumulated
+  int n_rays, n_stages;
+  int softplus, white, use_dir;
+};
+
+__device__ __forceinline__ uint4 ld_global_v4(const void *p) {
+  uint4 r;
+  asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+// keep the halves of `d` (packed bf16x2) whose relu output `h` (packed bf16x2, >= 0) is positive
+__device__ __forceinline__ uint32_t relu_mask2(uint32_t d, uint32_t h) {
+  uint32_t m;
+  asm("set.gt.u32.bf16x2 %0, %1, %2;" : "=r"(m) : "r"(h), "r"(0u));
+  return d & m;
+}
+__device__ __forceinline__ float warp_excl_suffix(float v, int lane, float &total) {
+  float inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const float t = __shfl_down_sync(0xffffffffu, inc, o);
+    if (lane + o < 32) inc += t;
+  }
+  total = __shfl_sync(0xffffffffu, inc, 0);
+  const float ex = __shfl_down_sync(0xffffffffu, inc, 1);
+  return lane == 31 ? 0.f : ex;
+}
+// gradient of the positional encoding: x_bar = g[c] + sum_l 2^l (cos(2^l x) g_sin[l] - sin(2^l x) g_cos[l])
+template <int LEVELS>
+__device__ __forceinline__ void enc_backward(const float x[3], const uint32_t *g, float out[3]) {
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    float acc = __uint_as_float(g[c]);
+    float sn, cs, f = 1.f;
+    sincosf(x[c], &sn, &cs);
+#pragma unroll
+    for (int l = 0; l < LEVELS; ++l) {
+      acc = fmaf(f, cs * __uint_as_float(g[3 + 6 * l + c]) - sn * __uint_as_float(g[3 + 6 * l + 3 + c]), acc);
+      const float s2 = 2.f * sn * cs, c2 = 1.f - 2.f * sn * sn;
+      sn = s2; cs = c2; f *= 2.f;
+    }
+    out[c] += acc;
+  }
+}
+
+__global__ void __launch_bounds__(320, 1) tc_bwd_kernel(const BwdArgs A) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const uint32_t sbase = smem_u32(smem);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float *sm_wrgb = reinterpret_cast<float *>(smem + SB_SMALL);
+  float *sm_scan = reinterpret_cast<float *>(smem + SB_SCAN);
+  const uint32_t bar_full = sbase + SB_BARS, bar_empty = bar_full + BW_RING * 8, bar_acc = bar_empty + BW_RING * 8,
+                 bar_act = bar_acc + 8;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + SB_BARS + 24 * 8);
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < BW_RING; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, 1); }
+    mbar_init(bar_acc, 1);
+    mbar_init(bar_act, 256);
+    mbar_fence_init();
+  }
+  for (int i = threadIdx.x; i < 384; i += blockDim.x) sm_wrgb[i] = A.w_rgb[i];
+  if (warp == 9) tmem_alloc(smem_u32(tmem_slot), 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const int n_pairs = (A.n_rays + 1) >> 1;
+
+  if (warp == 8) {
+    if (elect_one()) {
+      uint32_t slot = 0, phase = 0;
+      for (int pair = blockIdx.x; pair < n_pairs; pair += gridDim.x)
+        for (int i = 0; i < A.n_stages; ++i) {
+          const TcStage st = c_bwd_stages[i];
+          mbar_wait(bar_empty + 8 * slot, phase ^ 1);
+          const uint32_t bytes = (uint32_t)st.n * 32u;
+          mbar_arrive_expect_tx(bar_full + 8 * slot, bytes);
+          bulk_g2s(sbase + SB_RING + slot * TC_SLOT, A.wimg + st.w_off, bytes, bar_full + 8 * slot);
+          if (++slot == BW_RING) { slot = 0; phase ^= 1; }
+        }
+    }
+    __syncwarp();
+  } else if (warp == 9) {
+    if (elect_one()) {
+      uint32_t slot = 0, phase = 0, act_par = 0;
+      for (int pair = blockIdx.x; pair < n_pairs; pair += gridDim.x)
+        for (int i = 0; i < A.n_stages; ++i) {
+          const TcStage st = c_bwd_stages[i];
+          if (st.first) { mbar_wait(bar_act, act_par); act_par ^= 1; }
+          mbar_wait(bar_full + 8 * slot, phase);
+          tc_fence_after();
+          const uint32_t a_off = (st.a_src == A_DSMALL) ? SB_DSMALL : SB_ACT;
+          const uint32_t a_sz = (st.a_src == A_DSMALL) ? 4096u : 65536u;
+          const uint32_t a_gs = (st.a_src == A_ACT) ? 4096u : (st.a_src == A_ACT128 ? 2048u : 256u);
+          const uint64_t bd = desc_kmajor(sbase + SB_RING + slot * TC_SLOT, 256);
+          const uint32_t idesc = idesc_bf16(128, st.n, 0, 0);
+#pragma unroll
+          for (int t = 0; t < 2; ++t) {
+            const uint64_t ad = desc_kmajor(sbase + a_off + t * a_sz + (uint32_t)st.a_k * 256u, a_gs);
+            umma(tmem + t * 256, ad, bd, idesc, st.first ? 0u : 1u);
+          }
+          umma_commit(bar_empty + 8 * slot);
+          if (st.last) umma_commit(bar_acc);
+          if (++slot == BW_RING) { slot = 0; phase ^= 1; }
+        }
+    }
+    __syncwarp();
+  } else {
+    const int t = warp >> 2, q = warp & 3, row = q * 32 + lane;
+    const uint32_t rowoff256 = (row >> 3) * 4096u + (row & 7) * 16u;
+    const uint32_t rowoff128 = (row >> 3) * 2048u + (row & 7) * 16u;
+    const uint32_t act_row = sbase + SB_ACT + t * 65536u + rowoff256;
+    const uint32_t tacc = tmem + ((uint32_t)(q * 32) << 16) + t * 256;
+    float *scan = sm_scan + t * 64;
+    uint32_t acc_par = 0;
+    float acc_origin[3] = {0.f, 0.f, 0.f}, acc_bias[4] = {0.f, 0.f, 0.f, 0.f};  // meaningful on row 0 of each tile
+    for (int pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
+      const int ray_raw = 2 * pair + t;
+      const bool valid = ray_raw < A.n_rays;
+      const int ray = valid ? ray_raw : A.n_rays - 1;
+      const size_t m = (size_t)ray * 128 + row;
+      const uint8_t *ftile = A.ws_fwd + (size_t)ray * FWD_TILE_BYTES;
+      uint8_t *btile = A.ws_bwd + (size_t)ray * BWD_TILE_BYTES;
+      // ---- compositing backward (model/rendering.py:124-126) -> d_raw of the two heads
+      const float alpha = A.alpha[m], z = A.z_vals[m];
+      const float4 sv = A.ws_s[m];
+      float g0 = 0.f, g1 = 0.f, g2 = 0.f, gd = 0.f;
+      if (valid) {
+        if (A.d_rgb) { g0 = A.d_rgb[3 * ray]; g1 = A.d_rgb[3 * ray + 1]; g2 = A.d_rgb[3 * ray + 2]; }
+        if (A.d_dist) gd = A.d_dist[ray];
+      }
+      const float beta = 1.f - alpha + 1e-6f;
+      const float inc = warp_incl_prod(beta, lane);
+      if (lane == 31) scan[q] = inc;
+      named_bar_sync(1 + t, 128);
+      float T = __shfl_up_sync(0xffffffffu, inc, 1);
+      if (lane == 0) T = 1.f;
+      for (int k = 0; k < q; ++k) T *= scan[k];
+      const float w = alpha * T;
+      float g = g0 * sv.x + g1 * sv.y + g2 * sv.z + gd * z + (A.white ? -(g0 + g1 + g2) : 0.f);
+      if (A.d_weights_out && valid) g += A.d_weights_out[m];
+      float wtot;
+      float G = warp_excl_suffix(g * w, lane, wtot);
+      if (lane == 0) scan[4 + q] = wtot;
+      named_bar_sync(1 + t, 128);
+      for (int k = q + 1; k < 4; ++k) G += scan[4 + k];
+      float dalpha = g * T - G / beta;
+      if (A.d_alpha_out && valid) dalpha += A.d_alpha_out[m];
+      const float dact = A.softplus ? (sv.w > 20.f ? 1.f : 1.f / (1.f + expf(-sv.w))) : (sv.w > 0.f ? 1.f : 0.f);
+      const float dr_den = dalpha * (1.f - alpha) * dact;
+      const float dr0 = w * g0 * sv.x * (1.f - sv.x), dr1 = w * g1 * sv.y * (1.f - sv.y), dr2 = w * g2 * sv.z * (1.f - sv.z);
+      {
+        const uint32_t ds = sbase + SB_DSMALL + t * 4096u + (row >> 3) * 256u + (row & 7) * 16u;
+        const uint32_t p0 = pack_bf16(dr0, dr1), p1 = pack_bf16(dr2, dr_den);
+        st_shared_v4(ds, p0, p1, 0u, 0u);
+        st_shared_v4(ds + 128, 0u, 0u, 0u, 0u);
+        if (valid) {
+          uint8_t *gds = btile + BW_DSMALL + (row >> 3) * 256u + (row & 7) * 16u;
+          st_global_v4(gds, p0, p1, 0u, 0u);
+          st_global_v4(gds + 128, 0u, 0u, 0u, 0u);
+        }
+      }
+      // ---- dY of rgb_layers.0 = (fc_rgb^T d_raw_rgb) masked by relu(Hc) > 0  -> 128-col operand image
+#pragma unroll 1
+      for (int j = 0; j < 16; ++j) {
+        const uint4 h = ld_global_v4(ftile + FW_HC + rowoff128 + j * 128);
+        const float *w0 = sm_wrgb + 8 * j, *w1 = w0 + 128, *w2 = w0 + 256;
+        float v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = w0[k] * dr0 + w1[k] * dr1 + w2[k] * dr2;
+        const uint32_t o0 = relu_mask2(pack_bf16(v[0], v[1]), h.x), o1 = relu_mask2(pack_bf16(v[2], v[3]), h.y),
+                       o2 = relu_mask2(pack_bf16(v[4], v[5]), h.z), o3 = relu_mask2(pack_bf16(v[6], v[7]), h.w);
+        st_shared_v4(sbase + SB_ACT + t * 65536u + rowoff128 + j * 128, o0, o1, o2, o3);
+        if (valid) st_global_v4(btile + BW_DYRGB0 + rowoff128 + j * 128, o0, o1, o2, o3);
+      }
+      fence_async_smem();
+      tc_fence_before();
+      mbar_arrive(bar_act);
+
+      float xp[3], xv[3], d_p[3] = {0.f, 0.f, 0.f}, d_v[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const float d = A.dirs[3 * ray + c];
+        xp[c] = __fadd_rn(A.origin[c], __fmul_rn(d, z));
+        xv[c] = -d;
+      }
+      // ---- the chain: 12 accumulator epilogues
+      const uint8_t kind[12] = {EPI_DIR, EPI_FEAT, EPI_MASK, EPI_MASK, EPI_MASK, EPI_MASK, EPI_ENC, EPI_MASK, EPI_MASK, EPI_MASK, EPI_MASK, EPI_ENC};
+      const int8_t slot_of[12] = {0, 0, 7, 6, 5, 4, 0, 3, 2, 1, 0, 0};
+#pragma unroll 1
+      for (int e = 0; e < 12; ++e) {
+        const int ek = kind[e];
+        const uint8_t *hrow = ftile + FW_H + (uint32_t)slot_of[e] * 65536u + rowoff256;
+        uint4 hm[8];
+        if (ek == EPI_MASK) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) hm[j] = ld_global_v4(hrow + j * 128);
+        }
+        mbar_wait(bar_acc, acc_par);
+        acc_par ^= 1;
+        tc_fence_after();
+        if (ek == EPI_DIR) {
+          uint32_t v0[32];
+          tmem_ld32(tacc, v0);
+          tmem_ld_wait();
+          if (A.use_dir) enc_backward<4>(xv, v0, d_v);
+        } else if (ek == EPI_ENC) {
+          uint32_t v0[64];
+          tmem_ld32(tacc, *reinterpret_cast<uint32_t(*)[32]>(&v0[0]));
+          tmem_ld32(tacc + 32, *reinterpret_cast<uint32_t(*)[32]>(&v0[32]));
+          tmem_ld_wait();
+          enc_backward<10>(xp, v0, d_p);
+        } else {
+          uint8_t *grow = btile + (ek == EPI_FEAT ? BW_DYFEAT : BW_DY + (uint32_t)slot_of[e] * 65536u) + rowoff256;
+#pragma unroll 1
+          for (int c0 = 0; c0 < 256; c0 += 64) {
+            uint32_t v0[32], v1[32];
+            tmem_ld32(tacc + c0, v0);
+            tmem_ld32(tacc + c0 + 32, v1);
+            uint4 hn[8];
+            if (ek == EPI_MASK && c0 + 64 < 256) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) hn[j] = ld_global_v4(hrow + ((c0 + 64) >> 3) * 128 + j * 128);
+            }
+            tmem_ld_wait();
+#pragma unroll
+            for (int gch = 0; gch < 8; ++gch) {
+              const uint32_t *v = (gch < 4) ? &v0[8 * gch] : &v1[8 * (gch - 4)];
+              uint32_t o0 = pack_bf16(__uint_as_float(v[0]), __uint_as_float(v[1])), o1 = pack_bf16(__uint_as_float(v[2]), __uint_as_float(v[3]));
+              uint32_t o2 = pack_bf16(__uint_as_float(v[4]), __uint_as_float(v[5])), o3 = pack_bf16(__uint_as_float(v[6]), __uint_as_float(v[7]));
+              if (ek == EPI_MASK) {
+                o0 = relu_mask2(o0, hm[gch].x); o1 = relu_mask2(o1, hm[gch].y); o2 = relu_mask2(o2, hm[gch].z); o3 = relu_mask2(o3, hm[gch].w);
+              }
+              const uint32_t off = ((c0 >> 3) + gch) * 128;
+              st_shared_v4(act_row + off, o0, o1, o2, o3);
+              if (valid) st_global_v4(grow + off, o0, o1, o2, o3);
+            }
+            if (ek == EPI_MASK) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) hm[j] = hn[j];
+            }
+          }
+        }
+        if (e < 11) {
+          fence_async_smem();
+          tc_fence_before();
+          mbar_arrive(bar_act);
+        }
+      }
+      // ---- per-ray reductions: d_dirs, and the CTA-level accumulators (d_origin, head biases)
+      float r[10];
+      r[0] = d_p[0]; r[1] = d_p[1]; r[2] = d_p[2];
+      r[3] = z * d_p[0] - d_v[0]; r[4] = z * d_p[1] - d_v[1]; r[5] = z * d_p[2] - d_v[2];
+      r[6] = dr_den; r[7] = dr0; r[8] = dr1; r[9] = dr2;
+#pragma unroll
+      for (int k = 0; k < 10; ++k) {
+        r[k] = warp_sum(r[k]);
+        if (lane == 0) scan[8 + 4 * k + q] = r[k];
+      }
+      named_bar_sync(1 + t, 128);
+      if (row == 0 && valid) {
+        float sres[10];
+#pragma unroll
+        for (int k = 0; k < 10; ++k) sres[k] = scan[8 + 4 * k] + scan[9 + 4 * k] + scan[10 + 4 * k] + scan[11 + 4 * k];
+        acc_origin[0] += sres[0]; acc_origin[1] += sres[1]; acc_origin[2] += sres[2];
+        A.d_dirs[3 * ray] = sres[3]; A.d_dirs[3 * ray + 1] = sres[4]; A.d_dirs[3 * ray + 2] = sres[5];
+        acc_bias[0] += sres[6]; acc_bias[1] += sres[7]; acc_bias[2] += sres[8]; acc_bias[3] += sres[9];
+      }
+      named_bar_sync(1 + t, 128);
+    }
+    if (row == 0) {
+      if (A.d_origin) { atomicAdd(A.d_origin, acc_origin[0]); atomicAdd(A.d_origin + 1, acc_origin[1]); atomicAdd(A.d_origin + 2, acc_origin[2]); }
+      if (A.d_b_den) atomicAdd(A.d_b_den, acc_bias[0]);
+      if (A.d_b_rgb) { atomicAdd(A.d_b_rgb, acc_bias[1]); atomicAdd(A.d_b_rgb + 1, acc_bias[2]); atomicAdd(A.d_b_rgb + 2, acc_bias[3]); }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 9) tmem_dealloc(tmem, 512);
+}
+
+}  // namespace
+
+// =====================================================================================================================
+// weight-gradient kernel: D[128 x N] += P^T Q over samples, P/Q = saved operand images viewed MN-major (K = samples)
+// =====================================================================================================================
+namespace {
+
+constexpr int WG_MAX_JOBS = 32;
+constexpr int WG_RING = 7;
+constexpr uint32_t WG_SLOT = 30720;   // 32 samples: P 8 KB + Q parts up to 22 KB
+constexpr uint32_t SW_RING = 0;
+constexpr uint32_t SW_BARS = WG_RING * WG_SLOT;
+constexpr uint32_t SW_TOTAL = SW_BARS + 24 * 8 + 16;
+static_assert(SW_TOTAL <= 232448, "shared memory budget");
+
+struct WgPart { uint32_t slot_off, gs; uint16_t n, tm_col; uint8_t ws, pad[3]; };
+struct WgSeg { int32_t param, offset, stride_m, stride_n; uint16_t tm_col, count; };
+struct WgJob {
+  uint32_t p_slot_off, p_gs, p_col0;
+  uint8_t p_ws, n_parts, n_segs, pad;
+  uint16_t splits, cta0;   // CTAs [cta0, cta0 + splits) work on this job
+  WgPart q[3];
+  WgSeg seg[4];
+};
+__constant__ WgJob c_wg_jobs[WG_MAX_JOBS];
+
+struct WgArgs {
+  const uint8_t *ws_fwd, *ws_bwd;
+  float *d_params[NNB_NUM_PARAMS];
+  int n_tiles, n_jobs;
+};
+
+__global__ void __launch_bounds__(192, 1) tc_wgrad_kernel(const WgArgs A) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const uint32_t sbase = smem_u32(smem);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t bar_full = sbase + SW_BARS, bar_empty = bar_full + WG_RING * 8, bar_done = bar_empty + WG_RING * 8;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + SW_BARS + 24 * 8);
+  // which job / split
+  int j = 0;
+  for (; j < A.n_jobs; ++j)
+    if ((int)blockIdx.x < c_wg_jobs[j].cta0 + c_wg_jobs[j].splits) break;
+  if (j >= A.n_jobs) return;
+  const WgJob &J = c_wg_jobs[j];
+  const int split = blockIdx.x - J.cta0;
+  const int t0 = (int)((long long)A.n_tiles * split / J.splits), t1 = (int)((long long)A.n_tiles * (split + 1) / J.splits);
+  if (t1 <= t0) return;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < WG_RING; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, 1); }
+    mbar_init(bar_done, 1);
+    mbar_fence_init();
+  }
+  if (warp == 5) tmem_alloc(smem_u32(tmem_slot), 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  uint32_t q_off[3];
+  {
+    uint32_t o = 8192;
+    for (int p = 0; p < J.n_parts; ++p) { q_off[p] = o; o += 4 * J.q[p].gs; }
+  }
+  if (warp == 4) {
+    if (elect_one()) {
+      uint32_t slot = 0, phase = 0;
+      uint32_t bytes = 8192;
+      for (int p = 0; p < J.n_parts; ++p) bytes += 4 * J.q[p].gs;
+      const uint8_t *pbase = (J.p_ws ? A.ws_bwd : A.ws_fwd) + J.p_slot_off + (J.p_col0 >> 3) * 128;
+      const size_t pstride = J.p_ws ? BWD_TILE_BYTES : FWD_TILE_BYTES;
+      for (int t = t0; t < t1; ++t)
+        for (int sub = 0; sub < 4; ++sub) {
+          mbar_wait(bar_empty + 8 * slot, phase ^ 1);
+          mbar_arrive_expect_tx(bar_full + 8 * slot, bytes);
+          const uint32_t dst = sbase + SW_RING + slot * WG_SLOT;
+          for (int g = 0; g < 4; ++g)
+            bulk_g2s(dst + g * 2048, pbase + (size_t)t * pstride + (size_t)(4 * sub + g) * J.p_gs, 2048, bar_full + 8 * slot);
+          for (int p = 0; p < J.n_parts; ++p) {
+            const uint8_t *qb = (J.q[p].ws ? A.ws_bwd + (size_t)t * BWD_TILE_BYTES : A.ws_fwd + (size_t)t * FWD_TILE_BYTES) + J.q[p].slot_off;
+            bulk_g2s(dst + q_off[p], qb + (size_t)(4 * sub) * J.q[p].gs, 4 * J.q[p].gs, bar_full + 8 * slot);
+          }
+          if (++slot == WG_RING) { slot = 0; phase ^= 1; }
+        }
+    }
+    __syncwarp();
+  } else if (warp == 5) {
+    if (elect_one()) {
+      uint32_t slot = 0, phase = 0, accum = 0;
+      for (int t = t0; t < t1; ++t)
+        for (int sub = 0; sub < 4; ++sub) {
+          mbar_wait(bar_full + 8 * slot, phase);
+          tc_fence_after();
+          const uint32_t src = sbase + SW_RING + slot * WG_SLOT;
+#pragma unroll
+          for (int ks = 0; ks < 2; ++ks) {
+            const uint64_t pd = desc_mnmajor(src + ks * 4096, 2048);
+            for (int p = 0; p < J.n_parts; ++p) {
+              const uint64_t qd = desc_mnmajor(src + q_off[p] + ks * 2 * J.q[p].gs, J.q[p].gs);
+              umma(tmem + J.q[p].tm_col, pd, qd, idesc_bf16(128, J.q[p].n, 1, 1), accum);
+            }
+            accum = 1;
+          }
+          umma_commit(bar_empty + 8 * slot);
+          if (++slot == WG_RING) { slot = 0; phase ^= 1; }
+        }
+      umma_commit(bar_done);
+    }
+    __syncwarp();
+  } else {
+    // flush: thread = output row m (lane of TMEM), red.add into the fp32 gradient tensors
+    mbar_wait(bar_done, 0);
+    tc_fence_after();
+    const int m = warp * 32 + lane;
+    for (int sgi = 0; sgi < J.n_segs; ++sgi) {
+      const WgSeg sg = J.seg[sgi];
+      float *dst = A.d_params[sg.param] + sg.offset + (size_t)m * sg.stride_m;
+      for (int c0 = 0; c0 < sg.count; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + sg.tm_col + c0, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int k = 0; k < 32; ++k)
+          if (c0 + k < sg.count) atomicAdd(dst + (size_t)(c0 + k) * sg.stride_n, __uint_as_float(v[k]));
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 5) tmem_dealloc(tmem, 512);
+}
+
+struct WgPlan { std::vector<WgJob> jobs; int n_ctas = 0; };
+
+WgPlan build_wg_plan() {
+  WgPlan P;
+  auto part = [](int ws, uint32_t off, uint32_t gs, int n, int tm) { WgPart q{}; q.ws = (uint8_t)ws; q.slot_off = off; q.gs = gs; q.n = (uint16_t)n; q.tm_col = (uint16_t)tm; return q; };
+  auto seg = [](int param, int offset, int sm, int sn, int tm, int count) { WgSeg s{}; s.param = param; s.offset = offset; s.stride_m = sm; s.stride_n = sn; s.tm_col = (uint16_t)tm; s.count = (uint16_t)count; return s; };
+  auto push = [&](WgJob J, int splits) { J.splits = (uint16_t)splits; J.cta0 = (uint16_t)P.n_ctas; P.n_ctas += splits; P.jobs.push_back(J); };
+  const int BIG = 16, MID = 9, SMALL = 6;
+  for (int L = 0; L < 8; ++L)
+    for (int h = 0; h < 2; ++h) {
+      WgJob J{};
+      const int wp = P_L0 + 2 * L;
+      J.p_ws = 1; J.p_slot_off = BW_DY + (uint32_t)L * 65536u; J.p_gs = 4096; J.p_col0 = 128 * h;
+      if (L == 0) {
+        J.n_parts = 2;
+        J.q[0] = part(0, FW_ENC, 1024, 64, 0);
+        J.q[1] = part(0, FW_AUX, 512, 32, 64);
+        J.n_segs = 2;
+        J.seg[0] = seg(wp, 128 * h * 63, 63, 1, 0, 63);
+        J.seg[1] = seg(wp + 1, 128 * h, 1, 1, 64 + 27, 1);
+        push(J, MID);
+      } else if (L == 4) {
+        J.n_parts = 3;
+        J.q[0] = part(0, FW_H + 3 * 65536u, 4096, 256, 0);
+        J.q[1] = part(0, FW_ENC, 1024, 64, 256);
+        J.q[2] = part(0, FW_AUX, 512, 32, 320);
+        J.n_segs = 3;
+        J.seg[0] = seg(wp, 128 * h * 319, 319, 1, 0, 256);
+        J.seg[1] = seg(wp, 128 * h * 319 + 256, 319, 1, 256, 63);
+        J.seg[2] = seg(wp + 1, 128 * h, 1, 1, 320 + 27, 1);
+        push(J, BIG);
+      } else {
+        J.n_parts = 2;
+        J.q[0] = part(0, FW_H + (uint32_t)(L - 1) * 65536u, 4096, 256, 0);
+        J.q[1] = part(0, FW_AUX, 512, 32, 256);
+        J.n_segs = 2;
+        J.seg[0] = seg(wp, 128 * h * 256, 256, 1, 0, 256);
+        J.seg[1] = seg(wp + 1, 128 * h, 1, 1, 256 + 27, 1);
+        push(J, BIG);
+      }
+    }
+  for (int h = 0; h < 2; ++h) {  // fc_feature
+    WgJob J{};
+    J.p_ws = 1; J.p_slot_off = BW_DYFEAT; J.p_gs = 4096; J.p_col0 = 128 * h;
+    J.n_parts = 2;
+    J.q[0] = part(0, FW_H + 7 * 65536u, 4096, 256, 0);
+    J.q[1] = part(0, FW_AUX, 512, 32, 256);
+    J.n_segs = 2;
+    J.seg[0] = seg(P_FEAT, 128 * h * 256, 256, 1, 0, 256);
+    J.seg[1] = seg(P_FEAT + 1, 128 * h, 1, 1, 256 + 27, 1);
+    push(J, BIG);
+  }
+  {  // rgb_layers.0: input [feat(256), dir_enc(27)]
+    WgJob J{};
+    J.p_ws = 1; J.p_slot_off = BW_DYRGB0; J.p_gs = 2048; J.p_col0 = 0;
+    J.n_parts = 2;
+    J.q[0] = part(0, FW_FEAT, 4096, 256, 0);
+    J.q[1] = part(0, FW_AUX, 512, 32, 256);
+    J.n_segs = 3;
+    J.seg[0] = seg(P_RGB0, 0, 283, 1, 0, 256);
+    J.seg[1] = seg(P_RGB0, 256, 283, 1, 256, 27);
+    J.seg[2] = seg(P_RGB0 + 1, 0, 1, 1, 256 + 27, 1);
+    push(J, BIG);
+  }
+  for (int h = 0; h < 2; ++h) {  // fc_density weight: sum_s H7[s][m] * d_raw_den[s]
+    WgJob J{};
+    J.p_ws = 0; J.p_slot_off = FW_H + 7 * 65536u; J.p_gs = 4096; J.p_col0 = 128 * h;
+    J.n_parts = 1;
+    J.q[0] = part(1, BW_DSMALL, 256, 16, 0);
+    J.n_segs = 1;
+    J.seg[0] = seg(P_DEN, 128 * h, 1, 1, 3, 1);
+    push(J, SMALL);
+  }
+  {  // fc_rgb weight (3,128): sum_s Hc[s][m] * d_raw_rgb[s][c]
+    WgJob J{};
+    J.p_ws = 0; J.p_slot_off = FW_HC; J.p_gs = 2048; J.p_col0 = 0;
+    J.n_parts = 1;
+    J.q[0] = part(1, BW_DSMALL, 256, 16, 0);
+    J.n_segs = 1;
+    J.seg[0] = seg(P_RGB, 0, 1, 128, 0, 3);
+    push(J, SMALL);
+  }
+  return P;
+}
+const WgPlan &wg_plan() {
+  static WgPlan p = build_wg_plan();
+  return p;
+}
+
+}  // namespace
+
+// =====================================================================================================================
 // host side
 // =====================================================================================================================
 namespace {
@@ -442,11 +1037,21 @@ std::once_flag g_tables_once;
 int g_tables_err = 0;
 
 void upload_tables() {
-  const Schedule &S = fwd_schedule();
-  if ((int)S.st.size() > TC_MAX_STAGES) { g_tables_err = NNB_ERR_UNSUPPORTED; return; }
-  cudaError_t e = cudaMemcpyToSymbol(c_fwd_stages, S.st.data(), S.st.size() * sizeof(TcStage));
-  if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_fwd_pack, S.pk.data(), S.pk.size() * sizeof(TcPack));
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(tc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SM_TOTAL);
+  const Schedule &F = fwd_schedule(), &B = bwd_schedule();
+  const WgPlan &W = wg_plan();
+  if ((int)F.st.size() > TC_MAX_STAGES || (int)B.st.size() > TC_MAX_STAGES || (int)W.jobs.size() > WG_MAX_JOBS) {
+    g_tables_err = NNB_ERR_UNSUPPORTED;
+    return;
+  }
+  cudaError_t e = cudaMemcpyToSymbol(c_fwd_stages, F.st.data(), F.st.size() * sizeof(TcStage));
+  if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_fwd_pack, F.pk.data(), F.pk.size() * sizeof(TcPack));
+  if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_bwd_stages, B.st.data(), B.st.size() * sizeof(TcStage));
+  if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_bwd_pack, B.pk.data(), B.pk.size() * sizeof(TcPack));
+  if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_wg_jobs, W.jobs.data(), W.jobs.size() * sizeof(WgJob));
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(tc_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SM_TOTAL);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(tc_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SM_TOTAL);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(tc_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SB_TOTAL);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SW_TOTAL);
   g_tables_err = (int)e;
 }
 
@@ -455,18 +1060,28 @@ int ensure_tables() {
   return g_tables_err;
 }
 
+inline size_t ws_fwd_bytes(int R) { return (size_t)R * FWD_TILE_BYTES; }
+inline size_t ws_bwd_bytes(int R) { return (size_t)R * BWD_TILE_BYTES; }
+inline size_t ws_s_bytes(int R) { return (size_t)R * 128 * sizeof(float4); }
+
 }  // namespace
 
-size_t nnb_tc_workspace_bytes(const nnb_render_cfg *, int) { return 16; }
+// workspace = [forward activation images | backward dY images | per-sample {rgb_s, raw}]
+size_t nnb_tc_workspace_bytes(const nnb_render_cfg *cfg, int save) {
+  if (!save) return 16;
+  return ws_fwd_bytes(cfg->n_rays) + ws_bwd_bytes(cfg->n_rays) + ws_s_bytes(cfg->n_rays);
+}
 
 int nnb_tc_render_fwd(const nnb_render_cfg *cfg, const float *const *params, const void *packed, const float *origin,
                       const float *dirs, const float *noise, float *rgb, float *dist, float *weights, float *alpha, float *z_vals,
                       void *ws, size_t ws_bytes, int save, cudaStream_t s) {
-  (void)ws; (void)ws_bytes;
   if (!packed || !params || !origin || !dirs || !rgb || !dist) return NNB_ERR_BAD_ARG;
   if (cfg->n_samples != 128 || cfg->dist_alpha) return NNB_ERR_UNSUPPORTED;  // tile = one ray of 128 samples
-  if (save) return NNB_ERR_UNSUPPORTED;
   if (cfg->n_rays <= 0) return 0;
+  if (save) {
+    if (!ws || ws_bytes < nnb_tc_workspace_bytes(cfg, 1)) return NNB_ERR_WORKSPACE;
+    if (!weights || !alpha || !z_vals) return NNB_ERR_BAD_ARG;  // the backward reads them
+  }
   int e = ensure_tables();
   if (e) return e;
   FwdArgs A{};
@@ -477,21 +1092,57 @@ int nnb_tc_render_fwd(const nnb_render_cfg *cfg, const float *const *params, con
   A.n_rays = cfg->n_rays; A.S = cfg->n_samples; A.n_stages = (int)fwd_schedule().st.size();
   A.near_ = cfg->near_; A.far_ = cfg->far_;
   A.softplus = cfg->occ_softplus; A.white = cfg->white_bkgd; A.use_dir = cfg->use_dir;
+  if (save) {
+    A.ws_fwd = static_cast<uint8_t *>(ws);
+    A.ws_s = reinterpret_cast<float4 *>(static_cast<uint8_t *>(ws) + ws_fwd_bytes(cfg->n_rays) + ws_bwd_bytes(cfg->n_rays));
+  }
   const int n_pairs = (cfg->n_rays + 1) / 2;
   const int grid = n_pairs < nnb_sm_count() ? n_pairs : nnb_sm_count();
-  tc_fwd_kernel<<<grid, 320, SM_TOTAL, s>>>(A);
+  if (save) tc_fwd_kernel<true><<<grid, 320, SM_TOTAL, s>>>(A);
+  else tc_fwd_kernel<false><<<grid, 320, SM_TOTAL, s>>>(A);
   NNB_CHECK_LAUNCH();
   return 0;
 }
 
-int nnb_tc_render_bwd(const nnb_render_cfg *, const float *const *, const void *, const float *, const float *, const float *,
-                      const float *, const float *, const float *, const float *, const float *, const float *, float *const *,
-                      float *, float *, void *, size_t, cudaStream_t) {
-  return NNB_ERR_UNSUPPORTED;
+int nnb_tc_render_bwd(const nnb_render_cfg *cfg, const float *const *params, const void *packed, const float *origin,
+                      const float *dirs, const float *weights, const float *alpha, const float *z_vals, const float *d_rgb,
+                      const float *d_dist, const float *d_alpha_out, const float *d_weights_out, float *const *d_params,
+                      float *d_origin, float *d_dirs, void *ws, size_t ws_bytes, cudaStream_t s) {
+  (void)weights;
+  if (!packed || !params || !origin || !dirs || !alpha || !z_vals || !d_params || !d_origin || !d_dirs) return NNB_ERR_BAD_ARG;
+  if (cfg->n_samples != 128 || cfg->dist_alpha) return NNB_ERR_UNSUPPORTED;
+  if (!ws || ws_bytes < nnb_tc_workspace_bytes(cfg, 1)) return NNB_ERR_WORKSPACE;
+  int e = ensure_tables();
+  if (e) return e;
+  NNB_CUDA(cudaMemsetAsync(d_origin, 0, 3 * sizeof(float), s));
+  if (cfg->n_rays <= 0) return 0;
+  const int R = cfg->n_rays;
+  uint8_t *w8 = static_cast<uint8_t *>(ws);
+  BwdArgs B{};
+  B.wimg = static_cast<const uint8_t *>(packed) + fwd_schedule().bytes;
+  B.ws_fwd = w8; B.ws_bwd = w8 + ws_fwd_bytes(R);
+  B.ws_s = reinterpret_cast<const float4 *>(w8 + ws_fwd_bytes(R) + ws_bwd_bytes(R));
+  B.origin = origin; B.dirs = dirs; B.alpha = alpha; B.z_vals = z_vals;
+  B.d_rgb = d_rgb; B.d_dist = d_dist; B.d_alpha_out = d_alpha_out; B.d_weights_out = d_weights_out;
+  B.w_rgb = params[P_RGB];
+  B.d_origin = d_origin; B.d_dirs = d_dirs; B.d_b_den = d_params[P_DEN + 1]; B.d_b_rgb = d_params[P_RGB + 1];
+  B.n_rays = R; B.n_stages = (int)bwd_schedule().st.size();
+  B.softplus = cfg->occ_softplus; B.white = cfg->white_bkgd; B.use_dir = cfg->use_dir;
+  const int n_pairs = (R + 1) / 2;
+  const int grid = n_pairs < nnb_sm_count() ? n_pairs : nnb_sm_count();
+  tc_bwd_kernel<<<grid, 320, SB_TOTAL, s>>>(B);
+  NNB_CHECK_LAUNCH();
+  WgArgs W{};
+  W.ws_fwd = B.ws_fwd; W.ws_bwd = B.ws_bwd;
+  for (int i = 0; i < NNB_NUM_PARAMS; ++i) W.d_params[i] = d_params[i];
+  W.n_tiles = R; W.n_jobs = (int)wg_plan().jobs.size();
+  tc_wgrad_kernel<<<wg_plan().n_ctas, 192, SW_TOTAL, s>>>(W);
+  NNB_CHECK_LAUNCH();
+  return 0;
 }
 
 extern "C" {
-size_t nnb_pack_weights_bytes(void) { return (size_t)fwd_schedule().bytes; }
+size_t nnb_pack_weights_bytes(void) { return (size_t)fwd_schedule().bytes + (size_t)bwd_schedule().bytes; }
 
 int nnb_pack_weights(const float *const *params_host, void *packed, void *stream) {
   if (!params_host || !packed) return NNB_ERR_BAD_ARG;
@@ -499,8 +1150,10 @@ int nnb_pack_weights(const float *const *params_host, void *packed, void *stream
   if (e) return e;
   PackPtrs P;
   for (int i = 0; i < NNB_NUM_PARAMS; ++i) P.p[i] = params_host[i];
-  const int n = (int)fwd_schedule().st.size();
-  tc_pack_kernel<<<n, 256, 0, nnb_stream(stream)>>>(P, static_cast<uint8_t *>(packed), n, 0);
+  const int nf = (int)fwd_schedule().st.size(), nb = (int)bwd_schedule().st.size();
+  tc_pack_kernel<<<nf, 256, 0, nnb_stream(stream)>>>(P, static_cast<uint8_t *>(packed), nf, 0);
+  NNB_CHECK_LAUNCH();
+  tc_pack_kernel<<<nb, 256, 0, nnb_stream(stream)>>>(P, static_cast<uint8_t *>(packed) + fwd_schedule().bytes, nb, 1);
   NNB_CHECK_LAUNCH();
   return 0;
 }
