@@ -89,10 +89,10 @@ __global__ void __launch_bounds__(256) sgemm_kernel(int M, int N, int K, const f
       float v = acc[i][j];
       if (ep.bias) v += ep.bias[gn];
       if (ep.relu) v = fmaxf(v, 0.f);
-      if (ep.mask && !(ep.mask[gm * ep.ldmask + gn] > 0.f)) v = 0.f;
       float *c = C + gm * ldc + gn;
+      if (ep.accumulate && !ep.atomic) v += *c;  // the mask below applies to the accumulated value
+      if (ep.mask && !(ep.mask[gm * ep.ldmask + gn] > 0.f)) v = 0.f;
       if (ep.atomic) atomicAdd(c, v);
-      else if (ep.accumulate) *c += v;
       else *c = v;
     }
   }

@@ -152,7 +152,8 @@ def test_render_stage_backward_isolated():
         ref = P[k].grad
         e = float((p.grad.cpu() - ref).abs().max() / ref.abs().max().clamp_min(1e-12))
         worst = max(worst, e)
-        assert e < 2e-3, "grad %s: scale-relative err %.3e" % (k, e)
+        print("  grad %-24s scale-relative err %.3e" % (k, e))
     print("render bwd: worst scale-relative weight-grad err %.3e" % worst)
+    assert worst < 2e-3
     assert_close(od.grad, oc.grad, 2e-3, 1e-6 + 2e-3 * float(oc.grad.abs().max()), "d origin")
     assert_close(dd.grad, dc.grad, 2e-3, 1e-6 + 2e-3 * float(dc.grad.abs().max()), "d dirs")
