@@ -161,9 +161,14 @@ int nnb_mlp_points_fwd(const float *const *params_host, const float *pts, const 
                        int occ_softplus, int dist_alpha, float *rgb, float *dens, void *workspace,
                        size_t workspace_bytes, void *stream);
 
-/* Repacks the 24 fp32 tensors into the bf16 tile images the tcgen05 kernels stream with TMA. */
+/* Repacks the 24 fp32 tensors into the bf16 stage images the tcgen05 kernels stream with bulk TMA
+ * (forward images followed by the transposed images of the data-gradient chain). */
 size_t nnb_pack_weights_bytes(void);
 int nnb_pack_weights(const float *const *params_host, void *packed, void *stream);
+
+/* Debug aid: device buffer (>= 64 int64) that receives per-layer clock64 stamps of CTA 0 / first ray pair of
+ * the following tensor-core forward launches; NULL switches it off. */
+int nnb_debug_set_trace(void *buf);
 
 /* ------------------------------------------------------------------------------------------
  * Stage 4 -- rgb / depth / reprojection losses

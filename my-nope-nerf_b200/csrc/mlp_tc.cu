@@ -185,6 +185,7 @@ struct FwdArgs {
   int softplus, white, use_dir;
   uint8_t *ws_fwd;   // SAVE: per-ray activation images (FWD_TILE_BYTES each)
   float4 *ws_s;      // SAVE: per-sample {rgb_s, raw density}
+  long long *trace;  // debug: per-layer clock64 stamps of CTA 0 (nnb_debug_set_trace), else NULL
 };
 
 // saved-activation images of one ray (bf16, operand-image layout), written by the forward when SAVE, read by the
@@ -332,9 +333,14 @@ __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
       for (int pair = blockIdx.x; pair < n_pairs; pair += gridDim.x)
         for (int i = 0; i < A.n_stages; ++i) {
           const TcStage st = c_fwd_stages[i];
-          if (st.first) { mbar_wait(bar_act, act_par); act_par ^= 1; }
+          if (st.first) {
+            mbar_wait(bar_act, act_par);
+            act_par ^= 1;
+            if (A.trace && blockIdx.x == 0 && pair == 0) A.trace[st.layer * 4 + 2] = clock64();
+          }
           mbar_wait(bar_full + 8 * slot, phase);
           tc_fence_after();
+          if (st.last && A.trace && blockIdx.x == 0 && pair == 0) A.trace[st.layer * 4 + 3] = clock64();
           const uint32_t a_off = (st.a_src == A_ACT) ? SM_ACT : (st.a_src == A_ENC ? SM_ENC : SM_AUX);
           const uint32_t a_sz = (st.a_src == A_ACT) ? 65536u : (st.a_src == A_ENC ? 16384u : 8192u);
           const uint32_t a_gs = (st.a_src == A_ACT) ? GS_ACT : (st.a_src == A_ENC ? GS_ENC : GS_AUX);
@@ -389,6 +395,7 @@ __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
         mbar_wait(bar_acc, acc_par);
         acc_par ^= 1;
         tc_fence_after();
+        if (A.trace && blockIdx.x == 0 && pair == 0 && threadIdx.x == 0) A.trace[L * 4 + 0] = clock64();
         if (L < 9) {
           float dsum = 0.f;
 #pragma unroll 1
@@ -436,6 +443,7 @@ __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
           fence_async_smem();
           tc_fence_before();
           mbar_arrive(bar_act);
+          if (A.trace && blockIdx.x == 0 && pair == 0 && threadIdx.x == 0) A.trace[L * 4 + 1] = clock64();
         } else {
           // rgb head: relu(rgb_layers.0) (128 wide, TMEM cols 0..127) . fc_rgb^T + b -> sigmoid
           float s0 = sm_small[641], s1 = sm_small[642], s2 = sm_small[643];
@@ -1033,6 +1041,7 @@ const WgPlan &wg_plan() {
 // =====================================================================================================================
 namespace {
 
+long long *g_trace = nullptr;
 std::once_flag g_tables_once;
 int g_tables_err = 0;
 
@@ -1092,6 +1101,7 @@ int nnb_tc_render_fwd(const nnb_render_cfg *cfg, const float *const *params, con
   A.n_rays = cfg->n_rays; A.S = cfg->n_samples; A.n_stages = (int)fwd_schedule().st.size();
   A.near_ = cfg->near_; A.far_ = cfg->far_;
   A.softplus = cfg->occ_softplus; A.white = cfg->white_bkgd; A.use_dir = cfg->use_dir;
+  A.trace = g_trace;
   if (save) {
     A.ws_fwd = static_cast<uint8_t *>(ws);
     A.ws_s = reinterpret_cast<float4 *>(static_cast<uint8_t *>(ws) + ws_fwd_bytes(cfg->n_rays) + ws_bwd_bytes(cfg->n_rays));
@@ -1142,6 +1152,9 @@ int nnb_tc_render_bwd(const nnb_render_cfg *cfg, const float *const *params, con
 }
 
 extern "C" {
+/* debug: device buffer of >= 64 int64 receiving clock64 stamps of CTA 0 / pair 0 of the next forward launches */
+int nnb_debug_set_trace(void *buf) { g_trace = static_cast<long long *>(buf); return 0; }
+
 size_t nnb_pack_weights_bytes(void) { return (size_t)fwd_schedule().bytes + (size_t)bwd_schedule().bytes; }
 
 int nnb_pack_weights(const float *const *params_host, void *packed, void *stream) {
