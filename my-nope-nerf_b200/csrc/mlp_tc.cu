@@ -25,8 +25,9 @@ namespace {
 enum { P_L0 = 0, P_DEN = 16, P_FEAT = 18, P_RGB0 = 20, P_RGB = 22 };
 
 constexpr int TC_MAX_STAGES = 512;
-constexpr int TC_RING = 5;               // weight ring slots
-constexpr uint32_t TC_SLOT = 8192;       // bytes per slot (256 rows x 16 k x bf16)
+constexpr int TC_RING = 3;               // forward weight ring slots
+constexpr uint32_t TC_SLOT = 16384;      // bytes per slot: one group = up to 2 k-steps of [256 rows x 16 k] bf16
+constexpr int TC_MAX_GROUPS = 192;
 
 enum ASrc : uint8_t { A_ACT = 0, A_ENC = 1, A_AUX = 2, A_ACT128 = 3, A_DSMALL = 4 };
 enum Epi : uint8_t { EPI_DIR = 0, EPI_FEAT = 1, EPI_MASK = 2, EPI_ENC = 3 };
@@ -57,6 +58,11 @@ struct TcPack {
 __constant__ TcStage c_fwd_stages[TC_MAX_STAGES];
 __constant__ TcPack c_fwd_pack[TC_MAX_STAGES];
 __constant__ TcStage c_bwd_stages[TC_MAX_STAGES];
+// Issue groups: consecutive k-steps of one layer on one A image (<= 2), one bulk copy + one barrier round trip each.
+//   x = byte offset of the weight images   y = A offset in smem (18 bits) | nk << 18 | first << 20 | last << 21
+//   z = n | a_gs << 16                        w = A stride between the two tiles
+__constant__ uint4 c_fwd_groups[TC_MAX_GROUPS];
+__constant__ uint4 c_bwd_groups[TC_MAX_GROUPS];
 __constant__ TcPack c_bwd_pack[TC_MAX_STAGES];
 
 struct Schedule {
@@ -158,6 +164,67 @@ __global__ void tc_pack_kernel(PackPtrs P, uint8_t *out, int n_stages, int which
 
 }  // namespace
 
+
+// ---------------------------------------------------------------------------------------------------------------------
+// weight producer and MMA issuer loops shared by the forward and backward kernels (one elected thread each)
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+
+template <int RING>
+__device__ __forceinline__ void weight_producer(const uint4 *groups, int n_groups, int n_pairs, const uint8_t *wimg, uint32_t ring,
+                                                uint32_t bar_full, uint32_t bar_empty) {
+  uint32_t slot = 0, phase = 0;
+  for (int pair = blockIdx.x; pair < n_pairs; pair += gridDim.x)
+    for (int i = 0; i < n_groups; ++i) {
+      const uint4 g = groups[i];
+      const uint32_t bytes = (g.z & 0xFFFFu) * 32u * ((g.y >> 18) & 3u);
+      mbar_wait(bar_empty + 8 * slot, phase ^ 1);
+      mbar_arrive_expect_tx(bar_full + 8 * slot, bytes);
+      bulk_g2s(ring + slot * TC_SLOT, wimg + g.x, bytes, bar_full + 8 * slot);
+      if (++slot == RING) { slot = 0; phase ^= 1; }
+    }
+}
+
+// D(tile t) at tmem + t*256.  The next group's record is fetched before the barrier waits so that its latency hides there.
+template <int RING>
+__device__ __forceinline__ void mma_issuer(const uint4 *groups, int n_groups, int n_pairs, uint32_t sbase, uint32_t ring,
+                                           uint32_t bar_full, uint32_t bar_empty, uint32_t bar_acc, uint32_t bar_act, uint32_t tmem,
+                                           long long *trace) {
+  uint32_t slot = 0, phase = 0, act_par = 0;
+  uint4 nxt = groups[0];
+  for (int pair = blockIdx.x; pair < n_pairs; pair += gridDim.x)
+    for (int i = 0; i < n_groups; ++i) {
+      const uint4 g = nxt;
+      nxt = groups[(i + 1 == n_groups) ? 0 : i + 1];
+      const uint32_t nk = (g.y >> 18) & 3u, first = (g.y >> 20) & 1u, last = (g.y >> 21) & 1u;
+      const uint32_t n = g.z & 0xFFFFu, a_gs = g.z >> 16;
+      if (first) {
+        mbar_wait(bar_act, act_par);
+        act_par ^= 1;
+        if (trace && blockIdx.x == 0 && pair == 0) trace[2 * i] = clock64();
+      }
+      mbar_wait(bar_full + 8 * slot, phase);
+      tc_fence_after();
+      const uint32_t idesc = idesc_bf16(128, (int)n, 0, 0);
+      const uint32_t a0 = sbase + (g.y & 0x3FFFFu), b0 = ring + slot * TC_SLOT;
+#pragma unroll
+      for (uint32_t k = 0; k < 2; ++k)
+        if (k < nk) {
+          const uint64_t bd = desc_kmajor(b0 + k * n * 32u, 256);
+          umma(tmem, desc_kmajor(a0 + k * 256u, a_gs), bd, idesc, (first && k == 0) ? 0u : 1u);
+          umma(tmem + 256, desc_kmajor(a0 + g.w + k * 256u, a_gs), bd, idesc, (first && k == 0) ? 0u : 1u);
+        }
+      umma_commit(bar_empty + 8 * slot);
+      if (last) {
+        umma_commit(bar_acc);
+        if (trace && blockIdx.x == 0 && pair == 0) trace[2 * i + 1] = clock64();
+      }
+      if (++slot == RING) { slot = 0; phase ^= 1; }
+    }
+}
+
+}  // namespace
+
 // =====================================================================================================================
 // forward kernel
 // =====================================================================================================================
@@ -165,15 +232,15 @@ namespace {
 
 constexpr uint32_t SM_ACT = 0;                        // 2 x 65536  (128 rows x 256 cols bf16)
 constexpr uint32_t SM_ENC = 131072;                   // 2 x 16384  (128 x 64)
-constexpr uint32_t SM_AUX = SM_ENC + 32768;           // 2 x 8192   (128 x 32)
-constexpr uint32_t SM_RING = SM_AUX + 16384;          // TC_RING x 8192
+constexpr uint32_t SM_AUX = SM_ENC + 32768;           // 2 x 512: 8 identical rows x 32 cols (one ray per tile), group stride 0
+constexpr uint32_t SM_RING = SM_AUX + 1024;          // TC_RING x TC_SLOT
 constexpr uint32_t SM_SMALL = SM_RING + TC_RING * TC_SLOT;  // fp32: w_den[256] w_rgb[384] b_den b_rgb[3] (+pad) = 648 floats
 constexpr uint32_t SM_SCAN = SM_SMALL + 648 * 4;      // 2 tiles x 4 warps x 8 floats
 constexpr uint32_t SM_BARS = SM_SCAN + 2 * 4 * 8 * 4; // mbarriers
 constexpr uint32_t SM_TOTAL = SM_BARS + 16 * 8 + 16;
 static_assert(SM_TOTAL <= 232448, "shared memory budget");
 
-constexpr uint32_t GS_ACT = 4096, GS_ENC = 1024, GS_AUX = 512;
+constexpr uint32_t GS_ACT = 4096, GS_ENC = 1024, GS_AUX = 512;  // GS_AUX: stride of the SAVED aux image (global)
 
 struct FwdArgs {
   const uint8_t *wimg;
@@ -195,7 +262,8 @@ constexpr uint32_t FW_FEAT = 8 * 65536;      // fc_feature output (no activation
 constexpr uint32_t FW_HC = 9 * 65536;        // relu(rgb_layers.0), 128 cols (gs 2048)
 constexpr uint32_t FW_ENC = FW_HC + 32768;   // positional encoding, 64 cols
 constexpr uint32_t FW_AUX = FW_ENC + 16384;  // view-direction encoding + ones, 32 cols
-constexpr uint32_t FWD_TILE_BYTES = FW_AUX + 8192;
+constexpr uint32_t FW_MASK = FW_AUX + 8192;   // ReLU sign bitmasks: 9 layers (H0..H7, Hc) x 128 rows x 8 words
+constexpr uint32_t FWD_TILE_BYTES = FW_MASK + 9 * 4096;
 // gradient images written by the backward, read by the weight-gradient kernel
 constexpr uint32_t BW_DY = 0;                // dY0..dY7
 constexpr uint32_t BW_DYFEAT = 8 * 65536;
@@ -227,8 +295,8 @@ __device__ __forceinline__ float warp_incl_prod(float v, int lane) {
 // Sampling + positional encoding of one sample -> its rows of the enc (64 cols) and aux (32 cols) operand images.
 // Column order follows encode_position (model/official_nerf.py:99-119): [x, sin(2^l x), cos(2^l x)]_l, 3 wide each.
 template <bool SAVE>
-__device__ __forceinline__ void write_encodings(uint32_t enc_row, uint32_t aux_row, uint8_t *genc, uint8_t *gaux, const float p[3],
-                                                const float v[3]) {
+__device__ __forceinline__ void write_encodings(uint32_t enc_row, uint32_t aux_row, bool aux_smem, uint8_t *genc, uint8_t *gaux,
+                                                const float p[3], const float v[3]) {
   float e[64];
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
@@ -265,13 +333,25 @@ __device__ __forceinline__ void write_encodings(uint32_t enc_row, uint32_t aux_r
   a[27] = 1.f; a[28] = 1.f; a[29] = 0.f; a[30] = 0.f; a[31] = 0.f;
 #pragma unroll
   for (int g = 0; g < 4; ++g)
-    put_chunk<SAVE>(aux_row + g * 128, gaux + g * 128, pack_bf16(a[8 * g], a[8 * g + 1]), pack_bf16(a[8 * g + 2], a[8 * g + 3]),
-                    pack_bf16(a[8 * g + 4], a[8 * g + 5]), pack_bf16(a[8 * g + 6], a[8 * g + 7]));
+  {
+    const uint32_t w0 = pack_bf16(a[8 * g], a[8 * g + 1]), w1 = pack_bf16(a[8 * g + 2], a[8 * g + 3]),
+                   w2 = pack_bf16(a[8 * g + 4], a[8 * g + 5]), w3 = pack_bf16(a[8 * g + 6], a[8 * g + 7]);
+    if (aux_smem) st_shared_v4(aux_row + g * 128, w0, w1, w2, w3);
+    if (SAVE) st_global_v4(gaux + g * 128, w0, w1, w2, w3);
+  }
 }
 
-// 32 fp32 accumulator columns -> 4 chunks of 8 bf16 (optionally relu) into the operand image (+ global copy)
+// 1 where the bf16 half is > 0, as 0xFFFF per half
+__device__ __forceinline__ uint32_t gt0_mask2(uint32_t h) {
+  uint32_t m;
+  asm("set.gt.u32.bf16x2 %0, %1, %2;" : "=r"(m) : "r"(h), "r"(0u));
+  return m;
+}
+// 32 fp32 accumulator columns -> 4 chunks of 8 bf16 (optionally relu) into the operand image (+ global copy).
+// Returns the ReLU bitmask of the block: pair p (columns 2p, 2p+1) -> bit p (even column) and bit 16+p (odd column).
 template <bool RELU, bool SAVE>
-__device__ __forceinline__ void store32(uint32_t saddr, uint8_t *gaddr, const uint32_t (&v)[32]) {
+__device__ __forceinline__ uint32_t store32(uint32_t saddr, uint8_t *gaddr, const uint32_t (&v)[32]) {
+  uint32_t bits = 0;
 #pragma unroll
   for (int g = 0; g < 4; ++g) {
     uint32_t w[4];
@@ -279,9 +359,11 @@ __device__ __forceinline__ void store32(uint32_t saddr, uint8_t *gaddr, const ui
     for (int k = 0; k < 4; ++k) {
       const float a = __uint_as_float(v[8 * g + 2 * k]), b = __uint_as_float(v[8 * g + 2 * k + 1]);
       w[k] = RELU ? pack_bf16_relu(a, b) : pack_bf16(a, b);
+      if (RELU && SAVE) bits |= gt0_mask2(w[k]) & ((1u << (4 * g + k)) | (1u << (16 + 4 * g + k)));
     }
     put_chunk<SAVE>(saddr + g * 128, gaddr + g * 128, w[0], w[1], w[2], w[3]);
   }
+  return bits;
 }
 
 template <bool SAVE>
@@ -313,56 +395,20 @@ __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
 
   if (warp == 8) {
     // ------------------------------------------------ weight producer
-    if (elect_one()) {
-      uint32_t slot = 0, phase = 0;
-      for (int pair = blockIdx.x; pair < n_pairs; pair += gridDim.x)
-        for (int i = 0; i < A.n_stages; ++i) {
-          const TcStage st = c_fwd_stages[i];
-          mbar_wait(bar_empty + 8 * slot, phase ^ 1);
-          const uint32_t bytes = (uint32_t)st.n * 32u;
-          mbar_arrive_expect_tx(bar_full + 8 * slot, bytes);
-          bulk_g2s(sbase + SM_RING + slot * TC_SLOT, A.wimg + st.w_off, bytes, bar_full + 8 * slot);
-          if (++slot == TC_RING) { slot = 0; phase ^= 1; }
-        }
-    }
+    if (elect_one()) weight_producer<TC_RING>(c_fwd_groups, A.n_stages, n_pairs, A.wimg, sbase + SM_RING, bar_full, bar_empty);
     __syncwarp();
   } else if (warp == 9) {
     // ------------------------------------------------ MMA issuer
-    if (elect_one()) {
-      uint32_t slot = 0, phase = 0, act_par = 0;
-      for (int pair = blockIdx.x; pair < n_pairs; pair += gridDim.x)
-        for (int i = 0; i < A.n_stages; ++i) {
-          const TcStage st = c_fwd_stages[i];
-          if (st.first) {
-            mbar_wait(bar_act, act_par);
-            act_par ^= 1;
-            if (A.trace && blockIdx.x == 0 && pair == 0) A.trace[st.layer * 4 + 2] = clock64();
-          }
-          mbar_wait(bar_full + 8 * slot, phase);
-          tc_fence_after();
-          if (st.last && A.trace && blockIdx.x == 0 && pair == 0) A.trace[st.layer * 4 + 3] = clock64();
-          const uint32_t a_off = (st.a_src == A_ACT) ? SM_ACT : (st.a_src == A_ENC ? SM_ENC : SM_AUX);
-          const uint32_t a_sz = (st.a_src == A_ACT) ? 65536u : (st.a_src == A_ENC ? 16384u : 8192u);
-          const uint32_t a_gs = (st.a_src == A_ACT) ? GS_ACT : (st.a_src == A_ENC ? GS_ENC : GS_AUX);
-          const uint64_t bd = desc_kmajor(sbase + SM_RING + slot * TC_SLOT, 256);
-          const uint32_t idesc = idesc_bf16(128, st.n, 0, 0);
-#pragma unroll
-          for (int t = 0; t < 2; ++t) {
-            const uint64_t ad = desc_kmajor(sbase + a_off + t * a_sz + (uint32_t)st.a_k * 256u, a_gs);
-            umma(tmem + t * 256, ad, bd, idesc, st.first ? 0u : 1u);
-          }
-          umma_commit(bar_empty + 8 * slot);
-          if (st.last) umma_commit(bar_acc);
-          if (++slot == TC_RING) { slot = 0; phase ^= 1; }
-        }
-    }
+    if (elect_one())
+      mma_issuer<TC_RING>(c_fwd_groups, A.n_stages, n_pairs, sbase, sbase + SM_RING, bar_full, bar_empty, bar_acc, bar_act, tmem,
+                          A.trace ? A.trace + 64 : nullptr);
     __syncwarp();
   } else {
     // ------------------------------------------------ row owners: prologue, epilogues, heads, compositing
     const int t = warp >> 2, q = warp & 3, row = q * 32 + lane;
     const uint32_t act_row = sbase + SM_ACT + t * 65536u + (row >> 3) * GS_ACT + (row & 7) * 16;
     const uint32_t enc_row = sbase + SM_ENC + t * 16384u + (row >> 3) * GS_ENC + (row & 7) * 16;
-    const uint32_t aux_row = sbase + SM_AUX + t * 8192u + (row >> 3) * GS_AUX + (row & 7) * 16;
+    const uint32_t aux_row = sbase + SM_AUX + t * 512u + (row & 7) * 16;  // rows 0..7 write it (same ray => same values)
     const uint32_t tacc = tmem + ((uint32_t)(q * 32) << 16) + t * 256;
     float *scan = sm_scan + t * 32;
     uint32_t acc_par = 0;
@@ -382,9 +428,9 @@ __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
           p[c] = __fadd_rn(A.origin[c], __fmul_rn(d, z));
           v[c] = A.use_dir ? -d : 1.0f;
         }
-        if (SAVE && valid) write_encodings<true>(enc_row, aux_row, gtile + FW_ENC + (row >> 3) * GS_ENC + (row & 7) * 16,
+        if (SAVE && valid) write_encodings<true>(enc_row, aux_row, row < 8, gtile + FW_ENC + (row >> 3) * GS_ENC + (row & 7) * 16,
                                                  gtile + FW_AUX + (row >> 3) * GS_AUX + (row & 7) * 16, p, v);
-        else write_encodings<false>(enc_row, aux_row, nullptr, nullptr, p, v);
+        else write_encodings<false>(enc_row, aux_row, row < 8, nullptr, nullptr, p, v);
       }
       fence_async_smem();
       tc_fence_before();
@@ -397,8 +443,9 @@ __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
         tc_fence_after();
         if (A.trace && blockIdx.x == 0 && pair == 0 && threadIdx.x == 0) A.trace[L * 4 + 0] = clock64();
         if (L < 9) {
-          float dsum = 0.f;
-#pragma unroll 1
+          float ds0 = 0.f, ds1 = 0.f, ds2 = 0.f, ds3 = 0.f;
+          uint32_t mw[8];
+#pragma unroll
           for (int c0 = 0; c0 < 256; c0 += 64) {
             uint32_t v0[32], v1[32];
             tmem_ld32(tacc + c0, v0);
@@ -409,33 +456,38 @@ __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
                 const float4 w = wd[j];
-                dsum = fmaf(fmaxf(__uint_as_float(v0[4 * j]), 0.f), w.x, dsum);
-                dsum = fmaf(fmaxf(__uint_as_float(v0[4 * j + 1]), 0.f), w.y, dsum);
-                dsum = fmaf(fmaxf(__uint_as_float(v0[4 * j + 2]), 0.f), w.z, dsum);
-                dsum = fmaf(fmaxf(__uint_as_float(v0[4 * j + 3]), 0.f), w.w, dsum);
+                ds0 = fmaf(fmaxf(__uint_as_float(v0[4 * j]), 0.f), w.x, ds0);
+                ds1 = fmaf(fmaxf(__uint_as_float(v0[4 * j + 1]), 0.f), w.y, ds1);
+                ds2 = fmaf(fmaxf(__uint_as_float(v0[4 * j + 2]), 0.f), w.z, ds2);
+                ds3 = fmaf(fmaxf(__uint_as_float(v0[4 * j + 3]), 0.f), w.w, ds3);
               }
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
                 const float4 w = wd[8 + j];
-                dsum = fmaf(fmaxf(__uint_as_float(v1[4 * j]), 0.f), w.x, dsum);
-                dsum = fmaf(fmaxf(__uint_as_float(v1[4 * j + 1]), 0.f), w.y, dsum);
-                dsum = fmaf(fmaxf(__uint_as_float(v1[4 * j + 2]), 0.f), w.z, dsum);
-                dsum = fmaf(fmaxf(__uint_as_float(v1[4 * j + 3]), 0.f), w.w, dsum);
+                ds0 = fmaf(fmaxf(__uint_as_float(v1[4 * j]), 0.f), w.x, ds0);
+                ds1 = fmaf(fmaxf(__uint_as_float(v1[4 * j + 1]), 0.f), w.y, ds1);
+                ds2 = fmaf(fmaxf(__uint_as_float(v1[4 * j + 2]), 0.f), w.z, ds2);
+                ds3 = fmaf(fmaxf(__uint_as_float(v1[4 * j + 3]), 0.f), w.w, ds3);
               }
             }
             const uint32_t dst = act_row + (c0 >> 3) * 128;
             uint8_t *gdst = sv ? gtile + (uint32_t)L * 65536u + (row >> 3) * GS_ACT + (row & 7) * 16 + (c0 >> 3) * 128 : nullptr;
             if (L != 8) {
-              if (sv) { store32<true, true>(dst, gdst, v0); store32<true, true>(dst + 512, gdst + 512, v1); }
+              if (sv) { mw[c0 >> 5] = store32<true, true>(dst, gdst, v0); mw[(c0 >> 5) + 1] = store32<true, true>(dst + 512, gdst + 512, v1); }
               else { store32<true, false>(dst, nullptr, v0); store32<true, false>(dst + 512, nullptr, v1); }
             } else {
               if (sv) { store32<false, true>(dst, gdst, v0); store32<false, true>(dst + 512, gdst + 512, v1); }
               else { store32<false, false>(dst, nullptr, v0); store32<false, false>(dst + 512, nullptr, v1); }
             }
           }
+          if (sv && L != 8) {
+            uint8_t *gm = gtile + FW_MASK + (uint32_t)L * 4096u + row * 32;
+            st_global_v4(gm, mw[0], mw[1], mw[2], mw[3]);
+            st_global_v4(gm + 16, mw[4], mw[5], mw[6], mw[7]);
+          }
           if (L == 7) {
             // density head (model/official_nerf.py:66,77-83): softplus(beta 1, threshold 20) or relu, then 1 - exp(-d)
-            const float raw = dsum + sm_small[640];
+            const float raw = (ds0 + ds1) + (ds2 + ds3) + sm_small[640];
             raw_den = raw;
             const float d = A.softplus ? (raw > 20.f ? raw : log1pf(expf(raw))) : fmaxf(raw, 0.f);
             alpha = 1.f - expf(-d);
@@ -447,7 +499,8 @@ __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
         } else {
           // rgb head: relu(rgb_layers.0) (128 wide, TMEM cols 0..127) . fc_rgb^T + b -> sigmoid
           float s0 = sm_small[641], s1 = sm_small[642], s2 = sm_small[643];
-#pragma unroll 1
+          uint32_t mc[4];
+#pragma unroll
           for (int c0 = 0; c0 < 128; c0 += 32) {
             uint32_t v0[32];
             tmem_ld32(tacc + c0, v0);
@@ -455,12 +508,18 @@ __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
             const float *w0 = sm_small + 256 + c0, *w1 = w0 + 128, *w2 = w0 + 256;
             if (sv) {
               uint8_t *ghc = gtile + FW_HC + (row >> 3) * 2048 + (row & 7) * 16 + (c0 >> 3) * 128;
+              uint32_t bits = 0;
 #pragma unroll
-              for (int g = 0; g < 4; ++g)
-                st_global_v4(ghc + g * 128, pack_bf16_relu(__uint_as_float(v0[8 * g]), __uint_as_float(v0[8 * g + 1])),
-                             pack_bf16_relu(__uint_as_float(v0[8 * g + 2]), __uint_as_float(v0[8 * g + 3])),
-                             pack_bf16_relu(__uint_as_float(v0[8 * g + 4]), __uint_as_float(v0[8 * g + 5])),
-                             pack_bf16_relu(__uint_as_float(v0[8 * g + 6]), __uint_as_float(v0[8 * g + 7])));
+              for (int g = 0; g < 4; ++g) {
+                uint32_t w[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  w[k] = pack_bf16_relu(__uint_as_float(v0[8 * g + 2 * k]), __uint_as_float(v0[8 * g + 2 * k + 1]));
+                  bits |= gt0_mask2(w[k]) & ((1u << (4 * g + k)) | (1u << (16 + 4 * g + k)));
+                }
+                st_global_v4(ghc + g * 128, w[0], w[1], w[2], w[3]);
+              }
+              mc[c0 >> 5] = bits;
             }
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
@@ -473,7 +532,10 @@ __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
           r_s = 1.f / (1.f + expf(-s0));
           g_s = 1.f / (1.f + expf(-s1));
           b_s = 1.f / (1.f + expf(-s2));
-          if (sv) A.ws_s[(size_t)ray * 128 + row] = make_float4(r_s, g_s, b_s, raw_den);
+          if (sv) {
+            A.ws_s[(size_t)ray * 128 + row] = make_float4(r_s, g_s, b_s, raw_den);
+            st_global_v4(gtile + FW_MASK + 8 * 4096u + row * 32, mc[0], mc[1], mc[2], mc[3]);
+          }
         }
       }
       // ---- compositing over the ray (model/rendering.py:124-126): T = exclusive cumprod(1 - alpha + 1e-6)
@@ -516,10 +578,10 @@ __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
 // =====================================================================================================================
 namespace {
 
-constexpr int BW_RING = 8;
+constexpr int BW_RING = 4;
 constexpr uint32_t SB_ACT = 0;                         // 2 x 65536: dY operand image, updated in place layer by layer
 constexpr uint32_t SB_DSMALL = 131072;                 // 2 x 4096 : [128 x 16] d_raw {r,g,b,density}
-constexpr uint32_t SB_RING = SB_DSMALL + 8192;         // BW_RING x 8192
+constexpr uint32_t SB_RING = SB_DSMALL + 8192;         // BW_RING x TC_SLOT
 constexpr uint32_t SB_SMALL = SB_RING + BW_RING * TC_SLOT;  // fp32 w_rgb[384]
 constexpr uint32_t SB_SCAN = SB_SMALL + 384 * 4;       // 2 tiles x 64 floats
 constexpr uint32_t SB_BARS = SB_SCAN + 2 * 64 * 4;
@@ -544,10 +606,13 @@ __device__ __forceinline__ uint4 ld_global_v4(const void *p) {
   asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
   return r;
 }
-// keep the halves of `d` (packed bf16x2) whose relu output `h` (packed bf16x2, >= 0) is positive
-__device__ __forceinline__ uint32_t relu_mask2(uint32_t d, uint32_t h) {
+// keep the halves of the packed bf16x2 word `d` = columns (2p, 2p+1) of a 32-column block whose ReLU was active:
+// `bits` is the block's mask word written by the forward (bit p = even column, bit 16+p = odd column).
+template <int P>
+__device__ __forceinline__ uint32_t relu_mask_bits(uint32_t d, uint32_t bits) {
   uint32_t m;
-  asm("set.gt.u32.bf16x2 %0, %1, %2;" : "=r"(m) : "r"(h), "r"(0u));
+  const uint32_t t = bits << (15 - P);  // bit p -> sign of byte 1, bit 16+p -> sign of byte 3
+  asm("prmt.b32 %0, %1, %1, 0xBB99;" : "=r"(m) : "r"(t));  // replicate those sign bits over the low / high half
   return d & m;
 }
 __device__ __forceinline__ float warp_excl_suffix(float v, int lane, float &total) {
@@ -603,43 +668,11 @@ __global__ void __launch_bounds__(320, 1) tc_bwd_kernel(const BwdArgs A) {
   const int n_pairs = (A.n_rays + 1) >> 1;
 
   if (warp == 8) {
-    if (elect_one()) {
-      uint32_t slot = 0, phase = 0;
-      for (int pair = blockIdx.x; pair < n_pairs; pair += gridDim.x)
-        for (int i = 0; i < A.n_stages; ++i) {
-          const TcStage st = c_bwd_stages[i];
-          mbar_wait(bar_empty + 8 * slot, phase ^ 1);
-          const uint32_t bytes = (uint32_t)st.n * 32u;
-          mbar_arrive_expect_tx(bar_full + 8 * slot, bytes);
-          bulk_g2s(sbase + SB_RING + slot * TC_SLOT, A.wimg + st.w_off, bytes, bar_full + 8 * slot);
-          if (++slot == BW_RING) { slot = 0; phase ^= 1; }
-        }
-    }
+    if (elect_one()) weight_producer<BW_RING>(c_bwd_groups, A.n_stages, n_pairs, A.wimg, sbase + SB_RING, bar_full, bar_empty);
     __syncwarp();
   } else if (warp == 9) {
-    if (elect_one()) {
-      uint32_t slot = 0, phase = 0, act_par = 0;
-      for (int pair = blockIdx.x; pair < n_pairs; pair += gridDim.x)
-        for (int i = 0; i < A.n_stages; ++i) {
-          const TcStage st = c_bwd_stages[i];
-          if (st.first) { mbar_wait(bar_act, act_par); act_par ^= 1; }
-          mbar_wait(bar_full + 8 * slot, phase);
-          tc_fence_after();
-          const uint32_t a_off = (st.a_src == A_DSMALL) ? SB_DSMALL : SB_ACT;
-          const uint32_t a_sz = (st.a_src == A_DSMALL) ? 4096u : 65536u;
-          const uint32_t a_gs = (st.a_src == A_ACT) ? 4096u : (st.a_src == A_ACT128 ? 2048u : 256u);
-          const uint64_t bd = desc_kmajor(sbase + SB_RING + slot * TC_SLOT, 256);
-          const uint32_t idesc = idesc_bf16(128, st.n, 0, 0);
-#pragma unroll
-          for (int t = 0; t < 2; ++t) {
-            const uint64_t ad = desc_kmajor(sbase + a_off + t * a_sz + (uint32_t)st.a_k * 256u, a_gs);
-            umma(tmem + t * 256, ad, bd, idesc, st.first ? 0u : 1u);
-          }
-          umma_commit(bar_empty + 8 * slot);
-          if (st.last) umma_commit(bar_acc);
-          if (++slot == BW_RING) { slot = 0; phase ^= 1; }
-        }
-    }
+    if (elect_one())
+      mma_issuer<BW_RING>(c_bwd_groups, A.n_stages, n_pairs, sbase, sbase + SB_RING, bar_full, bar_empty, bar_acc, bar_act, tmem, nullptr);
     __syncwarp();
   } else {
     const int t = warp >> 2, q = warp & 3, row = q * 32 + lane;
@@ -697,17 +730,26 @@ __global__ void __launch_bounds__(320, 1) tc_bwd_kernel(const BwdArgs A) {
         }
       }
       // ---- dY of rgb_layers.0 = (fc_rgb^T d_raw_rgb) masked by relu(Hc) > 0  -> 128-col operand image
-#pragma unroll 1
-      for (int j = 0; j < 16; ++j) {
-        const uint4 h = ld_global_v4(ftile + FW_HC + rowoff128 + j * 128);
-        const float *w0 = sm_wrgb + 8 * j, *w1 = w0 + 128, *w2 = w0 + 256;
-        float v[8];
+      {
+        const uint4 hcm = ld_global_v4(ftile + FW_MASK + 8 * 4096u + row * 32);
+        const uint32_t hb[4] = {hcm.x, hcm.y, hcm.z, hcm.w};
 #pragma unroll
-        for (int k = 0; k < 8; ++k) v[k] = w0[k] * dr0 + w1[k] * dr1 + w2[k] * dr2;
-        const uint32_t o0 = relu_mask2(pack_bf16(v[0], v[1]), h.x), o1 = relu_mask2(pack_bf16(v[2], v[3]), h.y),
-                       o2 = relu_mask2(pack_bf16(v[4], v[5]), h.z), o3 = relu_mask2(pack_bf16(v[6], v[7]), h.w);
-        st_shared_v4(sbase + SB_ACT + t * 65536u + rowoff128 + j * 128, o0, o1, o2, o3);
-        if (valid) st_global_v4(btile + BW_DYRGB0 + rowoff128 + j * 128, o0, o1, o2, o3);
+        for (int j = 0; j < 16; ++j) {
+          const float *w0 = sm_wrgb + 8 * j, *w1 = w0 + 128, *w2 = w0 + 256;
+          float v[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) v[k] = w0[k] * dr0 + w1[k] * dr1 + w2[k] * dr2;
+          const uint32_t bits = hb[j >> 2];
+          uint32_t o0 = pack_bf16(v[0], v[1]), o1 = pack_bf16(v[2], v[3]), o2 = pack_bf16(v[4], v[5]), o3 = pack_bf16(v[6], v[7]);
+          switch (j & 3) {
+            case 0: o0 = relu_mask_bits<0>(o0, bits); o1 = relu_mask_bits<1>(o1, bits); o2 = relu_mask_bits<2>(o2, bits); o3 = relu_mask_bits<3>(o3, bits); break;
+            case 1: o0 = relu_mask_bits<4>(o0, bits); o1 = relu_mask_bits<5>(o1, bits); o2 = relu_mask_bits<6>(o2, bits); o3 = relu_mask_bits<7>(o3, bits); break;
+            case 2: o0 = relu_mask_bits<8>(o0, bits); o1 = relu_mask_bits<9>(o1, bits); o2 = relu_mask_bits<10>(o2, bits); o3 = relu_mask_bits<11>(o3, bits); break;
+            default: o0 = relu_mask_bits<12>(o0, bits); o1 = relu_mask_bits<13>(o1, bits); o2 = relu_mask_bits<14>(o2, bits); o3 = relu_mask_bits<15>(o3, bits); break;
+          }
+          st_shared_v4(sbase + SB_ACT + t * 65536u + rowoff128 + j * 128, o0, o1, o2, o3);
+          if (valid) st_global_v4(btile + BW_DYRGB0 + rowoff128 + j * 128, o0, o1, o2, o3);
+        }
       }
       fence_async_smem();
       tc_fence_before();
@@ -726,11 +768,11 @@ __global__ void __launch_bounds__(320, 1) tc_bwd_kernel(const BwdArgs A) {
 #pragma unroll 1
       for (int e = 0; e < 12; ++e) {
         const int ek = kind[e];
-        const uint8_t *hrow = ftile + FW_H + (uint32_t)slot_of[e] * 65536u + rowoff256;
-        uint4 hm[8];
+        uint32_t mw[8];
         if (ek == EPI_MASK) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) hm[j] = ld_global_v4(hrow + j * 128);
+          const uint8_t *gm = ftile + FW_MASK + (uint32_t)slot_of[e] * 4096u + row * 32;
+          const uint4 m0 = ld_global_v4(gm), m1 = ld_global_v4(gm + 16);
+          mw[0] = m0.x; mw[1] = m0.y; mw[2] = m0.z; mw[3] = m0.w; mw[4] = m1.x; mw[5] = m1.y; mw[6] = m1.z; mw[7] = m1.w;
         }
         mbar_wait(bar_acc, acc_par);
         acc_par ^= 1;
@@ -748,32 +790,25 @@ __global__ void __launch_bounds__(320, 1) tc_bwd_kernel(const BwdArgs A) {
           enc_backward<10>(xp, v0, d_p);
         } else {
           uint8_t *grow = btile + (ek == EPI_FEAT ? BW_DYFEAT : BW_DY + (uint32_t)slot_of[e] * 65536u) + rowoff256;
-#pragma unroll 1
-          for (int c0 = 0; c0 < 256; c0 += 64) {
-            uint32_t v0[32], v1[32];
-            tmem_ld32(tacc + c0, v0);
-            tmem_ld32(tacc + c0 + 32, v1);
-            uint4 hn[8];
-            if (ek == EPI_MASK && c0 + 64 < 256) {
+          const bool masked = (ek == EPI_MASK);
 #pragma unroll
-              for (int j = 0; j < 8; ++j) hn[j] = ld_global_v4(hrow + ((c0 + 64) >> 3) * 128 + j * 128);
-            }
+          for (int c0 = 0; c0 < 256; c0 += 32) {
+            uint32_t v[32];
+            tmem_ld32(tacc + c0, v);
             tmem_ld_wait();
+            const uint32_t bits = masked ? mw[c0 >> 5] : 0xFFFFFFFFu;
+            uint32_t o[16];
 #pragma unroll
-            for (int gch = 0; gch < 8; ++gch) {
-              const uint32_t *v = (gch < 4) ? &v0[8 * gch] : &v1[8 * (gch - 4)];
-              uint32_t o0 = pack_bf16(__uint_as_float(v[0]), __uint_as_float(v[1])), o1 = pack_bf16(__uint_as_float(v[2]), __uint_as_float(v[3]));
-              uint32_t o2 = pack_bf16(__uint_as_float(v[4]), __uint_as_float(v[5])), o3 = pack_bf16(__uint_as_float(v[6]), __uint_as_float(v[7]));
-              if (ek == EPI_MASK) {
-                o0 = relu_mask2(o0, hm[gch].x); o1 = relu_mask2(o1, hm[gch].y); o2 = relu_mask2(o2, hm[gch].z); o3 = relu_mask2(o3, hm[gch].w);
-              }
+            for (int p = 0; p < 16; ++p) o[p] = pack_bf16(__uint_as_float(v[2 * p]), __uint_as_float(v[2 * p + 1]));
+            o[0] = relu_mask_bits<0>(o[0], bits); o[1] = relu_mask_bits<1>(o[1], bits); o[2] = relu_mask_bits<2>(o[2], bits); o[3] = relu_mask_bits<3>(o[3], bits);
+            o[4] = relu_mask_bits<4>(o[4], bits); o[5] = relu_mask_bits<5>(o[5], bits); o[6] = relu_mask_bits<6>(o[6], bits); o[7] = relu_mask_bits<7>(o[7], bits);
+            o[8] = relu_mask_bits<8>(o[8], bits); o[9] = relu_mask_bits<9>(o[9], bits); o[10] = relu_mask_bits<10>(o[10], bits); o[11] = relu_mask_bits<11>(o[11], bits);
+            o[12] = relu_mask_bits<12>(o[12], bits); o[13] = relu_mask_bits<13>(o[13], bits); o[14] = relu_mask_bits<14>(o[14], bits); o[15] = relu_mask_bits<15>(o[15], bits);
+#pragma unroll
+            for (int gch = 0; gch < 4; ++gch) {
               const uint32_t off = ((c0 >> 3) + gch) * 128;
-              st_shared_v4(act_row + off, o0, o1, o2, o3);
-              if (valid) st_global_v4(grow + off, o0, o1, o2, o3);
-            }
-            if (ek == EPI_MASK) {
-#pragma unroll
-              for (int j = 0; j < 8; ++j) hm[j] = hn[j];
+              st_shared_v4(act_row + off, o[4 * gch], o[4 * gch + 1], o[4 * gch + 2], o[4 * gch + 3]);
+              if (valid) st_global_v4(grow + off, o[4 * gch], o[4 * gch + 1], o[4 * gch + 2], o[4 * gch + 3]);
             }
           }
         }
@@ -823,8 +858,10 @@ __global__ void __launch_bounds__(320, 1) tc_bwd_kernel(const BwdArgs A) {
 namespace {
 
 constexpr int WG_MAX_JOBS = 32;
-constexpr int WG_RING = 7;
-constexpr uint32_t WG_SLOT = 30720;   // 32 samples: P 8 KB + Q parts up to 22 KB
+constexpr int WG_RING = 3;
+constexpr int WG_SUB = 2;             // stages per 128-sample tile
+constexpr int WG_GROUPS = 8;          // 8-sample row groups per stage (64 samples, 4 k-steps)
+constexpr uint32_t WG_SLOT = 61440;   // P 16 KB + Q parts up to 44 KB
 constexpr uint32_t SW_RING = 0;
 constexpr uint32_t SW_BARS = WG_RING * WG_SLOT;
 constexpr uint32_t SW_TOTAL = SW_BARS + 24 * 8 + 16;
@@ -874,46 +911,59 @@ __global__ void __launch_bounds__(192, 1) tc_wgrad_kernel(const WgArgs A) {
   const uint32_t tmem = *tmem_slot;
   uint32_t q_off[3];
   {
-    uint32_t o = 8192;
-    for (int p = 0; p < J.n_parts; ++p) { q_off[p] = o; o += 4 * J.q[p].gs; }
+    uint32_t o = WG_GROUPS * 2048;
+    for (int p = 0; p < J.n_parts; ++p) { q_off[p] = o; o += WG_GROUPS * J.q[p].gs; }
   }
   if (warp == 4) {
-    if (elect_one()) {
-      uint32_t slot = 0, phase = 0;
-      uint32_t bytes = 8192;
-      for (int p = 0; p < J.n_parts; ++p) bytes += 4 * J.q[p].gs;
-      const uint8_t *pbase = (J.p_ws ? A.ws_bwd : A.ws_fwd) + J.p_slot_off + (J.p_col0 >> 3) * 128;
-      const size_t pstride = J.p_ws ? BWD_TILE_BYTES : FWD_TILE_BYTES;
-      for (int t = t0; t < t1; ++t)
-        for (int sub = 0; sub < 4; ++sub) {
+    // producer: lane 0 arms the barrier, then lanes 0..(copies-1) each issue one bulk copy
+    uint32_t slot = 0, phase = 0;
+    uint32_t bytes = WG_GROUPS * 2048;
+    for (int p = 0; p < J.n_parts; ++p) bytes += WG_GROUPS * J.q[p].gs;
+    const uint8_t *pbase = (J.p_ws ? A.ws_bwd : A.ws_fwd) + J.p_slot_off + (J.p_col0 >> 3) * 128;
+    const size_t pstride = J.p_ws ? BWD_TILE_BYTES : FWD_TILE_BYTES;
+    const bool p_contig = (J.p_gs == 2048);
+    const int n_pcopies = p_contig ? 1 : WG_GROUPS;
+    for (int t = t0; t < t1; ++t)
+      for (int sub = 0; sub < WG_SUB; ++sub) {
+        if (lane == 0) {
           mbar_wait(bar_empty + 8 * slot, phase ^ 1);
           mbar_arrive_expect_tx(bar_full + 8 * slot, bytes);
-          const uint32_t dst = sbase + SW_RING + slot * WG_SLOT;
-          for (int g = 0; g < 4; ++g)
-            bulk_g2s(dst + g * 2048, pbase + (size_t)t * pstride + (size_t)(4 * sub + g) * J.p_gs, 2048, bar_full + 8 * slot);
-          for (int p = 0; p < J.n_parts; ++p) {
-            const uint8_t *qb = (J.q[p].ws ? A.ws_bwd + (size_t)t * BWD_TILE_BYTES : A.ws_fwd + (size_t)t * FWD_TILE_BYTES) + J.q[p].slot_off;
-            bulk_g2s(dst + q_off[p], qb + (size_t)(4 * sub) * J.q[p].gs, 4 * J.q[p].gs, bar_full + 8 * slot);
-          }
-          if (++slot == WG_RING) { slot = 0; phase ^= 1; }
         }
-    }
-    __syncwarp();
+        __syncwarp();
+        const uint32_t dst = sbase + SW_RING + slot * WG_SLOT;
+        if (lane < n_pcopies) {
+          if (p_contig) bulk_g2s(dst, pbase + (size_t)t * pstride + (size_t)(WG_GROUPS * sub) * 2048, WG_GROUPS * 2048, bar_full + 8 * slot);
+          else bulk_g2s(dst + lane * 2048, pbase + (size_t)t * pstride + (size_t)(WG_GROUPS * sub + lane) * J.p_gs, 2048, bar_full + 8 * slot);
+        } else if (lane < n_pcopies + J.n_parts) {
+          const int p = lane - n_pcopies;
+          const uint8_t *qb = (J.q[p].ws ? A.ws_bwd + (size_t)t * BWD_TILE_BYTES : A.ws_fwd + (size_t)t * FWD_TILE_BYTES) + J.q[p].slot_off;
+          bulk_g2s(dst + q_off[p], qb + (size_t)(WG_GROUPS * sub) * J.q[p].gs, WG_GROUPS * J.q[p].gs, bar_full + 8 * slot);
+        }
+        __syncwarp();
+        if (++slot == WG_RING) { slot = 0; phase ^= 1; }
+      }
   } else if (warp == 5) {
     if (elect_one()) {
       uint32_t slot = 0, phase = 0, accum = 0;
+      // loop-invariant descriptor pieces
+      uint32_t qgs[3], qn_idesc[3], qtm[3];
+      for (int p = 0; p < 3; ++p) {
+        qgs[p] = p < J.n_parts ? J.q[p].gs : 0;
+        qn_idesc[p] = idesc_bf16(128, p < J.n_parts ? J.q[p].n : 16, 1, 1);
+        qtm[p] = tmem + (p < J.n_parts ? J.q[p].tm_col : 0);
+      }
+      const int n_parts = J.n_parts;
       for (int t = t0; t < t1; ++t)
-        for (int sub = 0; sub < 4; ++sub) {
+        for (int sub = 0; sub < WG_SUB; ++sub) {
           mbar_wait(bar_full + 8 * slot, phase);
           tc_fence_after();
           const uint32_t src = sbase + SW_RING + slot * WG_SLOT;
 #pragma unroll
-          for (int ks = 0; ks < 2; ++ks) {
+          for (int ks = 0; ks < WG_GROUPS / 2; ++ks) {
             const uint64_t pd = desc_mnmajor(src + ks * 4096, 2048);
-            for (int p = 0; p < J.n_parts; ++p) {
-              const uint64_t qd = desc_mnmajor(src + q_off[p] + ks * 2 * J.q[p].gs, J.q[p].gs);
-              umma(tmem + J.q[p].tm_col, pd, qd, idesc_bf16(128, J.q[p].n, 1, 1), accum);
-            }
+#pragma unroll
+            for (int p = 0; p < 3; ++p)
+              if (p < n_parts) umma(qtm[p], pd, desc_mnmajor(src + q_off[p] + ks * 2 * qgs[p], qgs[p]), qn_idesc[p], accum);
             accum = 1;
           }
           umma_commit(bar_empty + 8 * slot);
@@ -952,7 +1002,9 @@ WgPlan build_wg_plan() {
   auto part = [](int ws, uint32_t off, uint32_t gs, int n, int tm) { WgPart q{}; q.ws = (uint8_t)ws; q.slot_off = off; q.gs = gs; q.n = (uint16_t)n; q.tm_col = (uint16_t)tm; return q; };
   auto seg = [](int param, int offset, int sm, int sn, int tm, int count) { WgSeg s{}; s.param = param; s.offset = offset; s.stride_m = sm; s.stride_n = sn; s.tm_col = (uint16_t)tm; s.count = (uint16_t)count; return s; };
   auto push = [&](WgJob J, int splits) { J.splits = (uint16_t)splits; J.cta0 = (uint16_t)P.n_ctas; P.n_ctas += splits; P.jobs.push_back(J); };
-  const int BIG = 16, MID = 9, SMALL = 6;
+  // split counts proportional to the bytes each job streams per ray (memory-bound), summing to 2 x 148 CTAs:
+  // 17 x 14 (104 KB/ray) + 2 x 16 (layers1.0, 120 KB) + 2 x 7 (layers0.0, 56 KB) + 3 x 4 (heads, 36 KB) = 296
+  const int BIG = 14, BIG4 = 16, MID = 7, SMALL = 4;
   for (int L = 0; L < 8; ++L)
     for (int h = 0; h < 2; ++h) {
       WgJob J{};
@@ -975,7 +1027,7 @@ WgPlan build_wg_plan() {
         J.seg[0] = seg(wp, 128 * h * 319, 319, 1, 0, 256);
         J.seg[1] = seg(wp, 128 * h * 319 + 256, 319, 1, 256, 63);
         J.seg[2] = seg(wp + 1, 128 * h, 1, 1, 320 + 27, 1);
-        push(J, BIG);
+        push(J, BIG4);
       } else {
         J.n_parts = 2;
         J.q[0] = part(0, FW_H + (uint32_t)(L - 1) * 65536u, 4096, 256, 0);
@@ -1041,6 +1093,39 @@ const WgPlan &wg_plan() {
 // =====================================================================================================================
 namespace {
 
+
+// k-steps -> issue groups (see c_fwd_groups).  a_off/a_stride: shared-memory placement of each A image kind.
+struct ALayout { uint32_t off[5], tile_stride[5], gs[5]; };
+std::vector<uint4> build_groups(const Schedule &S, const ALayout &L) {
+  std::vector<uint4> G;
+  size_t i = 0;
+  while (i < S.st.size()) {
+    const TcStage &a = S.st[i];
+    uint32_t nk = 1;
+    if (i + 1 < S.st.size()) {
+      const TcStage &b = S.st[i + 1];
+      if (!a.last && !b.first && b.a_src == a.a_src && b.a_k == a.a_k + 1 && b.n == a.n && b.w_off == a.w_off + a.n * 32u) nk = 2;
+    }
+    const TcStage &z = S.st[i + nk - 1];
+    uint4 g;
+    g.x = a.w_off;
+    g.y = (L.off[a.a_src] + (uint32_t)a.a_k * 256u) | (nk << 18) | ((uint32_t)a.first << 20) | ((uint32_t)z.last << 21);
+    g.z = (uint32_t)a.n | (L.gs[a.a_src] << 16);
+    g.w = L.tile_stride[a.a_src];
+    G.push_back(g);
+    i += nk;
+  }
+  return G;
+}
+const std::vector<uint4> &fwd_groups() {
+  static std::vector<uint4> g = build_groups(fwd_schedule(), ALayout{{SM_ACT, SM_ENC, SM_AUX, 0, 0}, {65536u, 16384u, 512u, 0, 0}, {GS_ACT, GS_ENC, 0u, 0, 0}});
+  return g;
+}
+const std::vector<uint4> &bwd_groups() {
+  static std::vector<uint4> g = build_groups(bwd_schedule(), ALayout{{SB_ACT, 0, 0, SB_ACT, SB_DSMALL}, {65536u, 0, 0, 65536u, 4096u}, {4096u, 0, 0, 2048u, 256u}});
+  return g;
+}
+
 long long *g_trace = nullptr;
 std::once_flag g_tables_once;
 int g_tables_err = 0;
@@ -1056,6 +1141,9 @@ void upload_tables() {
   if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_fwd_pack, F.pk.data(), F.pk.size() * sizeof(TcPack));
   if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_bwd_stages, B.st.data(), B.st.size() * sizeof(TcStage));
   if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_bwd_pack, B.pk.data(), B.pk.size() * sizeof(TcPack));
+  if (e == cudaSuccess && (fwd_groups().size() > TC_MAX_GROUPS || bwd_groups().size() > TC_MAX_GROUPS)) { g_tables_err = NNB_ERR_UNSUPPORTED; return; }
+  if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_fwd_groups, fwd_groups().data(), fwd_groups().size() * sizeof(uint4));
+  if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_bwd_groups, bwd_groups().data(), bwd_groups().size() * sizeof(uint4));
   if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_wg_jobs, W.jobs.data(), W.jobs.size() * sizeof(WgJob));
   if (e == cudaSuccess) e = cudaFuncSetAttribute(tc_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SM_TOTAL);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(tc_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SM_TOTAL);
@@ -1098,7 +1186,7 @@ int nnb_tc_render_fwd(const nnb_render_cfg *cfg, const float *const *params, con
   A.origin = origin; A.dirs = dirs; A.noise = noise;
   A.w_den = params[P_DEN]; A.b_den = params[P_DEN + 1]; A.w_rgb = params[P_RGB]; A.b_rgb = params[P_RGB + 1];
   A.rgb = rgb; A.dist = dist; A.weights = weights; A.alpha = alpha; A.z_vals = z_vals;
-  A.n_rays = cfg->n_rays; A.S = cfg->n_samples; A.n_stages = (int)fwd_schedule().st.size();
+  A.n_rays = cfg->n_rays; A.S = cfg->n_samples; A.n_stages = (int)fwd_groups().size();
   A.near_ = cfg->near_; A.far_ = cfg->far_;
   A.softplus = cfg->occ_softplus; A.white = cfg->white_bkgd; A.use_dir = cfg->use_dir;
   A.trace = g_trace;
@@ -1136,7 +1224,7 @@ int nnb_tc_render_bwd(const nnb_render_cfg *cfg, const float *const *params, con
   B.d_rgb = d_rgb; B.d_dist = d_dist; B.d_alpha_out = d_alpha_out; B.d_weights_out = d_weights_out;
   B.w_rgb = params[P_RGB];
   B.d_origin = d_origin; B.d_dirs = d_dirs; B.d_b_den = d_params[P_DEN + 1]; B.d_b_rgb = d_params[P_RGB + 1];
-  B.n_rays = R; B.n_stages = (int)bwd_schedule().st.size();
+  B.n_rays = R; B.n_stages = (int)bwd_groups().size();
   B.softplus = cfg->occ_softplus; B.white = cfg->white_bkgd; B.use_dir = cfg->use_dir;
   const int n_pairs = (R + 1) / 2;
   const int grid = n_pairs < nnb_sm_count() ? n_pairs : nnb_sm_count();
