@@ -7,73 +7,122 @@
 // Index parity: the reference takes the FIRST index of the minimum of the fp32 value
 //     s_j = sqrt_rn( (dx*dx + dy*dy) + dz*dz )          (each op rounded; verified against torch CPU)
 // sqrt_rn maps up to a few adjacent d2 values to the same s, so comparing d2 alone would break ties the
-// reference does not break.  We keep, per source, the current minimum s and L(s) = the smallest d2 whose
-// sqrt_rn is still s; a candidate replaces the incumbent only if d2 < L(s) (strictly smaller s).  Candidates
-// are visited in ascending j, and partial results from different destination ranges are merged with an
-// atomicMin on (bits(s) << 32 | j), so the first index wins exactly as in torch.argmin.
+// reference does not break: a candidate replaces the incumbent only if its ROUNDED distance s is strictly
+// smaller.  Candidates are visited in ascending j, and partial results from different destination ranges are
+// merged with an atomicMin on (bits(s) << 32 | j), so the first index wins exactly as in torch.argmin.
 #include "nnb_common.cuh"
 
 #define CH_THREADS 128
-#define CH_SPT 2      // sources per thread
+#define CH_SPT 4      // sources per thread
 #define CH_TILE 1024  // destination points per shared-memory tile
 
-__device__ __forceinline__ float lowest_same_sqrt(float d2, float s) {
-  // smallest float x <= d2 with sqrt_rn(x) == s
-  float x = d2;
-  for (int it = 0; it < 8; ++it) {
-    if (x <= 0.f) break;
-    const float y = __uint_as_float(__float_as_uint(x) - 1u);
-    if (__fsqrt_rn(y) != s) break;
-    x = y;
-  }
-  return x;
-}
-
+// Two passes over the (source, destination) pairs, both with the expanded form  a = |q|^2 - 2 s.q  (three FMAs, |q|^2
+// rides in tile[].w) so that the hot loops are branch-free:
+//   pass 1 (EXACT = false): running minimum of a per source -> bound[s] = min_j (a_j + |s|^2)  (atomicMin over splits)
+//   pass 2 (EXACT = true) : pairs with a < (bound - |s|^2) + margin are re-evaluated exactly (direct differences in
+//                           the reference's op order); margin = 1e-6 (|s|^2 + 2 max|q|^2 + bound) covers twice the rounding
+//                           error of the expanded form (<= 4 eps (|s|^2 + 2|q|^2), eps = 6e-8) plus sqrt ties, so no pair the
+//                           reference could select is ever screened out and indices stay bit-exact.  Typically 1-3 pairs per
+//                           source survive, so the exact path is cold.
+template <bool EXACT>
 __global__ void __launch_bounds__(CH_THREADS) chamfer_nn_kernel(const float *__restrict__ src, int n_src,
                                                                 const float *__restrict__ dst, int n_dst, int dst_per_block,
+                                                                unsigned int *__restrict__ bound, unsigned int *__restrict__ qqmax_g,
                                                                 unsigned long long *__restrict__ best) {
   __shared__ float4 tile[CH_TILE];
+  __shared__ float qqmax_s[CH_THREADS / 32];
   const int s0 = (blockIdx.x * CH_THREADS + threadIdx.x) * CH_SPT;
-  float sx[CH_SPT], sy[CH_SPT], sz[CH_SPT], lim[CH_SPT], smin[CH_SPT];
+  float sx[CH_SPT], sy[CH_SPT], sz[CH_SPT], ss[CH_SPT], m2x[CH_SPT], m2y[CH_SPT], m2z[CH_SPT], thr[CH_SPT], smin[CH_SPT], amin[CH_SPT];
   int jbest[CH_SPT];
 #pragma unroll
   for (int k = 0; k < CH_SPT; ++k) {
     const int s = min(s0 + k, n_src - 1);
     sx[k] = src[3 * s]; sy[k] = src[3 * s + 1]; sz[k] = src[3 * s + 2];
-    lim[k] = INFINITY; smin[k] = INFINITY; jbest[k] = 0x7fffffff;
+    ss[k] = sx[k] * sx[k] + sy[k] * sy[k] + sz[k] * sz[k];
+    m2x[k] = -2.f * sx[k]; m2y[k] = -2.f * sy[k]; m2z[k] = -2.f * sz[k];
+    smin[k] = INFINITY; amin[k] = INFINITY; jbest[k] = 0x7fffffff;
+    if (EXACT) {
+      const float b = __uint_as_float(bound[s]);
+      thr[k] = (b - ss[k]) + 1e-6f * (ss[k] + 2.f * __uint_as_float(*qqmax_g) + b);
+    } else {
+      thr[k] = 0.f;
+    }
   }
   const int j_begin = blockIdx.y * dst_per_block;
   const int j_end = min(j_begin + dst_per_block, n_dst);
+  float qm = 0.f;
   for (int base = j_begin; base < j_end; base += CH_TILE) {
     const int cnt = min(CH_TILE, j_end - base);
     __syncthreads();
-    for (int t = threadIdx.x; t < cnt; t += CH_THREADS) {
-      const float *p = dst + 3 * (size_t)(base + t);
-      tile[t] = make_float4(p[0], p[1], p[2], 0.f);
+    for (int t = threadIdx.x; t < CH_TILE; t += CH_THREADS) {
+      float4 v = make_float4(0.f, 0.f, 0.f, INFINITY);  // padding never wins
+      if (t < cnt) {
+        const float *p = dst + 3 * (size_t)(base + t);
+        v.x = p[0]; v.y = p[1]; v.z = p[2];
+        v.w = v.x * v.x + v.y * v.y + v.z * v.z;
+        qm = fmaxf(qm, v.w);
+      }
+      tile[t] = v;
     }
     __syncthreads();
-#pragma unroll 4
-    for (int t = 0; t < cnt; ++t) {
-      const float4 q = tile[t];
+    for (int t = 0; t < cnt; t += 4) {
+      float a[CH_SPT][4];
 #pragma unroll
-      for (int k = 0; k < CH_SPT; ++k) {
-        const float dx = __fsub_rn(sx[k], q.x), dy = __fsub_rn(sy[k], q.y), dz = __fsub_rn(sz[k], q.z);
-        const float d2 = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
-        if (d2 < lim[k]) {  // rare path
-          const float s = __fsqrt_rn(d2);
-          smin[k] = s;
-          jbest[k] = base + t;
-          lim[k] = lowest_same_sqrt(d2, s);
+      for (int u = 0; u < 4; ++u) {
+        const float4 q = tile[t + u];
+#pragma unroll
+        for (int k = 0; k < CH_SPT; ++k) a[k][u] = fmaf(m2x[k], q.x, fmaf(m2y[k], q.y, fmaf(m2z[k], q.z, q.w)));
+      }
+      if (!EXACT) {
+#pragma unroll
+        for (int k = 0; k < CH_SPT; ++k) amin[k] = fminf(fminf(amin[k], fminf(a[k][0], a[k][1])), fminf(a[k][2], a[k][3]));
+      } else {
+        float worst = INFINITY;
+#pragma unroll
+        for (int k = 0; k < CH_SPT; ++k) worst = fminf(worst, fminf(fminf(a[k][0], a[k][1]), fminf(a[k][2], a[k][3])) - thr[k]);
+        if (worst < 0.f) {  // cold path
+#pragma unroll 1
+          for (int u = 0; u < 4; ++u) {
+            const float4 q = tile[t + u];
+#pragma unroll
+            for (int k = 0; k < CH_SPT; ++k) {
+              const float ak = fmaf(m2x[k], q.x, fmaf(m2y[k], q.y, fmaf(m2z[k], q.z, q.w)));
+              if (ak < thr[k]) {
+                const float dx = __fsub_rn(sx[k], q.x), dy = __fsub_rn(sy[k], q.y), dz = __fsub_rn(sz[k], q.z);
+                const float d2 = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+                const float s = __fsqrt_rn(d2);
+                if (s < smin[k]) {  // strictly smaller rounded distance: first index wins ties, as torch.argmin
+                  smin[k] = s;
+                  jbest[k] = base + t + u;
+                }
+              }
+            }
+          }
         }
       }
     }
   }
+  if (!EXACT) {
 #pragma unroll
-  for (int k = 0; k < CH_SPT; ++k) {
-    const int s = s0 + k;
-    if (s < n_src && jbest[k] != 0x7fffffff) {
-      const unsigned long long key = ((unsigned long long)__float_as_uint(smin[k]) << 32) | (unsigned int)jbest[k];
-      atomicMin(best + s, key);
+    for (int o = 16; o > 0; o >>= 1) qm = fmaxf(qm, __shfl_xor_sync(0xffffffffu, qm, o));
+    if ((threadIdx.x & 31) == 0) qqmax_s[threadIdx.x >> 5] = qm;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float q = 0.f;
+      for (int w = 0; w < CH_THREADS / 32; ++w) q = fmaxf(q, qqmax_s[w]);
+      atomicMax(qqmax_g, __float_as_uint(q));
+    }
+#pragma unroll
+    for (int k = 0; k < CH_SPT; ++k)
+      if (s0 + k < n_src) atomicMin(bound + s0 + k, __float_as_uint(fmaxf(amin[k] + ss[k], 0.f)));
+  } else {
+#pragma unroll
+    for (int k = 0; k < CH_SPT; ++k) {
+      const int s = s0 + k;
+      if (s < n_src && jbest[k] != 0x7fffffff) {
+        const unsigned long long key = ((unsigned long long)__float_as_uint(smin[k]) << 32) | (unsigned int)jbest[k];
+        atomicMin(best + s, key);
+      }
     }
   }
 }
@@ -117,11 +166,18 @@ __global__ void chamfer_err_bwd_kernel(const float *__restrict__ X, int n, const
 
 extern "C" {
 
-// `idx` (n_src int64) doubles as the 64-bit packed-key scratch, so no extra workspace is needed.
-int nnb_chamfer_nn(const float *src, int n_src, const float *dst, int n_dst, int64_t *idx, float *dist, void *stream) {
-  if (!src || !dst || !idx || n_src <= 0 || n_dst <= 0) return NNB_ERR_BAD_ARG;
+size_t nnb_chamfer_workspace_bytes(int n_src) { return ((size_t)(n_src > 0 ? n_src : 0) + 4) * sizeof(unsigned int); }
+
+// `idx` (n_src int64) doubles as the 64-bit packed-key scratch; `workspace` holds the pass-1 bounds and max |q|^2.
+int nnb_chamfer_nn(const float *src, int n_src, const float *dst, int n_dst, int64_t *idx, float *dist, void *workspace,
+                   size_t workspace_bytes, void *stream) {
+  if (!src || !dst || !idx || !workspace || n_src <= 0 || n_dst <= 0) return NNB_ERR_BAD_ARG;
+  if (workspace_bytes < nnb_chamfer_workspace_bytes(n_src)) return NNB_ERR_WORKSPACE;
   cudaStream_t s = nnb_stream(stream);
   unsigned long long *best = reinterpret_cast<unsigned long long *>(idx);
+  unsigned int *bound = static_cast<unsigned int *>(workspace), *qqmax = bound + n_src;
+  NNB_CUDA(cudaMemsetAsync(bound, 0x7f, (size_t)n_src * sizeof(unsigned int), s));
+  NNB_CUDA(cudaMemsetAsync(qqmax, 0, sizeof(unsigned int), s));
   NNB_CUDA(cudaMemsetAsync(best, 0xff, (size_t)n_src * sizeof(unsigned long long), s));
   const int gx = nnb_cdiv(n_src, CH_THREADS * CH_SPT);
   // split the destination range so that the grid covers the SMs a few times over
@@ -130,7 +186,9 @@ int nnb_chamfer_nn(const float *src, int n_src, const float *dst, int n_dst, int
   int gy = want < 1 ? 1 : (want > max_split ? max_split : want);
   int per = nnb_cdiv(nnb_cdiv(n_dst, gy), CH_TILE) * CH_TILE;
   gy = nnb_cdiv(n_dst, per);
-  chamfer_nn_kernel<<<dim3(gx, gy), CH_THREADS, 0, s>>>(src, n_src, dst, n_dst, per, best);
+  chamfer_nn_kernel<false><<<dim3(gx, gy), CH_THREADS, 0, s>>>(src, n_src, dst, n_dst, per, bound, qqmax, best);
+  NNB_CHECK_LAUNCH();
+  chamfer_nn_kernel<true><<<dim3(gx, gy), CH_THREADS, 0, s>>>(src, n_src, dst, n_dst, per, bound, qqmax, best);
   NNB_CHECK_LAUNCH();
   int g = nnb_cdiv(n_src, 256);
   chamfer_unpack_kernel<<<g, 256, 0, s>>>(best, n_src, idx, dist);

@@ -73,12 +73,13 @@ SIGNATURES = {
     "nnb_reproj_bwd": [_p, _i, _i, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p],
     "nnb_photometric_fwd": [_p, _p, _p, _i, _p, _p],
     "nnb_photometric_bwd": [_p, _p, _p, _i, _p, _p, _p, _p, _p],
-    "nnb_chamfer_nn": [_p, _i, _p, _i, _p, _p, _p],
+    "nnb_chamfer_workspace_bytes": [_i],
+    "nnb_chamfer_nn": [_p, _i, _p, _i, _p, _p, _p, C.c_size_t, _p],
     "nnb_chamfer_err_fwd": [_p, _i, _p, _p, _p, _p],
     "nnb_chamfer_err_bwd": [_p, _i, _p, _p, _p, _p, _p, _p],
     "nnb_adam_step": [_p, _p, _p, _p, _sz, _f, _f, _f, _f, _i, _p],
 }
-_RESTYPE = {"nnb_error_string": C.c_char_p, "nnb_launch_count": C.c_ulonglong, "nnb_render_workspace_bytes": C.c_size_t, "nnb_pack_weights_bytes": C.c_size_t,
+_RESTYPE = {"nnb_error_string": C.c_char_p, "nnb_launch_count": C.c_ulonglong, "nnb_render_workspace_bytes": C.c_size_t, "nnb_pack_weights_bytes": C.c_size_t, "nnb_chamfer_workspace_bytes": C.c_size_t,
             "nnb_mlp_points_workspace_bytes": C.c_size_t}
 
 _lib = None

@@ -131,6 +131,19 @@ def test_chamfer_indices_bit_exact_vs_oracle(n, m):
     assert_close(dist[sub], wd, 1e-6, 1e-7, 'nn distance')
 
 
+def test_chamfer_indices_far_from_origin():
+    """Clouds offset far from the origin: the expanded |q|^2 - 2 s.q screen loses ~7 digits to cancellation there;
+    the exact re-check must keep the indices bit-exact."""
+    from model import _ops
+    from oracle import nope_oracle as O
+    g = torch.Generator().manual_seed(77)
+    off = torch.tensor([30.0, -17.0, 55.0])
+    src, dst = torch.rand(2048, 3, generator=g) * 0.5 + off, torch.rand(5000, 3, generator=g) * 0.5 + off
+    idx, dist = _ops.chamfer_nn(src.to(dev()), dst.to(dev()), want_dist=True)
+    want = O.nearest_idx(src.t().contiguous(), dst.t().contiguous(), slice_len=256)
+    assert torch.equal(idx.cpu(), want)
+
+
 def test_backproject_and_reproject_vs_oracle():
     from model import _ops
     from oracle import nope_oracle as O
