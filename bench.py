@@ -94,9 +94,10 @@ def build_trainer(dev, n_frames, rays_global, precision, dp):
         pose.r.copy_(r0)
         pose.t.copy_(t0)
     tcfg = dict(cfg["training"], n_training_points=rays_global)
-    tr = mdl.Trainer(net, torch.optim.Adam(net.parameters(), lr=tcfg["learning_rate"]), tcfg, device=dev,
-                     optimizer_pose=torch.optim.Adam(pose.parameters(), lr=tcfg["pose_lr"]), pose_param_net=pose,
-                     optimizer_distortion=torch.optim.Adam(dist.parameters(), lr=tcfg["distortion_lr"]), distortion_net=dist,
+    # torch's fused multi-tensor Adam: same update rule as train.py:59,100,118, one launch per optimiser
+    tr = mdl.Trainer(net, torch.optim.Adam(net.parameters(), lr=tcfg["learning_rate"], fused=True), tcfg, device=dev,
+                     optimizer_pose=torch.optim.Adam(pose.parameters(), lr=tcfg["pose_lr"], fused=True), pose_param_net=pose,
+                     optimizer_distortion=torch.optim.Adam(dist.parameters(), lr=tcfg["distortion_lr"], fused=True), distortion_net=dist,
                      dp=dp)
     return cfg, scene, tr
 

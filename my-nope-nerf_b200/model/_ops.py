@@ -236,7 +236,11 @@ class RenderRays(torch.autograd.Function):
         origin, dirs, w, a, z, *params = ctx.saved_tensors
         cfg = ctx.cfg
         dev = dirs.device
-        grads = [torch.zeros_like(p) for p in params]
+        flat = torch.zeros(sum(p.numel() for p in params), device=dev)  # one fill instead of 24
+        grads, o = [], 0
+        for p in params:
+            grads.append(flat[o:o + p.numel()].view_as(p))
+            o += p.numel()
         d_origin, d_dirs = torch.empty(3, device=dev), torch.empty_like(dirs)
         parr, garr = K.param_ptr_array(params), K.param_ptr_array(grads)
 

@@ -54,28 +54,20 @@ def shard_range(n, rank, world_size):
 
 
 def flatten_grads(params):
-    dev = params[0].device
-    total = sum(p.numel() for p in params)
-    flat = torch.zeros(total, dtype=torch.float32, device=dev)
-    o = 0
-    for p in params:
-        n = p.numel()
-        if p.grad is not None:
-            flat[o:o + n].copy_(p.grad.reshape(-1))
-        o += n
-    return flat
+    """One fp32 buffer holding every gradient (zeros where a parameter has no gradient on this rank): one `cat` launch."""
+    return torch.cat([(p.grad if p.grad is not None else torch.zeros_like(p)).reshape(-1).float() for p in params])
 
 
 def unflatten_grads(flat, params):
-    o = 0
+    views, o = [], 0
     for p in params:
         n = p.numel()
-        g = flat[o:o + n].view_as(p)
-        if p.grad is None:
-            p.grad = g.clone()
-        else:
-            p.grad.copy_(g)
+        views.append(flat[o:o + n].view_as(p))
         o += n
+    missing = [i for i, p in enumerate(params) if p.grad is None]
+    for i in missing:
+        params[i].grad = torch.empty_like(params[i])
+    torch._foreach_copy_([p.grad for p in params], views)
 
 
 def init_from_env(backend=None):
