@@ -134,13 +134,53 @@ def run_b200(args):
             torch.cuda.synchronize()
 
     def timed(batches, steps, read_back):
+        """read_back=False: batches already on the device.  read_back=True (end to end): every step's batch starts in
+        pinned host memory and is uploaded on a copy stream while the previous step computes (what a DataLoader with
+        pin_memory + non_blocking does); every step's loss is copied to pinned host memory and read one step later, so
+        the read never stalls the launch queue.  All copies and reads are inside the timed region."""
         sync_all()
+        copy_stream = torch.cuda.Stream() if read_back else None
+        loss_host = torch.zeros(2, dtype=torch.float32).pin_memory() if read_back else None
+        loss_events = [None, None]
+
+        def upload(b):
+            with torch.cuda.stream(copy_stream):
+                d = {k: (v.to(dev, non_blocking=True) if torch.is_tensor(v) and k not in ("img.idx", "img.ref_idxs") else v)
+                     for k, v in b.items()}
+                ev = torch.cuda.Event()
+                ev.record(copy_stream)
+            return d, ev
+
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
+        nxt = upload(batches[0]) if read_back else None
+        losses = []
         for it in range(steps):
-            ld = tr.train_step(batches[it % n], it=it, epoch=0, scheduling_start=sched)
             if read_back:
-                float(ld["loss"])  # device->host read of the step's result
+                cur, ev = nxt
+                torch.cuda.current_stream().wait_event(ev)
+                if it + 1 < steps:
+                    nxt = upload(batches[(it + 1) % n])
+            else:
+                cur = batches[it % n]
+            ld = tr.train_step(cur, it=it, epoch=0, scheduling_start=sched)
+            if read_back:
+                slot = it & 1
+                if loss_events[slot] is not None:       # the loss of step it-2 has long arrived: read it
+                    loss_events[slot].synchronize()
+                    losses.append(float(loss_host[slot]))
+                loss_host[slot:slot + 1].copy_(ld["loss"].detach().reshape(1), non_blocking=True)
+                loss_events[slot] = torch.cuda.Event()
+                loss_events[slot].record()
+                for v in cur.values():                 # keep the uploaded batch alive until this step's kernels are queued
+                    if torch.is_tensor(v) and v.is_cuda:
+                        v.record_stream(torch.cuda.current_stream())
+        if read_back:
+            for slot in ((steps & 1), ((steps + 1) & 1)):
+                if loss_events[slot] is not None:
+                    loss_events[slot].synchronize()
+                    losses.append(float(loss_host[slot]))
+            assert len(losses) == steps
         e1.record()
         sync_all()
         ms = torch.tensor([e0.elapsed_time(e1)], device=dev)

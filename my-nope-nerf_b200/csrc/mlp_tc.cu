@@ -871,8 +871,8 @@ struct WgPart { uint32_t slot_off, gs; uint16_t n, tm_col; uint8_t ws, pad[3]; }
 struct WgSeg { int32_t param, offset, stride_m, stride_n; uint16_t tm_col, count; };
 struct WgJob {
   uint32_t p_slot_off, p_gs, p_col0;
-  uint8_t p_ws, n_parts, n_segs, pad;
-  uint16_t splits, cta0;   // CTAs [cta0, cta0 + splits) work on this job
+  uint8_t p_ws, n_parts, n_segs, shared;   // shared: the two CTAs of a cluster stream the same Q images (multicast halves)
+  uint16_t splits, cl0;    // clusters [cl0, cl0 + splits) work on this job pair; entry 2p / 2p+1 = cluster rank 0 / 1
   WgPart q[3];
   WgSeg seg[4];
 };
@@ -884,45 +884,59 @@ struct WgArgs {
   int n_tiles, n_jobs;
 };
 
-__global__ void __launch_bounds__(192, 1) tc_wgrad_kernel(const WgArgs A) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(192, 1) tc_wgrad_kernel(const WgArgs A) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const uint32_t sbase = smem_u32(smem);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t bar_full = sbase + SW_BARS, bar_empty = bar_full + WG_RING * 8, bar_done = bar_empty + WG_RING * 8;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + SW_BARS + 24 * 8);
-  // which job / split
-  int j = 0;
-  for (; j < A.n_jobs; ++j)
-    if ((int)blockIdx.x < c_wg_jobs[j].cta0 + c_wg_jobs[j].splits) break;
-  if (j >= A.n_jobs) return;
-  const WgJob &J = c_wg_jobs[j];
-  const int split = blockIdx.x - J.cta0;
-  const int t0 = (int)((long long)A.n_tiles * split / J.splits), t1 = (int)((long long)A.n_tiles * (split + 1) / J.splits);
-  if (t1 <= t0) return;
+  // which job pair / split: cluster c runs entry 2p + rank of pair p
+  const uint32_t rank = cluster_ctarank();
+  const int c = blockIdx.x >> 1;
+  int p = 0;
+  for (; 2 * p < A.n_jobs; ++p)
+    if (c < c_wg_jobs[2 * p].cl0 + c_wg_jobs[2 * p].splits) break;
+  const bool have_job = 2 * p < A.n_jobs;
+  const WgJob &J = c_wg_jobs[have_job ? 2 * p + rank : 0];
+  const bool shared = J.shared != 0;
+  int t0 = 0, t1 = 0;
+  if (have_job) {
+    // shared pairs walk the same rays; independent entries split the range once more between the two ranks
+    const int split = shared ? c - J.cl0 : 2 * (c - J.cl0) + (int)rank, nsplit = shared ? J.splits : 2 * J.splits;
+    t0 = (int)((long long)A.n_tiles * split / nsplit);
+    t1 = (int)((long long)A.n_tiles * (split + 1) / nsplit);
+  }
+  const bool active = t1 > t0;
+  const uint16_t mc_mask = shared ? (uint16_t)3 : (uint16_t)(1u << rank);
   if (threadIdx.x == 0) {
-    for (int i = 0; i < WG_RING; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, 1); }
+    for (int i = 0; i < WG_RING; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, shared ? 2 : 1); }
     mbar_init(bar_done, 1);
     mbar_fence_init();
   }
-  if (warp == 5) tmem_alloc(smem_u32(tmem_slot), 512);
+  if (warp == 5 && active) tmem_alloc(smem_u32(tmem_slot), 512);
   tc_fence_before();
   __syncthreads();
+  cluster_sync_all();   // the peer's barriers exist before anything is multicast to them
   tc_fence_after();
-  const uint32_t tmem = *tmem_slot;
+  const uint32_t tmem = active ? *tmem_slot : 0;
   uint32_t q_off[3];
   {
     uint32_t o = WG_GROUPS * 2048;
-    for (int p = 0; p < J.n_parts; ++p) { q_off[p] = o; o += WG_GROUPS * J.q[p].gs; }
+    for (int q = 0; q < J.n_parts; ++q) { q_off[q] = o; o += WG_GROUPS * J.q[q].gs; }
   }
-  if (warp == 4) {
-    // producer: lane 0 arms the barrier, then lanes 0..(copies-1) each issue one bulk copy
+  if (!active) {
+    // nothing to do (fewer rays than splits): fall through to the closing cluster barrier
+  } else if (warp == 4) {
+    // producer: lane 0 arms the barrier, then lanes 0..(copies-1) each issue one bulk copy.  In a shared pair each rank
+    // fetches half of the row groups of every Q part and multicasts them to both CTAs.
     uint32_t slot = 0, phase = 0;
     uint32_t bytes = WG_GROUPS * 2048;
-    for (int p = 0; p < J.n_parts; ++p) bytes += WG_GROUPS * J.q[p].gs;
+    for (int q = 0; q < J.n_parts; ++q) bytes += WG_GROUPS * J.q[q].gs;
     const uint8_t *pbase = (J.p_ws ? A.ws_bwd : A.ws_fwd) + J.p_slot_off + (J.p_col0 >> 3) * 128;
     const size_t pstride = J.p_ws ? BWD_TILE_BYTES : FWD_TILE_BYTES;
     const bool p_contig = (J.p_gs == 2048);
     const int n_pcopies = p_contig ? 1 : WG_GROUPS;
+    const uint32_t qg0 = shared ? rank * (WG_GROUPS / 2) : 0, qgn = shared ? WG_GROUPS / 2 : WG_GROUPS;
     for (int t = t0; t < t1; ++t)
       for (int sub = 0; sub < WG_SUB; ++sub) {
         if (lane == 0) {
@@ -935,9 +949,11 @@ __global__ void __launch_bounds__(192, 1) tc_wgrad_kernel(const WgArgs A) {
           if (p_contig) bulk_g2s(dst, pbase + (size_t)t * pstride + (size_t)(WG_GROUPS * sub) * 2048, WG_GROUPS * 2048, bar_full + 8 * slot);
           else bulk_g2s(dst + lane * 2048, pbase + (size_t)t * pstride + (size_t)(WG_GROUPS * sub + lane) * J.p_gs, 2048, bar_full + 8 * slot);
         } else if (lane < n_pcopies + J.n_parts) {
-          const int p = lane - n_pcopies;
-          const uint8_t *qb = (J.q[p].ws ? A.ws_bwd + (size_t)t * BWD_TILE_BYTES : A.ws_fwd + (size_t)t * FWD_TILE_BYTES) + J.q[p].slot_off;
-          bulk_g2s(dst + q_off[p], qb + (size_t)(WG_GROUPS * sub) * J.q[p].gs, WG_GROUPS * J.q[p].gs, bar_full + 8 * slot);
+          const int q = lane - n_pcopies;
+          const uint8_t *qb = (J.q[q].ws ? A.ws_bwd + (size_t)t * BWD_TILE_BYTES : A.ws_fwd + (size_t)t * FWD_TILE_BYTES) + J.q[q].slot_off;
+          const uint8_t *srcp = qb + (size_t)(WG_GROUPS * sub + qg0) * J.q[q].gs;
+          if (shared) bulk_g2s_mc(dst + q_off[q] + qg0 * J.q[q].gs, srcp, qgn * J.q[q].gs, bar_full + 8 * slot, mc_mask);
+          else bulk_g2s(dst + q_off[q], srcp, qgn * J.q[q].gs, bar_full + 8 * slot);
         }
         __syncwarp();
         if (++slot == WG_RING) { slot = 0; phase ^= 1; }
@@ -945,12 +961,11 @@ __global__ void __launch_bounds__(192, 1) tc_wgrad_kernel(const WgArgs A) {
   } else if (warp == 5) {
     if (elect_one()) {
       uint32_t slot = 0, phase = 0, accum = 0;
-      // loop-invariant descriptor pieces
       uint32_t qgs[3], qn_idesc[3], qtm[3];
-      for (int p = 0; p < 3; ++p) {
-        qgs[p] = p < J.n_parts ? J.q[p].gs : 0;
-        qn_idesc[p] = idesc_bf16(128, p < J.n_parts ? J.q[p].n : 16, 1, 1);
-        qtm[p] = tmem + (p < J.n_parts ? J.q[p].tm_col : 0);
+      for (int q = 0; q < 3; ++q) {
+        qgs[q] = q < J.n_parts ? J.q[q].gs : 0;
+        qn_idesc[q] = idesc_bf16(128, q < J.n_parts ? J.q[q].n : 16, 1, 1);
+        qtm[q] = tmem + (q < J.n_parts ? J.q[q].tm_col : 0);
       }
       const int n_parts = J.n_parts;
       for (int t = t0; t < t1; ++t)
@@ -962,11 +977,12 @@ __global__ void __launch_bounds__(192, 1) tc_wgrad_kernel(const WgArgs A) {
           for (int ks = 0; ks < WG_GROUPS / 2; ++ks) {
             const uint64_t pd = desc_mnmajor(src + ks * 4096, 2048);
 #pragma unroll
-            for (int p = 0; p < 3; ++p)
-              if (p < n_parts) umma(qtm[p], pd, desc_mnmajor(src + q_off[p] + ks * 2 * qgs[p], qgs[p]), qn_idesc[p], accum);
+            for (int q = 0; q < 3; ++q)
+              if (q < n_parts) umma(qtm[q], pd, desc_mnmajor(src + q_off[q] + ks * 2 * qgs[q], qgs[q]), qn_idesc[q], accum);
             accum = 1;
           }
-          umma_commit(bar_empty + 8 * slot);
+          if (shared) umma_commit_mc(bar_empty + 8 * slot, mc_mask);   // the slot is free once BOTH consumers are done
+          else umma_commit(bar_empty + 8 * slot);
           if (++slot == WG_RING) { slot = 0; phase ^= 1; }
         }
       umma_commit(bar_done);
@@ -992,20 +1008,33 @@ __global__ void __launch_bounds__(192, 1) tc_wgrad_kernel(const WgArgs A) {
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 5) tmem_dealloc(tmem, 512);
+  if (warp == 5 && active) tmem_dealloc(tmem, 512);
+  cluster_sync_all();   // neither CTA leaves while the other may still signal its barriers
 }
 
 struct WgPlan { std::vector<WgJob> jobs; int n_ctas = 0; };
 
+// Job pairs (entry 2p = cluster rank 0, 2p+1 = rank 1).  Cluster counts are proportional to the bytes a pair streams per
+// ray (the kernel is memory-bound) and sum to 148 = one 2-CTA cluster per SM pair:
+//   7 x {15,15,15,14,14,14,14} (256-wide layers + fc_feature, 136 KB/ray) + 16 (layers1.0, 152 KB) + 9 (layers0.0, 88 KB)
+//   + 7 (fc_density, 68 KB) + 11 (rgb_layers.0, 104 KB) + 4 (fc_rgb, 36 KB)
 WgPlan build_wg_plan() {
   WgPlan P;
+  int n_clusters = 0;
   auto part = [](int ws, uint32_t off, uint32_t gs, int n, int tm) { WgPart q{}; q.ws = (uint8_t)ws; q.slot_off = off; q.gs = gs; q.n = (uint16_t)n; q.tm_col = (uint16_t)tm; return q; };
   auto seg = [](int param, int offset, int sm, int sn, int tm, int count) { WgSeg s{}; s.param = param; s.offset = offset; s.stride_m = sm; s.stride_n = sn; s.tm_col = (uint16_t)tm; s.count = (uint16_t)count; return s; };
-  auto push = [&](WgJob J, int splits) { J.splits = (uint16_t)splits; J.cta0 = (uint16_t)P.n_ctas; P.n_ctas += splits; P.jobs.push_back(J); };
-  // split counts proportional to the bytes each job streams per ray (memory-bound), summing to 2 x 148 CTAs:
-  // 17 x 14 (104 KB/ray) + 2 x 16 (layers1.0, 120 KB) + 2 x 7 (layers0.0, 56 KB) + 3 x 4 (heads, 36 KB) = 296
-  const int BIG = 14, BIG4 = 16, MID = 7, SMALL = 4;
-  for (int L = 0; L < 8; ++L)
+  auto push_pair = [&](WgJob J0, WgJob J1, int shared, int clusters) {
+    J0.shared = J1.shared = (uint8_t)shared;
+    J0.splits = J1.splits = (uint16_t)clusters;
+    J0.cl0 = J1.cl0 = (uint16_t)n_clusters;
+    n_clusters += clusters;
+    P.jobs.push_back(J0);
+    P.jobs.push_back(J1);
+  };
+  int big_i = 0;
+  const int big_clusters[7] = {15, 15, 15, 14, 14, 14, 14};
+  for (int L = 0; L < 8; ++L) {
+    WgJob H[2];
     for (int h = 0; h < 2; ++h) {
       WgJob J{};
       const int wp = P_L0 + 2 * L;
@@ -1017,7 +1046,6 @@ WgPlan build_wg_plan() {
         J.n_segs = 2;
         J.seg[0] = seg(wp, 128 * h * 63, 63, 1, 0, 63);
         J.seg[1] = seg(wp + 1, 128 * h, 1, 1, 64 + 27, 1);
-        push(J, MID);
       } else if (L == 4) {
         J.n_parts = 3;
         J.q[0] = part(0, FW_H + 3 * 65536u, 4096, 256, 0);
@@ -1027,7 +1055,6 @@ WgPlan build_wg_plan() {
         J.seg[0] = seg(wp, 128 * h * 319, 319, 1, 0, 256);
         J.seg[1] = seg(wp, 128 * h * 319 + 256, 319, 1, 256, 63);
         J.seg[2] = seg(wp + 1, 128 * h, 1, 1, 320 + 27, 1);
-        push(J, BIG4);
       } else {
         J.n_parts = 2;
         J.q[0] = part(0, FW_H + (uint32_t)(L - 1) * 65536u, 4096, 256, 0);
@@ -1035,21 +1062,40 @@ WgPlan build_wg_plan() {
         J.n_segs = 2;
         J.seg[0] = seg(wp, 128 * h * 256, 256, 1, 0, 256);
         J.seg[1] = seg(wp + 1, 128 * h, 1, 1, 256 + 27, 1);
-        push(J, BIG);
       }
+      H[h] = J;
     }
-  for (int h = 0; h < 2; ++h) {  // fc_feature
-    WgJob J{};
-    J.p_ws = 1; J.p_slot_off = BW_DYFEAT; J.p_gs = 4096; J.p_col0 = 128 * h;
-    J.n_parts = 2;
-    J.q[0] = part(0, FW_H + 7 * 65536u, 4096, 256, 0);
-    J.q[1] = part(0, FW_AUX, 512, 32, 256);
-    J.n_segs = 2;
-    J.seg[0] = seg(P_FEAT, 128 * h * 256, 256, 1, 0, 256);
-    J.seg[1] = seg(P_FEAT + 1, 128 * h, 1, 1, 256 + 27, 1);
-    push(J, BIG);
+    push_pair(H[0], H[1], 1, L == 0 ? 9 : (L == 4 ? 16 : big_clusters[big_i++]));
   }
-  {  // rgb_layers.0: input [feat(256), dir_enc(27)]
+  {  // fc_feature
+    WgJob H[2];
+    for (int h = 0; h < 2; ++h) {
+      WgJob J{};
+      J.p_ws = 1; J.p_slot_off = BW_DYFEAT; J.p_gs = 4096; J.p_col0 = 128 * h;
+      J.n_parts = 2;
+      J.q[0] = part(0, FW_H + 7 * 65536u, 4096, 256, 0);
+      J.q[1] = part(0, FW_AUX, 512, 32, 256);
+      J.n_segs = 2;
+      J.seg[0] = seg(P_FEAT, 128 * h * 256, 256, 1, 0, 256);
+      J.seg[1] = seg(P_FEAT + 1, 128 * h, 1, 1, 256 + 27, 1);
+      H[h] = J;
+    }
+    push_pair(H[0], H[1], 1, big_clusters[big_i++]);
+  }
+  {  // fc_density weight: sum_s H7[s][m] * d_raw_den[s]
+    WgJob H[2];
+    for (int h = 0; h < 2; ++h) {
+      WgJob J{};
+      J.p_ws = 0; J.p_slot_off = FW_H + 7 * 65536u; J.p_gs = 4096; J.p_col0 = 128 * h;
+      J.n_parts = 1;
+      J.q[0] = part(1, BW_DSMALL, 256, 16, 0);
+      J.n_segs = 1;
+      J.seg[0] = seg(P_DEN, 128 * h, 1, 1, 3, 1);
+      H[h] = J;
+    }
+    push_pair(H[0], H[1], 1, 7);
+  }
+  {  // rgb_layers.0: input [feat(256), dir_enc(27)]; one 128-row block, the two ranks split the rays
     WgJob J{};
     J.p_ws = 1; J.p_slot_off = BW_DYRGB0; J.p_gs = 2048; J.p_col0 = 0;
     J.n_parts = 2;
@@ -1059,16 +1105,7 @@ WgPlan build_wg_plan() {
     J.seg[0] = seg(P_RGB0, 0, 283, 1, 0, 256);
     J.seg[1] = seg(P_RGB0, 256, 283, 1, 256, 27);
     J.seg[2] = seg(P_RGB0 + 1, 0, 1, 1, 256 + 27, 1);
-    push(J, BIG);
-  }
-  for (int h = 0; h < 2; ++h) {  // fc_density weight: sum_s H7[s][m] * d_raw_den[s]
-    WgJob J{};
-    J.p_ws = 0; J.p_slot_off = FW_H + 7 * 65536u; J.p_gs = 4096; J.p_col0 = 128 * h;
-    J.n_parts = 1;
-    J.q[0] = part(1, BW_DSMALL, 256, 16, 0);
-    J.n_segs = 1;
-    J.seg[0] = seg(P_DEN, 128 * h, 1, 1, 3, 1);
-    push(J, SMALL);
+    push_pair(J, J, 0, 11);
   }
   {  // fc_rgb weight (3,128): sum_s Hc[s][m] * d_raw_rgb[s][c]
     WgJob J{};
@@ -1077,8 +1114,9 @@ WgPlan build_wg_plan() {
     J.q[0] = part(1, BW_DSMALL, 256, 16, 0);
     J.n_segs = 1;
     J.seg[0] = seg(P_RGB, 0, 1, 128, 0, 3);
-    push(J, SMALL);
+    push_pair(J, J, 0, 4);
   }
+  P.n_ctas = 2 * n_clusters;
   return P;
 }
 const WgPlan &wg_plan() {
