@@ -233,8 +233,11 @@ int nnb_photometric_bwd(const float *rgb1, const float *rgb2, const uint8_t *val
 
 /* Loss.comp_closest_pts_idx_with_split: model/losses.py:129-144.  src (n_src,3), dst (n_dst,3).
  * idx[i] = first argmin_j of sqrt(sum_c (src_ic - dst_jc)^2) evaluated in fp32 like the reference.
- * dist (n_src,) = that minimum distance (may be NULL).  workspace: nnb_chamfer_workspace_bytes(n_src). */
-size_t nnb_chamfer_workspace_bytes(int n_src);
+ * dist (n_src,) = that minimum distance (may be NULL).  workspace: nnb_chamfer_workspace_bytes(n_src, n_dst)
+ * (bounds + the bf16 operand images of the tensor-core screening pass, 64 B per point). */
+size_t nnb_chamfer_workspace_bytes(int n_src, int n_dst);
+/* test hook: 1 = screening pass on the CUDA cores instead of tcgen05 (returns the previous setting) */
+int nnb_debug_chamfer_pass1(int cuda_cores);
 int nnb_chamfer_nn(const float *src, int n_src, const float *dst, int n_dst, int64_t *idx, float *dist, void *workspace,
                    size_t workspace_bytes, void *stream);
 /* Loss.comp_point_point_error: model/losses.py:145-150.  loss = mean_i ||X_i - Y[idx_i]||. */

@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libnope_nerf_b200.so")
-SOURCES = ["cabi.cu", "pose.cu", "raygen.cu", "composite.cu", "render.cu", "mlp_tc.cu", "losses.cu", "reproj.cu", "chamfer.cu"]
+SOURCES = ["cabi.cu", "pose.cu", "raygen.cu", "composite.cu", "render.cu", "mlp_tc.cu", "losses.cu", "reproj.cu", "chamfer.cu", "chamfer_tc.cu"]
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
          "--expt-relaxed-constexpr"]
 

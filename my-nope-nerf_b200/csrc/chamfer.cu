@@ -12,23 +12,31 @@
 // merged with an atomicMin on (bits(s) << 32 | j), so the first index wins exactly as in torch.argmin.
 #include "nnb_common.cuh"
 
+// chamfer_tc.cu
+size_t nnb_chamfer_tc_workspace_bytes(int n_src, int n_dst);
+size_t nnb_chamfer_tc_norm2_offset(int n_src, int n_dst);
+int nnb_chamfer_tc_bound(const float *src, int n_src, const float *dst, int n_dst, unsigned int *bound, unsigned int *stats, void *workspace,
+                         cudaStream_t s);
+
 #define CH_THREADS 128
 #define CH_SPT 4      // sources per thread
 #define CH_TILE 1024  // destination points per shared-memory tile
 
-// Two passes over the (source, destination) pairs, both with the expanded form  a = |q|^2 - 2 s.q  (three FMAs, |q|^2
-// rides in tile[].w) so that the hot loops are branch-free:
-//   pass 1 (EXACT = false): running minimum of a per source -> bound[s] = min_j (a_j + |s|^2)  (atomicMin over splits)
-//   pass 2 (EXACT = true) : pairs with a < (bound - |s|^2) + margin are re-evaluated exactly (direct differences in
-//                           the reference's op order); margin = 1e-6 (|s|^2 + 2 max|q|^2 + bound) covers twice the rounding
-//                           error of the expanded form (<= 4 eps (|s|^2 + 2|q|^2), eps = 6e-8) plus sqrt ties, so no pair the
-//                           reference could select is ever screened out and indices stay bit-exact.  Typically 1-3 pairs per
-//                           source survive, so the exact path is cold.
+// Two passes over the (source, destination) pairs, both with the expanded form  a = |q|^2 - 2 s.q :
+//   pass 1: bound[s] ~ min_j d2(s, j).  Production: tcgen05 GEMM with a min epilogue (chamfer_tc.cu, error
+//           <= 8e-6 (|s-c|^2 + 2 max|q-c|^2)).  EXACT = false below is the CUDA-core version of the same pass, kept as the
+//           probe the tensor-core pass is tested against (tests/test_gpu_losses.py).
+//   pass 2 (EXACT = true): three FMAs per pair (|q|^2 rides in tile[].w), branch-free; pairs with
+//           a < (bound - |s|^2) + margin are re-evaluated exactly (direct differences in the reference's op order).
+//           margin = 1e-6 (|s|^2 + 2 max|q|^2 + bound) [this pass's own screen: <= 4 eps (|s|^2 + 2|q|^2), eps = 6e-8, plus
+//           sqrt ties] + the pass-1 error term, so no pair the reference could select is screened out and indices stay
+//           bit-exact.  Typically a handful of pairs per source survive, so the exact path is cold.
 template <bool EXACT>
 __global__ void __launch_bounds__(CH_THREADS) chamfer_nn_kernel(const float *__restrict__ src, int n_src,
                                                                 const float *__restrict__ dst, int n_dst, int dst_per_block,
                                                                 unsigned int *__restrict__ bound, unsigned int *__restrict__ qqmax_g,
-                                                                unsigned long long *__restrict__ best) {
+                                                                unsigned long long *__restrict__ best,
+                                                                const float *__restrict__ tc_norm2, const unsigned int *__restrict__ tc_stats) {
   __shared__ float4 tile[CH_TILE];
   __shared__ float qqmax_s[CH_THREADS / 32];
   const int s0 = (blockIdx.x * CH_THREADS + threadIdx.x) * CH_SPT;
@@ -43,7 +51,9 @@ __global__ void __launch_bounds__(CH_THREADS) chamfer_nn_kernel(const float *__r
     smin[k] = INFINITY; amin[k] = INFINITY; jbest[k] = 0x7fffffff;
     if (EXACT) {
       const float b = __uint_as_float(bound[s]);
-      thr[k] = (b - ss[k]) + 1e-6f * (ss[k] + 2.f * __uint_as_float(*qqmax_g) + b);
+      float margin = 1e-6f * (ss[k] + 2.f * __uint_as_float(*qqmax_g) + b);
+      if (tc_norm2) margin += 8e-6f * (tc_norm2[s] + 2.f * __uint_as_float(tc_stats[0]) + b);
+      thr[k] = (b - ss[k]) + margin;
     } else {
       thr[k] = 0.f;
     }
@@ -127,9 +137,23 @@ __global__ void __launch_bounds__(CH_THREADS) chamfer_nn_kernel(const float *__r
   }
 }
 
-__global__ void chamfer_unpack_kernel(const unsigned long long *best, int n, int64_t *idx, float *__restrict__ dist) {
+// Also the safety net of the screen: a source for which pass 2 found no pair (its bound was violated; never seen, would
+// need a pass-1 error beyond the margin) is searched exhaustively here instead of returning garbage.
+__global__ void chamfer_unpack_kernel(const unsigned long long *best, int n, int64_t *idx, float *__restrict__ dist,
+                                      const float *__restrict__ src, const float *__restrict__ dst, int n_dst) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const unsigned long long k = best[i];
+    unsigned long long k = best[i];
+    if (k == ~0ull) {
+      const float sx = src[3 * i], sy = src[3 * i + 1], sz = src[3 * i + 2];
+      float smin = INFINITY;
+      unsigned int jb = 0;
+      for (int j = 0; j < n_dst; ++j) {
+        const float dx = __fsub_rn(sx, dst[3 * j]), dy = __fsub_rn(sy, dst[3 * j + 1]), dz = __fsub_rn(sz, dst[3 * j + 2]);
+        const float d = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
+        if (d < smin) { smin = d; jb = j; }
+      }
+      k = ((unsigned long long)__float_as_uint(smin) << 32) | jb;
+    }
     if (dist) dist[i] = __uint_as_float((unsigned int)(k >> 32));
     idx[i] = (int64_t)(unsigned int)(k & 0xffffffffull);  // written last: idx may alias best
   }
@@ -166,16 +190,30 @@ __global__ void chamfer_err_bwd_kernel(const float *__restrict__ X, int n, const
 
 extern "C" {
 
-size_t nnb_chamfer_workspace_bytes(int n_src) { return ((size_t)(n_src > 0 ? n_src : 0) + 4) * sizeof(unsigned int); }
+size_t nnb_chamfer_workspace_bytes(int n_src, int n_dst) {
+  if (n_src < 0) n_src = 0;
+  if (n_dst < 0) n_dst = 0;
+  return (((size_t)n_src + 4) * sizeof(unsigned int) + 255) / 256 * 256 + nnb_chamfer_tc_workspace_bytes(n_src, n_dst);
+}
+
+static int g_chamfer_pass1_cuda_cores = 0;
+// test hook: 1 = run pass 1 on the CUDA cores (the probe the tensor-core pass is checked against)
+int nnb_debug_chamfer_pass1(int cuda_cores) {
+  const int old = g_chamfer_pass1_cuda_cores;
+  g_chamfer_pass1_cuda_cores = cuda_cores;
+  return old;
+}
 
 // `idx` (n_src int64) doubles as the 64-bit packed-key scratch; `workspace` holds the pass-1 bounds and max |q|^2.
 int nnb_chamfer_nn(const float *src, int n_src, const float *dst, int n_dst, int64_t *idx, float *dist, void *workspace,
                    size_t workspace_bytes, void *stream) {
   if (!src || !dst || !idx || !workspace || n_src <= 0 || n_dst <= 0) return NNB_ERR_BAD_ARG;
-  if (workspace_bytes < nnb_chamfer_workspace_bytes(n_src)) return NNB_ERR_WORKSPACE;
+  if (workspace_bytes < nnb_chamfer_workspace_bytes(n_src, n_dst)) return NNB_ERR_WORKSPACE;
   cudaStream_t s = nnb_stream(stream);
   unsigned long long *best = reinterpret_cast<unsigned long long *>(idx);
-  unsigned int *bound = static_cast<unsigned int *>(workspace), *qqmax = bound + n_src;
+  unsigned int *bound = static_cast<unsigned int *>(workspace), *qqmax = bound + n_src, *tc_stats = qqmax + 1;
+  uint8_t *tc_ws = static_cast<uint8_t *>(workspace) + (((size_t)n_src + 4) * sizeof(unsigned int) + 255) / 256 * 256;
+  const float *tc_norm2 = reinterpret_cast<const float *>(tc_ws + nnb_chamfer_tc_norm2_offset(n_src, n_dst));
   NNB_CUDA(cudaMemsetAsync(bound, 0x7f, (size_t)n_src * sizeof(unsigned int), s));
   NNB_CUDA(cudaMemsetAsync(qqmax, 0, sizeof(unsigned int), s));
   NNB_CUDA(cudaMemsetAsync(best, 0xff, (size_t)n_src * sizeof(unsigned long long), s));
@@ -186,12 +224,18 @@ int nnb_chamfer_nn(const float *src, int n_src, const float *dst, int n_dst, int
   int gy = want < 1 ? 1 : (want > max_split ? max_split : want);
   int per = nnb_cdiv(nnb_cdiv(n_dst, gy), CH_TILE) * CH_TILE;
   gy = nnb_cdiv(n_dst, per);
-  chamfer_nn_kernel<false><<<dim3(gx, gy), CH_THREADS, 0, s>>>(src, n_src, dst, n_dst, per, bound, qqmax, best);
-  NNB_CHECK_LAUNCH();
-  chamfer_nn_kernel<true><<<dim3(gx, gy), CH_THREADS, 0, s>>>(src, n_src, dst, n_dst, per, bound, qqmax, best);
+  if (g_chamfer_pass1_cuda_cores) {
+    chamfer_nn_kernel<false><<<dim3(gx, gy), CH_THREADS, 0, s>>>(src, n_src, dst, n_dst, per, bound, qqmax, best, nullptr, nullptr);
+    NNB_CHECK_LAUNCH();
+    chamfer_nn_kernel<true><<<dim3(gx, gy), CH_THREADS, 0, s>>>(src, n_src, dst, n_dst, per, bound, qqmax, best, nullptr, nullptr);
+  } else {
+    const int rc = nnb_chamfer_tc_bound(src, n_src, dst, n_dst, bound, tc_stats, tc_ws, s);
+    if (rc) return rc;
+    chamfer_nn_kernel<true><<<dim3(gx, gy), CH_THREADS, 0, s>>>(src, n_src, dst, n_dst, per, bound, tc_stats + 1, best, tc_norm2, tc_stats);
+  }
   NNB_CHECK_LAUNCH();
   int g = nnb_cdiv(n_src, 256);
-  chamfer_unpack_kernel<<<g, 256, 0, s>>>(best, n_src, idx, dist);
+  chamfer_unpack_kernel<<<g, 256, 0, s>>>(best, n_src, idx, dist, src, dst, n_dst);
   NNB_CHECK_LAUNCH();
   return 0;
 }

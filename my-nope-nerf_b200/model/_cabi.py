@@ -73,7 +73,8 @@ SIGNATURES = {
     "nnb_reproj_bwd": [_p, _i, _i, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p],
     "nnb_photometric_fwd": [_p, _p, _p, _i, _p, _p],
     "nnb_photometric_bwd": [_p, _p, _p, _i, _p, _p, _p, _p, _p],
-    "nnb_chamfer_workspace_bytes": [_i],
+    "nnb_chamfer_workspace_bytes": [_i, _i],
+    "nnb_debug_chamfer_pass1": [_i],
     "nnb_chamfer_nn": [_p, _i, _p, _i, _p, _p, _p, C.c_size_t, _p],
     "nnb_chamfer_err_fwd": [_p, _i, _p, _p, _p, _p],
     "nnb_chamfer_err_bwd": [_p, _i, _p, _p, _p, _p, _p, _p],

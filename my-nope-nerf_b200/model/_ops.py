@@ -448,7 +448,7 @@ def chamfer_nn(src, dst, want_dist=False):
     src, dst = f32(src.detach()).reshape(-1, 3), f32(dst.detach()).reshape(-1, 3)
     idx = _new(src, src.shape[0], dtype=torch.int64)
     dist = _new(src, src.shape[0]) if want_dist else None
-    nb = int(K.lib().nnb_chamfer_workspace_bytes(src.shape[0]))
+    nb = int(K.lib().nnb_chamfer_workspace_bytes(src.shape[0], dst.shape[0]))
     ws = _workspace(src.device, nb, "chamfer")
     call("nnb_chamfer_nn", ptr(src), src.shape[0], ptr(dst), dst.shape[0], ptr(idx), ptr(dist), ptr(ws), nb, stream())
     return (idx, dist) if want_dist else idx

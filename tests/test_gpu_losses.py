@@ -114,8 +114,17 @@ def test_chamfer_vs_reference(golden):
     assert torch.isfinite(Xr.grad).all()
 
 
+@pytest.fixture(params=["tcgen05", "cuda_cores"])
+def chamfer_pass1(request):
+    """Screening pass on the tensor cores (production) or on the CUDA cores (the probe it is checked against)."""
+    from model import _cabi as K
+    old = K.lib().nnb_debug_chamfer_pass1(1 if request.param == "cuda_cores" else 0)
+    yield request.param
+    K.lib().nnb_debug_chamfer_pass1(old)
+
+
 @pytest.mark.parametrize("n,m", [(1, 1), (5, 4099), (3000, 2000), (28830, 28830)])
-def test_chamfer_indices_bit_exact_vs_oracle(n, m):
+def test_chamfer_indices_bit_exact_vs_oracle(n, m, chamfer_pass1):
     from model import _ops
     from oracle import nope_oracle as O
     g = torch.Generator().manual_seed(n + m)
@@ -131,7 +140,30 @@ def test_chamfer_indices_bit_exact_vs_oracle(n, m):
     assert_close(dist[sub], wd, 1e-6, 1e-7, 'nn distance')
 
 
-def test_chamfer_indices_far_from_origin():
+def test_chamfer_depth_clouds_both_paths_agree(chamfer_pass1):
+    """Back-projected depth clouds at training size (two smooth surfaces 28,830 points each, a small rigid offset
+    apart -- dense near-ties between neighbouring pixels): every index and distance of the full problem must agree
+    with the brute-force oracle on a slice and be identical between the two screening passes."""
+    from model import _ops, _cabi as K
+    from oracle import nope_oracle as O
+    g = torch.Generator().manual_seed(3)
+    v, u = torch.meshgrid(torch.linspace(-0.75, 0.75, 155), torch.linspace(-1, 1, 186), indexing="ij")
+    z = 2.0 + 0.3 * torch.sin(3 * u) * torch.cos(2 * v)
+    a = torch.stack([u * z, v * z, -z], -1).reshape(-1, 3)
+    b = a + torch.tensor([0.013, -0.007, 0.02]) + 1e-3 * torch.randn(a.shape, generator=g)
+    idx, dist = _ops.chamfer_nn(a.to(dev()), b.to(dev()), want_dist=True)
+    sub = slice(11000, 11000 + 4096)
+    want = O.nearest_idx(a[sub].t().contiguous(), b.t().contiguous(), slice_len=256)
+    assert torch.equal(idx.cpu()[sub], want)
+    old = K.lib().nnb_debug_chamfer_pass1(1)
+    try:
+        idx2, dist2 = _ops.chamfer_nn(a.to(dev()), b.to(dev()), want_dist=True)
+    finally:
+        K.lib().nnb_debug_chamfer_pass1(old)
+    assert torch.equal(idx, idx2) and torch.equal(dist, dist2)
+
+
+def test_chamfer_indices_far_from_origin(chamfer_pass1):
     """Clouds offset far from the origin: the expanded |q|^2 - 2 s.q screen loses ~7 digits to cancellation there;
     the exact re-check must keep the indices bit-exact."""
     from model import _ops

@@ -1,0 +1,39 @@
+"""Where does a training step's wall time go?  CPU launch time vs GPU busy time, via torch.profiler."""
+import os, sys, json
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "my-nope-nerf_b200")):
+    sys.path.insert(0, p)
+import torch
+import bench, synthetic_scene as syn
+from model import parallel
+dev = torch.device("cuda:0")
+dp = parallel.DataParallelContext(0, 1)
+cfg, scene, tr = bench.build_trainer(dev, 20, 4096, "bf16", dp)
+n = scene["n"]
+sched = cfg["training"]["scheduling_start"]
+batches = []
+for i in range(4):
+    b = syn.make_batch(scene, i, i + 1)
+    batches.append({k: (v.to(dev) if torch.is_tensor(v) and k not in ("img.idx", "img.ref_idxs") else v) for k, v in b.items()})
+for it in range(5):
+    tr.train_step(batches[it % 4], it=it, epoch=0, scheduling_start=sched)
+torch.cuda.synchronize()
+import time
+t0 = time.perf_counter()
+for it in range(20):
+    tr.train_step(batches[it % 4], it=it, epoch=0, scheduling_start=sched)
+t1 = time.perf_counter()
+torch.cuda.synchronize()
+t2 = time.perf_counter()
+print("cpu issue time per step %.3f ms; wall per step incl. drain %.3f ms" % ((t1 - t0) / 20 * 1e3, (t2 - t0) / 20 * 1e3))
+from torch.profiler import profile, ProfilerActivity
+with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
+    for it in range(3):
+        tr.train_step(batches[it % 4], it=it, epoch=0, scheduling_start=sched)
+    torch.cuda.synchronize()
+ev = prof.key_averages()
+rows = sorted(ev, key=lambda e: -e.self_cpu_time_total)[:25]
+for e in rows:
+    print("%-60s cpu %8.1f us  n=%d" % (e.key[:60], e.self_cpu_time_total / 3, e.count // 3))
+tot_cuda = sum(e.self_device_time_total for e in ev) / 3
+print("GPU kernel time per step: %.3f ms" % (tot_cuda / 1e3))
