@@ -236,7 +236,8 @@ int nnb_photometric_bwd(const float *rgb1, const float *rgb2, const uint8_t *val
  * dist (n_src,) = that minimum distance (may be NULL).  workspace: nnb_chamfer_workspace_bytes(n_src, n_dst)
  * (bounds + the bf16 operand images of the tensor-core screening pass, 64 B per point). */
 size_t nnb_chamfer_workspace_bytes(int n_src, int n_dst);
-/* test hook: 1 = screening pass on the CUDA cores instead of tcgen05 (returns the previous setting) */
+/* test hook: 0 = both sweeps on tcgen05 (default), 1 = both on the CUDA cores, 2 = tcgen05 screen + CUDA-core exact sweep
+ * (returns the previous setting) */
 int nnb_debug_chamfer_pass1(int cuda_cores);
 int nnb_chamfer_nn(const float *src, int n_src, const float *dst, int n_dst, int64_t *idx, float *dist, void *workspace,
                    size_t workspace_bytes, void *stream);

@@ -16,7 +16,7 @@
 size_t nnb_chamfer_tc_workspace_bytes(int n_src, int n_dst);
 size_t nnb_chamfer_tc_norm2_offset(int n_src, int n_dst);
 int nnb_chamfer_tc_bound(const float *src, int n_src, const float *dst, int n_dst, unsigned int *bound, unsigned int *stats, void *workspace,
-                         cudaStream_t s);
+                         unsigned long long *best_init, unsigned long long *best, cudaStream_t s);
 
 #define CH_THREADS 128
 #define CH_SPT 4      // sources per thread
@@ -197,7 +197,7 @@ size_t nnb_chamfer_workspace_bytes(int n_src, int n_dst) {
 }
 
 static int g_chamfer_pass1_cuda_cores = 0;
-// test hook: 1 = run pass 1 on the CUDA cores (the probe the tensor-core pass is checked against)
+// test hook: 0 = both passes on tcgen05 (production); 1 = both on the CUDA cores; 2 = tcgen05 screen + CUDA-core exact pass
 int nnb_debug_chamfer_pass1(int cuda_cores) {
   const int old = g_chamfer_pass1_cuda_cores;
   g_chamfer_pass1_cuda_cores = cuda_cores;
@@ -214,9 +214,11 @@ int nnb_chamfer_nn(const float *src, int n_src, const float *dst, int n_dst, int
   unsigned int *bound = static_cast<unsigned int *>(workspace), *qqmax = bound + n_src, *tc_stats = qqmax + 1;
   uint8_t *tc_ws = static_cast<uint8_t *>(workspace) + (((size_t)n_src + 4) * sizeof(unsigned int) + 255) / 256 * 256;
   const float *tc_norm2 = reinterpret_cast<const float *>(tc_ws + nnb_chamfer_tc_norm2_offset(n_src, n_dst));
-  NNB_CUDA(cudaMemsetAsync(bound, 0x7f, (size_t)n_src * sizeof(unsigned int), s));
-  NNB_CUDA(cudaMemsetAsync(qqmax, 0, sizeof(unsigned int), s));
-  NNB_CUDA(cudaMemsetAsync(best, 0xff, (size_t)n_src * sizeof(unsigned long long), s));
+  if (g_chamfer_pass1_cuda_cores == 1) {
+    NNB_CUDA(cudaMemsetAsync(bound, 0x7f, (size_t)n_src * sizeof(unsigned int), s));
+    NNB_CUDA(cudaMemsetAsync(qqmax, 0, sizeof(unsigned int), s));
+    NNB_CUDA(cudaMemsetAsync(best, 0xff, (size_t)n_src * sizeof(unsigned long long), s));
+  }
   const int gx = nnb_cdiv(n_src, CH_THREADS * CH_SPT);
   // split the destination range so that the grid covers the SMs a few times over
   int want = nnb_cdiv(nnb_sm_count() * 6, gx);
@@ -224,12 +226,15 @@ int nnb_chamfer_nn(const float *src, int n_src, const float *dst, int n_dst, int
   int gy = want < 1 ? 1 : (want > max_split ? max_split : want);
   int per = nnb_cdiv(nnb_cdiv(n_dst, gy), CH_TILE) * CH_TILE;
   gy = nnb_cdiv(n_dst, per);
-  if (g_chamfer_pass1_cuda_cores) {
+  if (g_chamfer_pass1_cuda_cores == 1) {
     chamfer_nn_kernel<false><<<dim3(gx, gy), CH_THREADS, 0, s>>>(src, n_src, dst, n_dst, per, bound, qqmax, best, nullptr, nullptr);
     NNB_CHECK_LAUNCH();
     chamfer_nn_kernel<true><<<dim3(gx, gy), CH_THREADS, 0, s>>>(src, n_src, dst, n_dst, per, bound, qqmax, best, nullptr, nullptr);
+  } else if (g_chamfer_pass1_cuda_cores == 0) {
+    const int rc = nnb_chamfer_tc_bound(src, n_src, dst, n_dst, bound, tc_stats, tc_ws, best, best, s);
+    if (rc) return rc;
   } else {
-    const int rc = nnb_chamfer_tc_bound(src, n_src, dst, n_dst, bound, tc_stats, tc_ws, s);
+    const int rc = nnb_chamfer_tc_bound(src, n_src, dst, n_dst, bound, tc_stats, tc_ws, best, nullptr, s);
     if (rc) return rc;
     chamfer_nn_kernel<true><<<dim3(gx, gy), CH_THREADS, 0, s>>>(src, n_src, dst, n_dst, per, bound, tc_stats + 1, best, tc_norm2, tc_stats);
   }

@@ -114,11 +114,11 @@ def test_chamfer_vs_reference(golden):
     assert torch.isfinite(Xr.grad).all()
 
 
-@pytest.fixture(params=["tcgen05", "cuda_cores"])
+@pytest.fixture(params=["tcgen05", "cuda_cores", "mixed"])
 def chamfer_pass1(request):
     """Screening pass on the tensor cores (production) or on the CUDA cores (the probe it is checked against)."""
     from model import _cabi as K
-    old = K.lib().nnb_debug_chamfer_pass1(1 if request.param == "cuda_cores" else 0)
+    old = K.lib().nnb_debug_chamfer_pass1({"tcgen05": 0, "cuda_cores": 1, "mixed": 2}[request.param])
     yield request.param
     K.lib().nnb_debug_chamfer_pass1(old)
 

@@ -11,7 +11,7 @@ g = torch.Generator().manual_seed(0)
 a = torch.rand(P, 3, generator=g)
 a = torch.stack([(a[:, 0] * 2 - 1) * 2, (a[:, 1] * 1.5 - 0.75) * 2, -(1.5 + a[:, 2])], 1).to(dev)
 b = (a + 0.01 * torch.randn(P, 3, generator=g).to(dev))[torch.randperm(P, generator=g).to(dev)]
-for mode, name in ((0, "tcgen05 pass 1"), (1, "cuda-core pass 1")):
+for mode, name in ((0, "tcgen05 both"), (2, "tcgen05 + cc exact"), (1, "cuda cores both")):
     K.lib().nnb_debug_chamfer_pass1(mode)
     for _ in range(3):
         idx, d = _ops.chamfer_nn(a, b, want_dist=True)
