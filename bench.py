@@ -225,7 +225,7 @@ def run_b200(args):
                                % (n, RAYS_PER_GPU),
                    "global_rays": rays_global, "parallelism": "dp%d" % world, "precision": args.precision,
                    "l2_policy": "working set per step (activation workspace %.1f GB) exceeds the 126 MB L2; no explicit flush"
-                                % (13.0e3 * RAYS_PER_GPU * 128 / 1e9 if args.precision == "fp32" else 0.0)},
+                                % (13.0e3 * RAYS_PER_GPU * 128 / 1e9 if args.precision == "fp32" else 1.31e6 * RAYS_PER_GPU / 1e9)},
         "clocks": sampler.result(),
         "e2e": {"value": rays_per_s_e2e, "unit": "rays/s", "h2d_bytes_per_step": batch_bytes(host_batches[0]),
                 "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps},
@@ -237,6 +237,8 @@ def run_b200(args):
                      "algorithmic_flop_per_step": FLOP_PER_RAY_TRAIN * RAYS_PER_GPU},
         "stages_ms_per_step": {k: round(v, 4) for k, v in sorted(prof.items(), key=lambda kv: -kv[1])},
     }
+    if world == 1:
+        out["extras"] = extras(dev, cfg, scene, tr, args.precision)
     if dp.rank == 0 and not args.no_cpu_baseline and world == 1:
         out["cpu_baseline"] = cpu_baseline(max_seconds=25.0)
     if dp.rank == 0:
@@ -244,6 +246,48 @@ def run_b200(args):
     if world > 1:
         torch.distributed.barrier()
         torch.distributed.destroy_process_group()
+
+
+def extras(dev, cfg, scene, tr, precision):
+    """The two other BASELINE.json workloads that fit one GPU, device-timed (reported next to the headline, not part of it):
+    cfg4 = one full 375 x 1242 frame through Extract_Images.render_frame (ray generation + fused forward, 100,000-pixel
+    chunks as the reference's extractor uses); cfg5 = Chamfer nearest neighbours on 100,000-point clouds, one direction."""
+    import model as mdl
+    from model import _ops
+    out = {}
+
+    def med_ms(fn, reps):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(reps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1))
+        return sorted(ts)[len(ts) // 2]
+
+    h, w = scene["h"], scene["w"]
+    ex = mdl.Extract_Images(tr.model.renderer, {"extract_images": {"resolution": [h, w]}}, device=dev, render_type=tr.rendering_technique)
+    cam, scl = scene["camera_mat"].to(dev).reshape(1, 4, 4), torch.eye(4, device=dev).reshape(1, 4, 4)
+    with torch.no_grad():
+        wm = _ops.Mat4Inverse.apply(tr.pose_param_net(0)).unsqueeze(0)
+    tr.model.eval()
+    ms = med_ms(lambda: ex.render_frame(cam, wm, scl, h, w), 5)
+    tr.model.train()
+    out["cfg4_render_ms_per_frame"] = ms
+    out["cfg4_render_tflops"] = 151_912_448 * h * w / ms / 1e9
+    g = torch.Generator().manual_seed(7)
+    a = torch.rand(100000, 3, generator=g)
+    a = torch.stack([(a[:, 0] * 2 - 1) * 2, (a[:, 1] * 1.5 - 0.75) * 2, -(1.5 + a[:, 2])], 1).to(dev)
+    b = (a + 0.01 * torch.randn(100000, 3, generator=g).to(dev))[torch.randperm(100000, generator=g).to(dev)]
+    ms = med_ms(lambda: _ops.chamfer_nn(a, b), 5)
+    out["cfg5_chamfer_100k_ms_per_direction"] = ms
+    out["cfg5_chamfer_gpairs_per_s"] = 1e10 / ms / 1e6
+    return out
 
 
 # ---------------------------------------------------------------------------------------------------------------

@@ -24,6 +24,8 @@ class Loss(nn.Module):
         self.depth_loss_type = cfg['depth_loss_type']
         self.cfg = cfg
         self.check_nan = True
+        # data-parallel context (set by Trainer): the Chamfer SOURCE points are sharded across ranks
+        self.dp = None
 
     # -- individual terms (reference method names) ----------------------------------------------
     def get_rgb_full_loss(self, rgb_values, rgb_gt, rgb_loss_type='l2'):
@@ -51,11 +53,25 @@ class Loss(nn.Module):
         X, Y = Xt.t().contiguous(), Yt.t().contiguous()
         return _ops.ChamferErr.apply(X, Y, _ops.chamfer_nn(X, Y))
 
+    def _point_point_error_rows(self, X, Y):
+        """mean_i |X_i - Y[nn(i)]| over the rows of X (P,3).  With world_size G > 1 this rank searches only its slice
+        of the source rows (both clouds stay whole on every rank) and returns G * (its partial sum) / P: the gradient
+        allreduce AVERAGES over ranks, so the average of these terms -- value and gradient -- is the full-batch one."""
+        dp = self.dp
+        if dp is None or dp.world_size == 1:
+            return _ops.ChamferErr.apply(X, Y, _ops.chamfer_nn(X, Y))
+        n = X.shape[0]
+        lo, hi = dp.shard(n)
+        if hi == lo:
+            return X.sum() * 0.0
+        Xs = X[lo:hi]
+        return _ops.ChamferErr.apply(Xs, Y, _ops.chamfer_nn(Xs, Y)) * (float(hi - lo) * dp.world_size / float(n))
+
     def get_pc_loss(self, Xt, Yt):
         if self.cfg['match_method'] != 'dense':
             raise ValueError("match_method %r" % (self.cfg['match_method'],))
         X, Y = Xt[0], Yt[0]  # (P,3) row-major: the layout the kernels want (the reference permutes to (3,P))
-        return _ops.ChamferErr.apply(X, Y, _ops.chamfer_nn(X, Y)) + _ops.ChamferErr.apply(Y, X, _ops.chamfer_nn(Y, X))
+        return self._point_point_error_rows(X, Y) + self._point_point_error_rows(Y, X)
 
     def get_rgb_s_loss(self, rgb1, rgb2, valid_points):
         if self.cfg['with_ssim']:

@@ -51,6 +51,7 @@ class Trainer(object):
         self.loss = Loss(cfg)
         # data-parallel context (world size 1 unless torch.distributed is initialised)
         self.dp = kwargs.get('dp') or parallel.DataParallelContext.from_env()
+        self.loss.dp = self.dp
         # test hooks: inject the ray choice / jitter instead of drawing them (parity tests)
         self.fixed_ray_idx = None
         self.fixed_noise = None

@@ -167,6 +167,40 @@ def _gloo_worker(rank, world, port, out_dir):
     assert torch.allclose(ps[0].grad, torch.full((3, 5), mean))
     assert torch.allclose(ps[1].grad, torch.arange(7.0) * mean)
     assert torch.allclose(ps[2].grad, torch.ones(2) / world)
+    # Chamfer with the SOURCE points sharded by rank: averaging the ranks' terms and gradients must give the
+    # one-rank loss and gradient.  The two kernels are replaced by torch stand-ins: this checks the host-side sharding.
+    from model import _ops, losses
+
+    class _Err(torch.autograd.Function):  # signature of _ops.ChamferErr
+        @staticmethod
+        def forward(ctx, X, Y, idx):
+            ctx.save_for_backward(X, Y, idx)
+            return (X - Y[idx]).norm(dim=1).mean()
+
+        @staticmethod
+        def backward(ctx, g):
+            X, Y, idx = ctx.saved_tensors
+            d = X - Y[idx]
+            u = d / d.norm(dim=1, keepdim=True).clamp_min(1e-30) * (g / X.shape[0])
+            return u, torch.zeros_like(Y).index_add_(0, idx, -u), None
+
+    _ops.chamfer_nn = lambda src, dst, want_dist=False: torch.cdist(src.detach(), dst.detach()).argmin(dim=1)
+    _ops.ChamferErr = _Err
+    g = torch.Generator().manual_seed(5)
+    X0, Y0 = torch.rand(1, 301, 3, generator=g), torch.rand(1, 257, 3, generator=g)
+    L = losses.Loss(syn.default_cfg()["training"])
+    Xf, Yf = X0.clone().requires_grad_(True), Y0.clone().requires_grad_(True)
+    full = L.get_pc_loss(Xf, Yf)
+    full.backward()
+    L.dp = dp
+    Xs, Ys = X0.clone().requires_grad_(True), Y0.clone().requires_grad_(True)
+    part = L.get_pc_loss(Xs, Ys)
+    part.backward()
+    red = torch.cat([part.detach().reshape(1), Xs.grad.reshape(-1), Ys.grad.reshape(-1)])
+    dist.all_reduce(red)
+    red /= world
+    want = torch.cat([full.detach().reshape(1), Xf.grad.reshape(-1), Yf.grad.reshape(-1)])
+    assert torch.allclose(red, want, rtol=1e-5, atol=1e-7), float((red - want).abs().max())
     open(os.path.join(out_dir, "ok%d" % rank), "w").write("ok")
     dist.destroy_process_group()
 

@@ -163,6 +163,29 @@ def test_chamfer_depth_clouds_both_paths_agree(chamfer_pass1):
     assert torch.equal(idx, idx2) and torch.equal(dist, dist2)
 
 
+def test_chamfer_source_sharding_matches_one_rank():
+    """Data-parallel Chamfer: every rank searches its slice of the source points.  Simulated here with the
+    rank contexts of a world of 3 on one GPU: the rank-average of losses and gradients equals the one-rank result."""
+    from model import parallel
+    L = _loss()
+    g = torch.Generator().manual_seed(9)
+    X0, Y0 = torch.rand(1, 3001, 3, generator=g).to(dev()), torch.rand(1, 2500, 3, generator=g).to(dev())
+    Xf, Yf = X0.clone().requires_grad_(True), Y0.clone().requires_grad_(True)
+    full = L.get_pc_loss(Xf, Yf)
+    full.backward()
+    world = 3
+    acc_l, acc_x, acc_y = 0.0, torch.zeros_like(X0), torch.zeros_like(Y0)
+    for rank in range(world):
+        L.dp = parallel.DataParallelContext(rank, world)
+        Xs, Ys = X0.clone().requires_grad_(True), Y0.clone().requires_grad_(True)
+        part = L.get_pc_loss(Xs, Ys)
+        part.backward()
+        acc_l, acc_x, acc_y = acc_l + part.detach() / world, acc_x + Xs.grad / world, acc_y + Ys.grad / world
+    assert_close(acc_l, full.detach(), 1e-5, 1e-7, "sharded chamfer loss")
+    assert_close(acc_x, Xf.grad, 1e-4, 1e-8, "sharded d X")
+    assert_close(acc_y, Yf.grad, 1e-4, 1e-8, "sharded d Y")
+
+
 def test_chamfer_indices_far_from_origin(chamfer_pass1):
     """Clouds offset far from the origin: the expanded |q|^2 - 2 s.q screen loses ~7 digits to cancellation there;
     the exact re-check must keep the indices bit-exact."""
