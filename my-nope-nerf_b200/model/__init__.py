@@ -15,4 +15,5 @@ from model.eval_pose_one_epoch import Trainer_pose
 from model.distortions import Learn_Distortion
 from model.losses import Loss, Loss_Eval
 from model.extracting_images import Extract_Images
+from model.optim import FlatAdam
 from model import parallel

@@ -479,6 +479,12 @@ def adam_step(param, grad, exp_avg, exp_avg_sq, lr, beta1, beta2, eps, step):
          float(eps), int(step), stream())
 
 
+def adam_step_raw(param_ptr, grad_ptr, m_ptr, v_ptr, n, lr, beta1, beta2, eps, step):
+    """Same on raw device addresses (sub-ranges of the flat buffers of model/optim.py)."""
+    call("nnb_adam_step", C.c_void_p(param_ptr), C.c_void_p(grad_ptr), C.c_void_p(m_ptr), C.c_void_p(v_ptr), int(n), float(lr),
+         float(beta1), float(beta2), float(eps), int(step), stream())
+
+
 def mlp_points(params, pts, viewdirs, occ_softplus, dist_alpha):
     """OfficialStaticNerf.forward at explicit points (forward only).  -> rgb (M,3) or None, dens (M,1)."""
     pts = f32(pts)

@@ -11,7 +11,7 @@ import logging
 
 import torch
 
-from . import _ops, parallel
+from . import _cabi, _ops, parallel
 from .losses import Loss
 
 logger_py = logging.getLogger(__name__)
@@ -84,6 +84,92 @@ class Trainer(object):
             self.optimizer_distortion.step()
         return loss_dict
 
+    # -- the same step as a CUDA graph -----------------------------------------
+    def train_step_graphed(self, data, it=None, epoch=None, scheduling_start=None):
+        """`train_step` with compute_loss + backward captured in a CUDA graph and replayed: one launch instead of ~150, no
+        launch gaps on the device.  Everything that varies from step to step flows through device memory -- the batch is
+        copied into static input buffers, the frame indices travel as device tensors (LearnPose / Learn_Distortion gather
+        their rows on the device), ray choice and jitter are drawn inside the graph (graph-safe Philox state).  What stays
+        host-side selects WHICH graph runs: the last-frame branch of model/training.py:322-345, the fix_scaleN pin, the
+        annealed loss weights and the tensor shapes; a new combination is captured on first use (two eager warm-up passes
+        + capture, ~50 ms).  The optimiser steps and the gradient allreduce run eagerly after the replay.
+        Returns the loss dict of the replayed graph (static tensors, overwritten by the next replay of the same graph)."""
+        if not hasattr(self, '_graphs'):
+            self._graphs = {}
+        n = self.pose_param_net.num_cams
+        idx = int(data.get('img.idx'))
+        ref = int(data.get('img.ref_idxs')) if data.get('img.ref_idxs') is not None else -1
+        wkey = tuple(self.anneal(getattr(self, w)[0], getattr(self, w)[1], scheduling_start, self.annealing_epochs, epoch)
+                     for w in WEIGHT_NAMES) + (epoch < self.annealing_epochs + scheduling_start,)
+        tensors = sorted(k for k, v in data.items() if torch.is_tensor(v) and k not in ('img.idx', 'img.ref_idxs'))
+        key = (idx < n - 1, idx == n - 1, ref == n - 1, wkey, tuple((k, tuple(data[k].shape), data[k].dtype) for k in tensors))
+        slot = self._graphs.get(key)
+        if slot is None:
+            slot = self._capture_step(data, tensors, it, epoch, scheduling_start)
+            self._graphs[key] = slot
+        static = slot['static']
+        for k in tensors:
+            static[k].copy_(data[k], non_blocking=True)
+        static['img.idx_dev'].copy_(data['img.idx'].reshape(1), non_blocking=True)
+        if ref >= 0:
+            static['img.ref_idxs_dev'].copy_(data['img.ref_idxs'].reshape(1), non_blocking=True)
+        static['img.idx'], static['img.ref_idxs'] = data.get('img.idx'), data.get('img.ref_idxs')
+        slot['graph'].replay()
+        self.graphed_launches = getattr(self, 'graphed_launches', 0) + slot['n_launches']
+        for p, g in slot['grads']:
+            p.grad = g
+        self._optimizer_tail()
+        return slot['loss_dict']
+
+    def _all_nets(self):
+        return [m for m in (self.model, self.pose_param_net, self.distortion_net, self.focal_net) if m is not None]
+
+    def _optimizer_tail(self):
+        if self.dp.world_size > 1:
+            self.dp.allreduce_grads([p for m in self._all_nets() for p in m.parameters()])
+        for opt in (self.optimizer, self.optimizer_pose, self.optimizer_focal, self.optimizer_distortion):
+            if opt:
+                opt.step()
+
+    def _capture_step(self, data, tensors, it, epoch, scheduling_start):
+        dev = self.device
+        for m in self._all_nets():
+            m.train()
+        static = {k: data[k].to(dev, copy=True) for k in tensors}
+        static['img.idx_dev'] = data['img.idx'].reshape(1).to(dev)
+        static['img.idx'] = data.get('img.idx')
+        static['img.ref_idxs'] = data.get('img.ref_idxs')
+        if data.get('img.ref_idxs') is not None:
+            static['img.ref_idxs_dev'] = data['img.ref_idxs'].reshape(1).to(dev)
+        params = [p for m in self._all_nets() for p in m.parameters() if p.requires_grad]
+
+        def body():
+            for p in params:
+                p.grad = None
+            ld = self.compute_loss(static, it=it, epoch=epoch, scheduling_start=scheduling_start)
+            ld['loss'].backward()
+            return ld
+
+        warn = getattr(torch.autograd.graph, 'set_warn_on_accumulate_grad_stream_mismatch', None)
+        if warn is not None:
+            warn(False)   # warm-up and capture run on side streams on purpose
+        cur = torch.cuda.current_stream()
+        side = torch.cuda.Stream()
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):      # eager warm-up passes (allocator, lazily built tables); gradients are discarded
+            body()
+            body()
+        cur.wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        for p in params:
+            p.grad = None
+        l0 = _cabi.kernel_launches()
+        with torch.cuda.graph(graph):
+            loss_dict = body()
+        return {'graph': graph, 'static': static, 'loss_dict': loss_dict, 'n_launches': _cabi.kernel_launches() - l0,
+                'grads': [(p, p.grad) for p in params if p.grad is not None]}
+
     def process_data_dict(self, data):
         device = self.device
         img = data.get('img').to(device)
@@ -139,14 +225,15 @@ class Trainer(object):
         kwargs['weights'] = weights
         kwargs['rgb_loss_type'] = rgb_loss_type
         img_idx_i = int(img_idx)
+        idx_dev, ref_idx_dev = data.get('img.idx_dev'), data.get('img.ref_idxs_dev')   # set by train_step_graphed only
 
         num_cams = self.pose_param_net.num_cams
-        c2w = self.pose_param_net(img_idx_i)                       # exp-map kernel
+        c2w = self.pose_param_net(img_idx_i, idx_dev)              # exp-map kernel
         world_mat = _ops.Mat4Inverse.apply(c2w).unsqueeze(0)       # model/training.py:257
 
         ss_in = None
         if self.distortion_net is not None:
-            ss_in = self.distortion_net.scale_shift(img_idx_i)     # [scale, shift] on device, no host sync
+            ss_in = self.distortion_net.scale_shift(img_idx_i, idx_dev)   # [scale, shift] on device, no host sync
         if self.optimizer_focal:
             fxfy = self.focal_net(0)
             pad = torch.zeros(4, device=device)
@@ -196,8 +283,8 @@ class Trainer(object):
 
         if use_ref_imgs:
             ref_idx_i = int(ref_idx)
-            c2w_ref = self.pose_param_net(ref_idx_i)
-            ss_ref = self.distortion_net.scale_shift(ref_idx_i) if self.distortion_net is not None else None
+            c2w_ref = self.pose_param_net(ref_idx_i, ref_idx_dev)
+            ss_ref = self.distortion_net.scale_shift(ref_idx_i, ref_idx_dev) if self.distortion_net is not None else None
             if self.detach_ref_img:
                 c2w_ref = c2w_ref.detach()
                 ss_ref = ss_ref.detach() if ss_ref is not None else None

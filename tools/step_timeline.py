@@ -37,3 +37,8 @@ for e in rows:
     print("%-60s cpu %8.1f us  n=%d" % (e.key[:60], e.self_cpu_time_total / 3, e.count // 3))
 tot_cuda = sum(e.self_device_time_total for e in ev) / 3
 print("GPU kernel time per step: %.3f ms" % (tot_cuda / 1e3))
+rows = sorted(ev, key=lambda e: -e.self_device_time_total)[:30]
+print("--- GPU time per step by kernel")
+for e in rows:
+    if e.self_device_time_total > 0:
+        print("%-90s gpu %8.1f us  n=%d" % (e.key[:90], e.self_device_time_total / 3, e.count // 3))
