@@ -107,6 +107,7 @@ def batch_bytes(b):
 
 
 def run_b200(args):
+    os.environ.setdefault("NCCL_DEBUG", "WARN")   # NCCL's version banner goes to stdout otherwise: stdout carries ONE JSON line
     from model import _cabi, parallel
     dp = parallel.init_from_env()
     world = dp.world_size

@@ -15,13 +15,14 @@ batches = []
 for i in range(4):
     b = syn.make_batch(scene, i, i + 1)
     batches.append({k: (v.to(dev) if torch.is_tensor(v) and k not in ("img.idx", "img.ref_idxs") else v) for k, v in b.items()})
+step = tr.train_step if '--no-graph' in sys.argv else tr.train_step_graphed
 for it in range(5):
-    tr.train_step(batches[it % 4], it=it, epoch=0, scheduling_start=sched)
+    step(batches[it % 4], it=it, epoch=0, scheduling_start=sched)
 torch.cuda.synchronize()
 import time
 t0 = time.perf_counter()
 for it in range(20):
-    tr.train_step(batches[it % 4], it=it, epoch=0, scheduling_start=sched)
+    step(batches[it % 4], it=it, epoch=0, scheduling_start=sched)
 t1 = time.perf_counter()
 torch.cuda.synchronize()
 t2 = time.perf_counter()
@@ -29,7 +30,7 @@ print("cpu issue time per step %.3f ms; wall per step incl. drain %.3f ms" % ((t
 from torch.profiler import profile, ProfilerActivity
 with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
     for it in range(3):
-        tr.train_step(batches[it % 4], it=it, epoch=0, scheduling_start=sched)
+        step(batches[it % 4], it=it, epoch=0, scheduling_start=sched)
     torch.cuda.synchronize()
 ev = prof.key_averages()
 rows = sorted(ev, key=lambda e: -e.self_cpu_time_total)[:25]
