@@ -97,3 +97,96 @@ def test_tc_backward_vs_oracle(R):
         print("tc backward R=%d vs %s: worst rel-L2 %.3e" % (R, name, max(errs.values())))
         print("   ", {k: "%.1e" % v for k, v in errs.items()})
         assert max(errs.values()) <= tol, name
+
+
+def _full_size_inputs(R, seed=5):
+    from model import _cabi
+    g = torch.Generator().manual_seed(seed)
+    sd = syn.init_mlp_state(42)
+    params = [sd[k].to(dev()).requires_grad_(True) for k in _cabi.PARAM_ORDER]
+    o = (torch.randn(3, generator=g) * 0.3).to(dev()).requires_grad_(True)
+    d = torch.nn.functional.normalize(torch.randn(R, 3, generator=g) + torch.tensor([0., 0., -2.]), dim=-1).to(dev()).requires_grad_(True)
+    noise = torch.rand(R, 128, generator=g).to(dev())
+    return params, o, d, noise
+
+
+def test_tc_full_size_properties_cfg2():
+    """BASELINE.json cfg2 size (4,096 rays x 128 samples), where the CPU oracle takes minutes: size-independent properties.
+    (1) ranges: rgb in [0,1], weights >= 0 with sum <= 1, near <= expected distance / sum(w) <= far;
+    (2) rays are independent: rendering a permutation of the rays gives the permuted result bit for bit, in the forward
+        AND in the per-ray gradients; parameter gradients agree up to the fp32 summation order;
+    (3) the backward is linear in the upstream gradient: doubling it doubles the per-ray gradients bit for bit (power-of-two
+        scaling commutes with every bf16 / fp32 rounding in the chain) and the atomically accumulated ones (origin,
+        parameters) up to the fp32 summation order;
+    (4) the oracle agrees on a 96-ray slice of the same batch."""
+    from model import _cabi, _ops
+    R = 4096
+    params, o, d, noise = _full_size_inputs(R)
+    packed = _ops.pack_weights([p.detach() for p in params])
+    rc = _ops.make_cfg(R, 128, 0.01, 10.0, 1, 0, 0, 1, _cabi.PREC_BF16)
+    g = torch.Generator().manual_seed(1)
+    p_rgb, p_dist = torch.randn(R, 3, generator=g).to(dev()) / R, torch.randn(R, generator=g).to(dev()) / R
+
+    def run(perm=None, scale=1.0):
+        for t in params + [o, d]:
+            t.grad = None
+        dd, nn, pr, pd = (d, noise, p_rgb, p_dist) if perm is None else (d[perm], noise[perm], p_rgb[perm], p_dist[perm])
+        rgb, dist, w, a, z = _ops.RenderRays.apply(rc, packed, o, dd, nn, *params)
+        (((rgb * pr).sum() + (dist * pd).sum()) * scale).backward()
+        return rgb.detach(), dist.detach(), w.detach(), d.grad.clone(), o.grad.clone(), [p.grad.clone() for p in params]
+
+    rgb, dist, w, dd, do, dp = run()
+    assert float(rgb.min()) >= 0.0 and float(rgb.max()) <= 1.0 and float(w.min()) >= 0.0
+    ws = w.sum(1)
+    assert float(ws.max()) <= 1.0 + 1e-4
+    ok = ws > 1e-3
+    mean_z = dist[ok] / ws[ok]
+    assert float(mean_z.min()) >= 0.01 - 1e-4 and float(mean_z.max()) <= 10.0 + 1e-3
+    # (2) permutation equivariance
+    perm = torch.randperm(R, generator=g).to(dev())
+    rgb_p, dist_p, w_p, dd_p, do_p, dp_p = run(perm)
+    assert torch.equal(rgb_p, rgb[perm]) and torch.equal(dist_p, dist[perm]) and torch.equal(w_p, w[perm])
+    assert torch.equal(dd_p, dd)   # d.grad is scattered back through the index: same rows, same bits
+    for a, b in zip(dp, dp_p):
+        assert max_err(b, a) <= 1e-5 * float(a.abs().max()) + 1e-9
+    # (3) linearity in the upstream gradient
+    _, _, _, dd2, do2, dp2 = run(scale=2.0)
+    assert torch.equal(dd2, 2 * dd)              # per-ray gradients: no cross-CTA accumulation, bit for bit
+    assert max_err(do2, 2 * do) <= 1e-5 * float(do.abs().max())   # atomically accumulated across CTAs: order varies
+    for a, b in zip(dp, dp2):
+        assert max_err(b, 2 * a) <= 2e-5 * float(a.abs().max()) + 1e-9
+    # (4) oracle on a slice
+    from oracle import nope_oracle as O
+    sl = slice(1000, 1096)
+    sd = syn.init_mlp_state(42)
+    with torch.no_grad():
+        zc = O.stratified_z(96, 128, 0.01, 10.0, noise[sl].cpu())
+        oc, dc = o.detach().cpu(), d.detach().cpu()[sl]
+        pts = (oc.reshape(1, 1, 3) + dc.unsqueeze(1) * zc.unsqueeze(-1)).reshape(-1, 3)
+        view = (-dc).unsqueeze(1).expand(96, 128, 3).reshape(-1, 3)
+        rgb_s, alpha = O.mlp_forward(sd, pts, view)
+        rgb_o, dist_o, _, _ = O.composite(alpha.reshape(96, 128), rgb_s.reshape(96, 128, 3), zc)
+    assert max_err(rgb[sl], rgb_o) <= 1e-2 and max_err(dist[sl], dist_o) <= 1e-1
+
+
+def test_tc_render_chunking_invariance_cfg4_slice():
+    """Full-frame rendering (cfg4) walks the frame in chunks: the result must not depend on where the chunk boundaries fall
+    (odd chunk sizes exercise the half-filled last ray pair of a CTA)."""
+    from model import _cabi, _ops
+    R = 20001
+    params, o, d, _ = _full_size_inputs(R, seed=9)
+    params = [p.detach() for p in params]
+    o, d = o.detach(), d.detach()
+    packed = _ops.pack_weights(params)
+
+    def render(chunk):
+        outs = []
+        for a in range(0, R, chunk):
+            n = min(chunk, R - a)
+            rc = _ops.make_cfg(n, 128, 0.01, 10.0, 1, 0, 0, 1, _cabi.PREC_BF16)
+            rgb, dist, _, _, _ = _ops.render_nograd(rc, params, packed, o, d[a:a + n].contiguous(), None, want_aux=False)
+            outs.append(torch.cat([rgb, dist.reshape(-1, 1)], 1))
+        return torch.cat(outs)
+
+    whole = render(R)
+    assert torch.equal(render(4097), whole) and torch.equal(render(333), whole)
