@@ -53,6 +53,9 @@ struct TcPack {
   int32_t row0;
   int32_t transposed;
   int32_t n_valid;  // rows n >= n_valid are zero (0 = all rows valid)
+  // CTA-pair layout (forward): gnk > 0 -> this stage is k-step gk of a group of gnk stages starting at w_off; the group is stored
+  // as [rows 0..n/2 of every k-step | rows n/2..n of every k-step] so that each CTA of a pair fetches its half with ONE bulk copy
+  int16_t gk, gnk;
 };
 
 __constant__ TcStage c_fwd_stages[TC_MAX_STAGES];
@@ -126,8 +129,9 @@ const Schedule &bwd_schedule() {
   return s;
 }
 
+Schedule build_fwd_schedule_grouped();
 const Schedule &fwd_schedule() {
-  static Schedule s = build_fwd_schedule();
+  static Schedule s = build_fwd_schedule_grouped();
   return s;
 }
 
@@ -157,8 +161,14 @@ __global__ void tc_pack_kernel(PackPtrs P, uint8_t *out, int n_stages, int which
       row[12] = __float2bfloat16_rn(b - __bfloat162float(hi));
     }
     uint8_t *dst = out + st.w_off;
+    int nrow = n;
+    if (pk.gnk > 0) {
+      const int half = st.n >> 1, h = n >= half;
+      dst += (size_t)h * pk.gnk * st.n * 16 + (size_t)pk.gk * st.n * 16;
+      nrow = n - h * half;
+    }
 #pragma unroll
-    for (int kk = 0; kk < 16; ++kk) *reinterpret_cast<__nv_bfloat16 *>(dst + img_off(n, kk, 16)) = row[kk];
+    for (int kk = 0; kk < 16; ++kk) *reinterpret_cast<__nv_bfloat16 *>(dst + img_off(nrow, kk, 16)) = row[kk];
   }
 }
 
@@ -225,6 +235,123 @@ __device__ __forceinline__ void mma_issuer(const uint4 *groups, int n_groups, in
 
 }  // namespace
 
+// ---------------------------------------------------------------------------------------------------------------------
+// CTA-pair flavour (2-CTA clusters, tcgen05.mma.cta_group::2), used by the forward kernel.
+// One MMA spans the pair: M = 256 = tile t of CTA 0 (128 rows) + tile t of CTA 1, and every CTA stages only HALF of the
+// weight rows (N / 2) in its ring -- half the L2->SM and shared-memory bytes per FLOP of the single-CTA form.  That pays
+// for running the two tiles of a CTA OUT of phase (layer L on tile 0, then layer L on tile 1, each consuming the layer's
+// weight stages once): the epilogue of one tile overlaps the MMAs of the other instead of idling the tensor pipe.
+//   producer (one warp per CTA)  : per group, lanes 0..nk-1 copy this CTA's half of each k-step image; full[slot] (tx)
+//   forwarder (CTA 1, one thread): full[slot] observed -> remote arrive on the leader's peer_full[slot]
+//   issuer (leader, one thread)  : act[t] (256 arrivals: the row owners of tile t in BOTH CTAs) at a layer's first group,
+//                                  full[slot] + peer_full[slot], MMAs, multicast commit -> empty[slot] in both CTAs and,
+//                                  after a layer's last group, -> acc[t] in both CTAs
+// n_iters (ray pairs per CTA) is the same in both CTAs of a cluster.
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+
+constexpr int TC2_RING = 4;               // slots of TC2_SLOT bytes (this CTA's half of a group of up to TC2_GK k-steps of [256 x 16] images)
+constexpr uint32_t TC2_GK = 4;
+constexpr uint32_t TC2_SLOT = TC2_GK * 4096;
+// pair-flavour group records: y = A offset (18 bits) | nk << 18 (3 bits) | first << 21 | last << 22
+
+__device__ __forceinline__ int layer_end(const uint4 *groups, int i) {
+  while (!((groups[i].y >> 22) & 1u)) ++i;
+  return i + 1;
+}
+
+// whole warp
+__device__ __forceinline__ void weight_producer_pair(const uint4 *groups, int n_groups, int n_iters, const uint8_t *wimg, uint32_t ring,
+                                                     uint32_t bar_full, uint32_t bar_empty, uint32_t rank, int lane) {
+  uint32_t slot = 0, phase = 0;
+  for (int it = 0; it < n_iters; ++it)
+    for (int i = 0; i < n_groups;) {
+      const int j = layer_end(groups, i);
+      for (int t = 0; t < 2; ++t)
+        for (int gi = i; gi < j; ++gi) {
+          const uint4 g = groups[gi];
+          const uint32_t bytes = (g.z & 0xFFFFu) * 16u * ((g.y >> 18) & 7u);   // this CTA's half of the group: N/2 rows x nk k-steps
+          if (lane == 0) {
+            mbar_wait(bar_empty + 8 * slot, phase ^ 1);
+            mbar_arrive_expect_tx(bar_full + 8 * slot, bytes);
+            bulk_g2s(ring + slot * TC2_SLOT, wimg + g.x + rank * bytes, bytes, bar_full + 8 * slot);
+          }
+          __syncwarp();
+          if (++slot == TC2_RING) { slot = 0; phase ^= 1; }
+        }
+      i = j;
+    }
+}
+
+// CTA 1, lanes 0..TC2_RING-1 of one warp: lane l forwards slot l (every TC2_RING-th group), so that TC2_RING remote arrivals
+// (several hundred cycles each) are in flight at once
+__device__ __forceinline__ void full_forwarder_pair(const uint4 *groups, int n_groups, int n_iters, uint32_t bar_full, int lane) {
+  if (lane >= TC2_RING) return;
+  long long total = 0;
+  for (int i = 0; i < n_groups;) {
+    const int j = layer_end(groups, i);
+    total += 2 * (j - i);
+    i = j;
+  }
+  total *= n_iters;
+  uint32_t phase = 0;
+  for (long long g = lane; g < total; g += TC2_RING) {
+    mbar_wait(bar_full + 8 * lane, phase);
+    mbar_arrive_remote_relaxed(bar_full + 8 * lane, 0);   // same offset in the leader: its full[slot] counts this arrival
+    phase ^= 1;
+  }
+}
+
+// leader CTA, one thread.  bar_acc / bar_act: one barrier per tile (+0 / +8)
+__device__ __forceinline__ void mma_issuer_pair(const uint4 *groups, int n_groups, int n_iters, uint32_t sbase, uint32_t ring,
+                                                uint32_t bar_full, uint32_t bar_empty, uint32_t bar_acc, uint32_t bar_act, uint32_t tmem,
+                                                long long *trace) {
+  uint32_t slot = 0, phase = 0, act_par = 0;
+  long long w_act = 0, w_full = 0, w_peer = 0, t_begin = clock64();   // w_peer: unused (merged into w_full)
+  for (int it = 0; it < n_iters; ++it)
+    for (int i = 0; i < n_groups;) {
+      const int j = layer_end(groups, i);
+      for (uint32_t t = 0; t < 2; ++t) {
+        uint4 nxt = groups[i];
+        for (int gi = i; gi < j; ++gi) {
+          const uint4 g = nxt;
+          if (gi + 1 < j) nxt = groups[gi + 1];
+          const uint32_t nk = (g.y >> 18) & 7u, first = (g.y >> 21) & 1u, last = (g.y >> 22) & 1u;
+          const uint32_t n = g.z & 0xFFFFu, a_gs = g.z >> 16;
+          long long c0 = 0, c1 = 0, c2 = 0;
+          if (trace) c0 = clock64();
+          if (first) {
+            mbar_wait_cluster(bar_act + 8 * t, (act_par >> t) & 1u);
+            act_par ^= 1u << t;
+          }
+          if (trace) c1 = clock64();
+          mbar_wait_cluster(bar_full + 8 * slot, phase);
+          if (trace) { c2 = clock64(); w_act += c1 - c0; w_full += c2 - c1; }
+          tc_fence_after();
+          const uint32_t idesc = idesc_bf16(256, (int)n, 0, 0);
+          const uint32_t a0 = sbase + (g.y & 0x3FFFFu) + t * g.w, b0 = ring + slot * TC2_SLOT, d = tmem + t * 256;
+          // descriptors advance by plain adds on the 14-bit start-address field (256 B per k-step of A, N/2 rows x 32 B of B)
+          uint64_t ad = desc_kmajor(a0, a_gs), bd = desc_kmajor(b0, 256);
+          const uint64_t bstep = (uint64_t)(n * 16u >> 4);
+#pragma unroll
+          for (uint32_t k = 0; k < 4; ++k)
+            if (k < nk) {
+              umma2(d, ad, bd, idesc, (first && k == 0) ? 0u : 1u);
+              ad += 16;
+              bd += bstep;
+            }
+          umma2_commit_mc(bar_empty + 8 * slot, (uint16_t)3);
+          if (last) umma2_commit_mc(bar_acc + 8 * t, (uint16_t)3);
+          if (++slot == TC2_RING) { slot = 0; phase ^= 1; }
+        }
+      }
+      i = j;
+    }
+  if (trace && blockIdx.x == 0) { trace[100] = w_act; trace[101] = w_full; trace[102] = w_peer; trace[103] = clock64() - t_begin; trace[104] = n_iters; }
+}
+
+}  // namespace
+
 // =====================================================================================================================
 // forward kernel
 // =====================================================================================================================
@@ -234,10 +361,10 @@ constexpr uint32_t SM_ACT = 0;                        // 2 x 65536  (128 rows x 
 constexpr uint32_t SM_ENC = 131072;                   // 2 x 16384  (128 x 64)
 constexpr uint32_t SM_AUX = SM_ENC + 32768;           // 2 x 512: 8 identical rows x 32 cols (one ray per tile), group stride 0
 constexpr uint32_t SM_RING = SM_AUX + 1024;          // TC_RING x TC_SLOT
-constexpr uint32_t SM_SMALL = SM_RING + TC_RING * TC_SLOT;  // fp32: w_den[256] w_rgb[384] b_den b_rgb[3] (+pad) = 648 floats
-constexpr uint32_t SM_SCAN = SM_SMALL + 648 * 4;      // 2 tiles x 4 warps x 8 floats
+constexpr uint32_t SM_SMALL = SM_RING + 4 * 16384;   // ring: TC2_RING x TC2_SLOT  // fp32: w_den[256] w_rgb[384] b_den b_rgb[3] (+pad) = 648 floats
+constexpr uint32_t SM_SCAN = SM_SMALL + 8 * 4;       // SM_SMALL: b_den, b_rgb[3]; the head weights are read through L1 (__ldg)      // 2 tiles x 4 warps x 8 floats
 constexpr uint32_t SM_BARS = SM_SCAN + 2 * 4 * 8 * 4; // mbarriers
-constexpr uint32_t SM_TOTAL = SM_BARS + 16 * 8 + 16;
+constexpr uint32_t SM_TOTAL = SM_BARS + 24 * 8 + 16;
 static_assert(SM_TOTAL <= 232448, "shared memory budget");
 
 constexpr uint32_t GS_ACT = 4096, GS_ENC = 1024, GS_AUX = 512;  // GS_AUX: stride of the SAVED aux image (global)
@@ -366,42 +493,59 @@ __device__ __forceinline__ uint32_t store32(uint32_t saddr, uint8_t *gaddr, cons
   return bits;
 }
 
+// row owner -> leader's issuer: "my row of tile t is published / my accumulator row is drained"
+// (CTA 1: the row's shared-memory stores are already fenced towards the async proxy of its own SM -- the only reader, the
+// SM's tensor core -- so the notification itself carries no release: the release.cluster form costs ~900 cycles per layer.)
+__device__ __forceinline__ void act_arrive(uint32_t bar, uint32_t rank) {
+  if (rank == 0) mbar_arrive(bar);
+  else mbar_arrive_remote_relaxed(bar, 0);
+}
+
 template <bool SAVE>
-__global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const uint32_t sbase = smem_u32(smem);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float *sm_small = reinterpret_cast<float *>(smem + SM_SMALL);
   float *sm_scan = reinterpret_cast<float *>(smem + SM_SCAN);
-  const uint32_t bar_full = sbase + SM_BARS, bar_empty = bar_full + TC_RING * 8, bar_acc = bar_empty + TC_RING * 8,
-                 bar_act = bar_acc + 8;
-  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + SM_BARS + 16 * 8);
+  // full / empty: TC2_RING each; acc / act: one per tile (+0 / +8)
+  const uint32_t bar_full = sbase + SM_BARS, bar_empty = bar_full + TC2_RING * 8, bar_acc = bar_empty + TC2_RING * 8,
+                 bar_act = bar_acc + 16;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + SM_BARS + 24 * 8);
+  const uint32_t rank = cluster_ctarank();
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < TC_RING; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, 1); }
+    // leader: full[slot] completes on its own copies (arrive + tx bytes) AND the peer's forwarded "my half landed" arrival
+    for (int i = 0; i < TC2_RING; ++i) { mbar_init(bar_full + 8 * i, rank == 0 ? 2 : 1); mbar_init(bar_empty + 8 * i, 1); }
     mbar_init(bar_acc, 1);
-    mbar_init(bar_act, 256);
+    mbar_init(bar_acc + 8, 1);
+    mbar_init(bar_act, 256);       // used in the leader CTA: 128 local + 128 remote arrivals per tile
+    mbar_init(bar_act + 8, 256);
     mbar_fence_init();
   }
-  for (int i = threadIdx.x; i < 256; i += blockDim.x) sm_small[i] = A.w_den[i];
-  for (int i = threadIdx.x; i < 384; i += blockDim.x) sm_small[256 + i] = A.w_rgb[i];
-  if (threadIdx.x == 0) { sm_small[640] = A.b_den[0]; sm_small[641] = A.b_rgb[0]; sm_small[642] = A.b_rgb[1]; sm_small[643] = A.b_rgb[2]; }
-  if (warp == 9) tmem_alloc(smem_u32(tmem_slot), 512);
+  if (threadIdx.x == 0) { sm_small[0] = A.b_den[0]; sm_small[1] = A.b_rgb[0]; sm_small[2] = A.b_rgb[1]; sm_small[3] = A.b_rgb[2]; }
+  if (warp == 9) tmem_alloc2(smem_u32(tmem_slot), 512);
   tc_fence_before();
   __syncthreads();
+  cluster_sync_all();   // the peer's barriers exist before anything signals them
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   const int n_pairs = (A.n_rays + 1) >> 1;
+  // both CTAs of a cluster run the same number of ray pairs (they share every MMA); a pair index >= n_pairs is a dummy
+  // pass (both tiles invalid: computed, never stored)
+  const int n_iters = (n_pairs - (int)(blockIdx.x & ~1u) + (int)gridDim.x - 1) / (int)gridDim.x;
 
   if (warp == 8) {
     // ------------------------------------------------ weight producer
-    if (elect_one()) weight_producer<TC_RING>(c_fwd_groups, A.n_stages, n_pairs, A.wimg, sbase + SM_RING, bar_full, bar_empty);
-    __syncwarp();
+    weight_producer_pair(c_fwd_groups, A.n_stages, n_iters, A.wimg, sbase + SM_RING, bar_full, bar_empty, rank, lane);
   } else if (warp == 9) {
     // ------------------------------------------------ MMA issuer
-    if (elect_one())
-      mma_issuer<TC_RING>(c_fwd_groups, A.n_stages, n_pairs, sbase, sbase + SM_RING, bar_full, bar_empty, bar_acc, bar_act, tmem,
-                          A.trace ? A.trace + 64 : nullptr);
+    if (rank == 0) {
+      if (elect_one())
+        mma_issuer_pair(c_fwd_groups, A.n_stages, n_iters, sbase, sbase + SM_RING, bar_full, bar_empty, bar_acc, bar_act, tmem, A.trace);
+    } else {
+      full_forwarder_pair(c_fwd_groups, A.n_stages, n_iters, bar_full, lane);
+    }
     __syncwarp();
   } else {
     // ------------------------------------------------ row owners: prologue, epilogues, heads, compositing
@@ -412,7 +556,9 @@ __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
     const uint32_t tacc = tmem + ((uint32_t)(q * 32) << 16) + t * 256;
     float *scan = sm_scan + t * 32;
     uint32_t acc_par = 0;
-    for (int pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
+    const uint32_t bar_acc_t = bar_acc + 8 * t, bar_act_t = bar_act + 8 * t;
+    for (int it = 0; it < n_iters; ++it) {
+      const int pair = blockIdx.x + it * gridDim.x;
       const int ray_raw = 2 * pair + t;
       const bool valid = ray_raw < A.n_rays;
       const int ray = valid ? ray_raw : A.n_rays - 1;
@@ -434,11 +580,11 @@ __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
       }
       fence_async_smem();
       tc_fence_before();
-      mbar_arrive(bar_act);
+      act_arrive(bar_act_t, rank);
 
       float alpha = 0.f, r_s = 0.f, g_s = 0.f, b_s = 0.f, raw_den = 0.f;
       for (int L = 0; L < 10; ++L) {
-        mbar_wait(bar_acc, acc_par);
+        mbar_wait(bar_acc_t, acc_par);
         acc_par ^= 1;
         tc_fence_after();
         if (A.trace && blockIdx.x == 0 && pair == 0 && threadIdx.x == 0) A.trace[L * 4 + 0] = clock64();
@@ -452,10 +598,10 @@ __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
             tmem_ld32(tacc + c0 + 32, v1);
             tmem_ld_wait();
             if (L == 7) {
-              const float4 *wd = reinterpret_cast<const float4 *>(sm_small + c0);
+              const float4 *wd = reinterpret_cast<const float4 *>(A.w_den + c0);   // same address in every lane: L1 broadcast
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
-                const float4 w = wd[j];
+                const float4 w = __ldg(wd + j);
                 ds0 = fmaf(fmaxf(__uint_as_float(v0[4 * j]), 0.f), w.x, ds0);
                 ds1 = fmaf(fmaxf(__uint_as_float(v0[4 * j + 1]), 0.f), w.y, ds1);
                 ds2 = fmaf(fmaxf(__uint_as_float(v0[4 * j + 2]), 0.f), w.z, ds2);
@@ -463,7 +609,7 @@ __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
               }
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
-                const float4 w = wd[8 + j];
+                const float4 w = __ldg(wd + 8 + j);
                 ds0 = fmaf(fmaxf(__uint_as_float(v1[4 * j]), 0.f), w.x, ds0);
                 ds1 = fmaf(fmaxf(__uint_as_float(v1[4 * j + 1]), 0.f), w.y, ds1);
                 ds2 = fmaf(fmaxf(__uint_as_float(v1[4 * j + 2]), 0.f), w.z, ds2);
@@ -487,25 +633,25 @@ __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
           }
           if (L == 7) {
             // density head (model/official_nerf.py:66,77-83): softplus(beta 1, threshold 20) or relu, then 1 - exp(-d)
-            const float raw = (ds0 + ds1) + (ds2 + ds3) + sm_small[640];
+            const float raw = (ds0 + ds1) + (ds2 + ds3) + sm_small[0];
             raw_den = raw;
             const float d = A.softplus ? (raw > 20.f ? raw : log1pf(expf(raw))) : fmaxf(raw, 0.f);
             alpha = 1.f - expf(-d);
           }
           fence_async_smem();
           tc_fence_before();
-          mbar_arrive(bar_act);
+          act_arrive(bar_act_t, rank);
           if (A.trace && blockIdx.x == 0 && pair == 0 && threadIdx.x == 0) A.trace[L * 4 + 1] = clock64();
         } else {
           // rgb head: relu(rgb_layers.0) (128 wide, TMEM cols 0..127) . fc_rgb^T + b -> sigmoid
-          float s0 = sm_small[641], s1 = sm_small[642], s2 = sm_small[643];
+          float s0 = sm_small[1], s1 = sm_small[2], s2 = sm_small[3];
           uint32_t mc[4];
 #pragma unroll
           for (int c0 = 0; c0 < 128; c0 += 32) {
             uint32_t v0[32];
             tmem_ld32(tacc + c0, v0);
             tmem_ld_wait();
-            const float *w0 = sm_small + 256 + c0, *w1 = w0 + 128, *w2 = w0 + 256;
+            const float *w0 = A.w_rgb + c0, *w1 = w0 + 128, *w2 = w0 + 256;
             if (sv) {
               uint8_t *ghc = gtile + FW_HC + (row >> 3) * 2048 + (row & 7) * 16 + (c0 >> 3) * 128;
               uint32_t bits = 0;
@@ -524,9 +670,9 @@ __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
               const float h = fmaxf(__uint_as_float(v0[j]), 0.f);
-              s0 = fmaf(h, w0[j], s0);
-              s1 = fmaf(h, w1[j], s1);
-              s2 = fmaf(h, w2[j], s2);
+              s0 = fmaf(h, __ldg(w0 + j), s0);
+              s1 = fmaf(h, __ldg(w1 + j), s1);
+              s2 = fmaf(h, __ldg(w2 + j), s2);
             }
           }
           r_s = 1.f / (1.f + expf(-s0));
@@ -568,7 +714,8 @@ __global__ void __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 9) tmem_dealloc(tmem, 512);
+  cluster_sync_all();   // neither CTA leaves (or frees TMEM) while pair-MMAs or remote arrivals may still be in flight
+  if (warp == 9) tmem_dealloc2(tmem, 512);
 }
 
 }  // namespace
@@ -1155,8 +1302,52 @@ std::vector<uint4> build_groups(const Schedule &S, const ALayout &L) {
   }
   return G;
 }
+// pair flavour: up to 4 consecutive k-steps per group (see TC2_SLOT)
+std::vector<uint4> build_groups_pair(const Schedule &S, const ALayout &L) {
+  std::vector<uint4> G;
+  size_t i = 0;
+  while (i < S.st.size()) {
+    const TcStage &a = S.st[i];
+    uint32_t nk = 1;
+    while (nk < TC2_GK && i + nk < S.st.size()) {
+      const TcStage &p = S.st[i + nk - 1], &b = S.st[i + nk];
+      if (p.last || b.first || b.a_src != a.a_src || b.a_k != p.a_k + 1 || b.n != a.n || b.w_off != p.w_off + p.n * 32u) break;
+      ++nk;
+    }
+    const TcStage &z = S.st[i + nk - 1];
+    uint4 g;
+    g.x = a.w_off;
+    g.y = (L.off[a.a_src] + (uint32_t)a.a_k * 256u) | (nk << 18) | ((uint32_t)a.first << 21) | ((uint32_t)z.last << 22);
+    g.z = (uint32_t)a.n | (L.gs[a.a_src] << 16);
+    g.w = L.tile_stride[a.a_src];
+    G.push_back(g);
+    i += nk;
+  }
+  return G;
+}
+const ALayout kFwdLayout{{SM_ACT, SM_ENC, SM_AUX, 0, 0}, {65536u, 16384u, 512u, 0, 0}, {GS_ACT, GS_ENC, 0u, 0, 0}};
+// the forward schedule with every stage told where it sits inside its issue group (TcPack::gk / gnk, w_off = group start)
+Schedule build_fwd_schedule_grouped() {
+  Schedule S = build_fwd_schedule();
+  const std::vector<uint4> G = build_groups_pair(S, kFwdLayout);
+  size_t i = 0;
+  for (const uint4 &g : G) {
+    const int nk = (int)((g.y >> 18) & 7u);
+    for (int k = 0; k < nk; ++k) {
+      S.st[i + k].w_off = g.x;
+      S.pk[i + k].gk = (int16_t)k;
+      S.pk[i + k].gnk = (int16_t)nk;
+    }
+    i += nk;
+  }
+  return S;
+}
+std::vector<uint4> build_fwd_groups() {
+  // group boundaries from the plain schedule (the grouped one has w_off rewritten)
+  return build_groups_pair(build_fwd_schedule(), kFwdLayout);
+}
 const std::vector<uint4> &fwd_groups() {
-  static std::vector<uint4> g = build_groups(fwd_schedule(), ALayout{{SM_ACT, SM_ENC, SM_AUX, 0, 0}, {65536u, 16384u, 512u, 0, 0}, {GS_ACT, GS_ENC, 0u, 0, 0}});
+  static std::vector<uint4> g = build_fwd_groups();
   return g;
 }
 const std::vector<uint4> &bwd_groups() {
@@ -1233,7 +1424,9 @@ int nnb_tc_render_fwd(const nnb_render_cfg *cfg, const float *const *params, con
     A.ws_s = reinterpret_cast<float4 *>(static_cast<uint8_t *>(ws) + ws_fwd_bytes(cfg->n_rays) + ws_bwd_bytes(cfg->n_rays));
   }
   const int n_pairs = (cfg->n_rays + 1) / 2;
-  const int grid = n_pairs < nnb_sm_count() ? n_pairs : nnb_sm_count();
+  int grid = n_pairs < nnb_sm_count() ? n_pairs : nnb_sm_count();
+  grid = (grid + 1) & ~1;                       // 2-CTA clusters
+  if (grid > (nnb_sm_count() & ~1)) grid = nnb_sm_count() & ~1;
   if (save) tc_fwd_kernel<true><<<grid, 320, SM_TOTAL, s>>>(A);
   else tc_fwd_kernel<false><<<grid, 320, SM_TOTAL, s>>>(A);
   NNB_CHECK_LAUNCH();

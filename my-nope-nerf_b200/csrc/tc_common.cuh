@@ -186,6 +186,16 @@ __device__ __forceinline__ void mbar_arrive_remote(uint32_t bar, uint32_t rank) 
       ::"r"(bar), "r"(rank)
       : "memory");
 }
+// same without release semantics: for pure notifications (the forwarded fact was established by an async-proxy copy that
+// the notifier has already observed complete; it has no writes of its own to publish).  Much cheaper than the release form.
+__device__ __forceinline__ void mbar_arrive_remote_relaxed(uint32_t bar, uint32_t rank) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [ra];\n\t}"
+      ::"r"(bar), "r"(rank)
+      : "memory");
+}
 // wait with acquire at cluster scope (pairs with mbar_arrive_remote)
 __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
   uint32_t ok;
