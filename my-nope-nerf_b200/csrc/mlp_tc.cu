@@ -124,8 +124,9 @@ Schedule build_bwd_schedule() {
   return S;
 }
 
+Schedule build_bwd_schedule_grouped();
 const Schedule &bwd_schedule() {
-  static Schedule s = build_bwd_schedule();
+  static Schedule s = build_bwd_schedule_grouped();
   return s;
 }
 
@@ -791,35 +792,44 @@ __device__ __forceinline__ void enc_backward(const float x[3], const uint32_t *g
   }
 }
 
-__global__ void __launch_bounds__(320, 1) tc_bwd_kernel(const BwdArgs A) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1) tc_bwd_kernel(const BwdArgs A) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const uint32_t sbase = smem_u32(smem);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float *sm_wrgb = reinterpret_cast<float *>(smem + SB_SMALL);
   float *sm_scan = reinterpret_cast<float *>(smem + SB_SCAN);
-  const uint32_t bar_full = sbase + SB_BARS, bar_empty = bar_full + BW_RING * 8, bar_acc = bar_empty + BW_RING * 8,
-                 bar_act = bar_acc + 8;
+  // CTA-pair flavour, as the forward (see weight_producer_pair): full / empty: TC2_RING each; acc / act: one per tile (+0 / +8)
+  const uint32_t bar_full = sbase + SB_BARS, bar_empty = bar_full + TC2_RING * 8, bar_acc = bar_empty + TC2_RING * 8,
+                 bar_act = bar_acc + 16;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + SB_BARS + 24 * 8);
+  const uint32_t rank = cluster_ctarank();
   if (threadIdx.x == 0) {
-    for (int i = 0; i < BW_RING; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, 1); }
+    for (int i = 0; i < TC2_RING; ++i) { mbar_init(bar_full + 8 * i, rank == 0 ? 2 : 1); mbar_init(bar_empty + 8 * i, 1); }
     mbar_init(bar_acc, 1);
+    mbar_init(bar_acc + 8, 1);
     mbar_init(bar_act, 256);
+    mbar_init(bar_act + 8, 256);
     mbar_fence_init();
   }
   for (int i = threadIdx.x; i < 384; i += blockDim.x) sm_wrgb[i] = A.w_rgb[i];
-  if (warp == 9) tmem_alloc(smem_u32(tmem_slot), 512);
+  if (warp == 9) tmem_alloc2(smem_u32(tmem_slot), 512);
   tc_fence_before();
   __syncthreads();
+  cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   const int n_pairs = (A.n_rays + 1) >> 1;
+  const int n_iters = (n_pairs - (int)(blockIdx.x & ~1u) + (int)gridDim.x - 1) / (int)gridDim.x;   // same in both CTAs of a pair
 
   if (warp == 8) {
-    if (elect_one()) weight_producer<BW_RING>(c_bwd_groups, A.n_stages, n_pairs, A.wimg, sbase + SB_RING, bar_full, bar_empty);
-    __syncwarp();
+    weight_producer_pair(c_bwd_groups, A.n_stages, n_iters, A.wimg, sbase + SB_RING, bar_full, bar_empty, rank, lane);
   } else if (warp == 9) {
-    if (elect_one())
-      mma_issuer<BW_RING>(c_bwd_groups, A.n_stages, n_pairs, sbase, sbase + SB_RING, bar_full, bar_empty, bar_acc, bar_act, tmem, nullptr);
+    if (rank == 0) {
+      if (elect_one())
+        mma_issuer_pair(c_bwd_groups, A.n_stages, n_iters, sbase, sbase + SB_RING, bar_full, bar_empty, bar_acc, bar_act, tmem, nullptr);
+    } else {
+      full_forwarder_pair(c_bwd_groups, A.n_stages, n_iters, bar_full, lane);
+    }
     __syncwarp();
   } else {
     const int t = warp >> 2, q = warp & 3, row = q * 32 + lane;
@@ -829,8 +839,10 @@ __global__ void __launch_bounds__(320, 1) tc_bwd_kernel(const BwdArgs A) {
     const uint32_t tacc = tmem + ((uint32_t)(q * 32) << 16) + t * 256;
     float *scan = sm_scan + t * 64;
     uint32_t acc_par = 0;
+    const uint32_t bar_acc_t = bar_acc + 8 * t, bar_act_t = bar_act + 8 * t;
     float acc_origin[3] = {0.f, 0.f, 0.f}, acc_bias[4] = {0.f, 0.f, 0.f, 0.f};  // meaningful on row 0 of each tile
-    for (int pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
+    for (int it = 0; it < n_iters; ++it) {
+      const int pair = blockIdx.x + it * gridDim.x;
       const int ray_raw = 2 * pair + t;
       const bool valid = ray_raw < A.n_rays;
       const int ray = valid ? ray_raw : A.n_rays - 1;
@@ -900,7 +912,7 @@ __global__ void __launch_bounds__(320, 1) tc_bwd_kernel(const BwdArgs A) {
       }
       fence_async_smem();
       tc_fence_before();
-      mbar_arrive(bar_act);
+      act_arrive(bar_act_t, rank);
 
       float xp[3], xv[3], d_p[3] = {0.f, 0.f, 0.f}, d_v[3] = {0.f, 0.f, 0.f};
 #pragma unroll
@@ -921,7 +933,7 @@ __global__ void __launch_bounds__(320, 1) tc_bwd_kernel(const BwdArgs A) {
           const uint4 m0 = ld_global_v4(gm), m1 = ld_global_v4(gm + 16);
           mw[0] = m0.x; mw[1] = m0.y; mw[2] = m0.z; mw[3] = m0.w; mw[4] = m1.x; mw[5] = m1.y; mw[6] = m1.z; mw[7] = m1.w;
         }
-        mbar_wait(bar_acc, acc_par);
+        mbar_wait(bar_acc_t, acc_par);
         acc_par ^= 1;
         tc_fence_after();
         if (ek == EPI_DIR) {
@@ -962,7 +974,7 @@ __global__ void __launch_bounds__(320, 1) tc_bwd_kernel(const BwdArgs A) {
         if (e < 11) {
           fence_async_smem();
           tc_fence_before();
-          mbar_arrive(bar_act);
+          act_arrive(bar_act_t, rank);
         }
       }
       // ---- per-ray reductions: d_dirs, and the CTA-level accumulators (d_origin, head biases)
@@ -994,7 +1006,8 @@ __global__ void __launch_bounds__(320, 1) tc_bwd_kernel(const BwdArgs A) {
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 9) tmem_dealloc(tmem, 512);
+  cluster_sync_all();
+  if (warp == 9) tmem_dealloc2(tmem, 512);
 }
 
 }  // namespace
@@ -1342,6 +1355,22 @@ Schedule build_fwd_schedule_grouped() {
   }
   return S;
 }
+const ALayout kBwdLayout{{SB_ACT, 0, 0, SB_ACT, SB_DSMALL}, {65536u, 0, 0, 65536u, 4096u}, {4096u, 0, 0, 2048u, 256u}};
+Schedule group_schedule(Schedule S, const ALayout &L) {
+  const std::vector<uint4> G = build_groups_pair(S, L);
+  size_t i = 0;
+  for (const uint4 &g : G) {
+    const int nk = (int)((g.y >> 18) & 7u);
+    for (int k = 0; k < nk; ++k) {
+      S.st[i + k].w_off = g.x;
+      S.pk[i + k].gk = (int16_t)k;
+      S.pk[i + k].gnk = (int16_t)nk;
+    }
+    i += nk;
+  }
+  return S;
+}
+Schedule build_bwd_schedule_grouped() { return group_schedule(build_bwd_schedule(), kBwdLayout); }
 std::vector<uint4> build_fwd_groups() {
   // group boundaries from the plain schedule (the grouped one has w_off rewritten)
   return build_groups_pair(build_fwd_schedule(), kFwdLayout);
@@ -1351,7 +1380,7 @@ const std::vector<uint4> &fwd_groups() {
   return g;
 }
 const std::vector<uint4> &bwd_groups() {
-  static std::vector<uint4> g = build_groups(bwd_schedule(), ALayout{{SB_ACT, 0, 0, SB_ACT, SB_DSMALL}, {65536u, 0, 0, 65536u, 4096u}, {4096u, 0, 0, 2048u, 256u}});
+  static std::vector<uint4> g = build_groups_pair(build_bwd_schedule(), kBwdLayout);
   return g;
 }
 
@@ -1458,7 +1487,9 @@ int nnb_tc_render_bwd(const nnb_render_cfg *cfg, const float *const *params, con
   B.n_rays = R; B.n_stages = (int)bwd_groups().size();
   B.softplus = cfg->occ_softplus; B.white = cfg->white_bkgd; B.use_dir = cfg->use_dir;
   const int n_pairs = (R + 1) / 2;
-  const int grid = n_pairs < nnb_sm_count() ? n_pairs : nnb_sm_count();
+  int grid = n_pairs < nnb_sm_count() ? n_pairs : nnb_sm_count();
+  grid = (grid + 1) & ~1;                       // 2-CTA clusters
+  if (grid > (nnb_sm_count() & ~1)) grid = nnb_sm_count() & ~1;
   tc_bwd_kernel<<<grid, 320, SB_TOTAL, s>>>(B);
   NNB_CHECK_LAUNCH();
   WgArgs W{};
