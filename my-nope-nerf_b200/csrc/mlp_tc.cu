@@ -265,6 +265,7 @@ __device__ __forceinline__ int layer_end(const uint4 *groups, int i) {
 __device__ __forceinline__ void weight_producer_pair(const uint4 *groups, int n_groups, int n_iters, const uint8_t *wimg, uint32_t ring,
                                                      uint32_t bar_full, uint32_t bar_empty, uint32_t rank, int lane) {
   uint32_t slot = 0, phase = 0;
+  const uint64_t keep = l2_policy_evict_last();
   for (int it = 0; it < n_iters; ++it)
     for (int i = 0; i < n_groups;) {
       const int j = layer_end(groups, i);
@@ -275,7 +276,7 @@ __device__ __forceinline__ void weight_producer_pair(const uint4 *groups, int n_
           if (lane == 0) {
             mbar_wait(bar_empty + 8 * slot, phase ^ 1);
             mbar_arrive_expect_tx(bar_full + 8 * slot, bytes);
-            bulk_g2s(ring + slot * TC2_SLOT, wimg + g.x + rank * bytes, bytes, bar_full + 8 * slot);
+            bulk_g2s_hint(ring + slot * TC2_SLOT, wimg + g.x + rank * bytes, bytes, bar_full + 8 * slot, keep);
           }
           __syncwarp();
           if (++slot == TC2_RING) { slot = 0; phase ^= 1; }
@@ -400,7 +401,8 @@ constexpr uint32_t BW_DSMALL = BW_DYRGB0 + 32768;  // 16 cols: d_raw rgb (3), d_
 constexpr uint32_t BWD_TILE_BYTES = BW_DSMALL + 4096;
 
 __device__ __forceinline__ void st_global_v4(void *p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
-  asm volatile("st.global.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+  // streaming (evict-first): the saved images are read back only after several GB of other traffic
+  asm volatile("st.global.cs.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 // one 16-byte chunk (8 bf16) of an operand image: shared-memory copy (MMA operand) and optional global copy
 template <bool SAVE>

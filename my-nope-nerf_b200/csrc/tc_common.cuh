@@ -59,6 +59,17 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst_smem, const void *src, uin
                "l"(src), "r"(bytes), "r"(bar)
                : "memory");
 }
+// same with an L2 evict_last hint: for the small, endlessly re-read weight images that share L2 with a multi-GB store stream
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ void bulk_g2s_hint(uint32_t dst_smem, const void *src, uint32_t bytes, uint32_t bar, uint64_t policy) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(dst_smem),
+               "l"(src), "r"(bytes), "r"(bar), "l"(policy)
+               : "memory");
+}
 // global -> the same shared-memory offset of every CTA in `cta_mask` of this cluster; each destination's `bar` (same offset)
 // receives the complete_tx
 __device__ __forceinline__ void bulk_g2s_mc(uint32_t dst_smem, const void *src, uint32_t bytes, uint32_t bar, uint16_t cta_mask) {
