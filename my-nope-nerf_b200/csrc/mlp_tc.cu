@@ -394,7 +394,8 @@ constexpr uint32_t FW_AUX = FW_ENC + 16384;  // view-direction encoding + ones, 
 constexpr uint32_t FW_MASK = FW_AUX + 8192;   // ReLU sign bitmasks: 9 layers (H0..H7, Hc) x 128 rows x 8 words
 constexpr uint32_t FWD_TILE_BYTES = FW_MASK + 9 * 4096;
 // gradient images written by the backward, read by the weight-gradient kernel
-constexpr uint32_t BW_DY = 0;                // dY0..dY7
+constexpr uint32_t BW_DY = 0;                // dY0..dY7; each 64 KB image is SAVED as two 128-column images (columns 0..127 | 128..255,
+                                             // gs 2048) so that the weight-gradient kernel fetches its half of a stage with one bulk copy
 constexpr uint32_t BW_DYFEAT = 8 * 65536;
 constexpr uint32_t BW_DYRGB0 = 9 * 65536;    // 128 cols
 constexpr uint32_t BW_DSMALL = BW_DYRGB0 + 32768;  // 16 cols: d_raw rgb (3), d_raw density (1)
@@ -950,7 +951,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1) tc_bwd_kerne
           tmem_ld_wait();
           enc_backward<10>(xp, v0, d_p);
         } else {
-          uint8_t *grow = btile + (ek == EPI_FEAT ? BW_DYFEAT : BW_DY + (uint32_t)slot_of[e] * 65536u) + rowoff256;
+          uint8_t *grow = btile + (ek == EPI_FEAT ? BW_DYFEAT : BW_DY + (uint32_t)slot_of[e] * 65536u) + rowoff128;   // split-halves layout
           const bool masked = (ek == EPI_MASK);
 #pragma unroll
           for (int c0 = 0; c0 < 256; c0 += 32) {
@@ -969,7 +970,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1) tc_bwd_kerne
             for (int gch = 0; gch < 4; ++gch) {
               const uint32_t off = ((c0 >> 3) + gch) * 128;
               st_shared_v4(act_row + off, o[4 * gch], o[4 * gch + 1], o[4 * gch + 2], o[4 * gch + 3]);
-              if (valid) st_global_v4(grow + off, o[4 * gch], o[4 * gch + 1], o[4 * gch + 2], o[4 * gch + 3]);
+              if (valid) st_global_v4(grow + (off >> 11) * 32768u + (off & 2047u), o[4 * gch], o[4 * gch + 1], o[4 * gch + 2], o[4 * gch + 3]);
             }
           }
         }
@@ -1200,7 +1201,7 @@ WgPlan build_wg_plan() {
     for (int h = 0; h < 2; ++h) {
       WgJob J{};
       const int wp = P_L0 + 2 * L;
-      J.p_ws = 1; J.p_slot_off = BW_DY + (uint32_t)L * 65536u; J.p_gs = 4096; J.p_col0 = 128 * h;
+      J.p_ws = 1; J.p_slot_off = BW_DY + (uint32_t)L * 65536u + (uint32_t)h * 32768u; J.p_gs = 2048; J.p_col0 = 0;
       if (L == 0) {
         J.n_parts = 2;
         J.q[0] = part(0, FW_ENC, 1024, 64, 0);
@@ -1233,7 +1234,7 @@ WgPlan build_wg_plan() {
     WgJob H[2];
     for (int h = 0; h < 2; ++h) {
       WgJob J{};
-      J.p_ws = 1; J.p_slot_off = BW_DYFEAT; J.p_gs = 4096; J.p_col0 = 128 * h;
+      J.p_ws = 1; J.p_slot_off = BW_DYFEAT + (uint32_t)h * 32768u; J.p_gs = 2048; J.p_col0 = 0;
       J.n_parts = 2;
       J.q[0] = part(0, FW_H + 7 * 65536u, 4096, 256, 0);
       J.q[1] = part(0, FW_AUX, 512, 32, 256);
