@@ -1021,23 +1021,28 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1) tc_bwd_kerne
 namespace {
 
 constexpr int WG_MAX_JOBS = 32;
-constexpr int WG_RING = 3;
+constexpr int WG_MAX_RING = 8;        // ring depth = min(8, ring bytes / stage bytes of the job): 3 for the 256-wide layers, 8 for the heads
 constexpr int WG_SUB = 2;             // stages per 128-sample tile
 constexpr int WG_GROUPS = 8;          // 8-sample row groups per stage (64 samples, 4 k-steps)
-constexpr uint32_t WG_SLOT = 61440;   // P 16 KB + Q parts up to 44 KB
+constexpr uint32_t WG_RING_BYTES = 184320;   // a stage is P 16 KB + Q parts up to 44 KB
 constexpr uint32_t SW_RING = 0;
-constexpr uint32_t SW_BARS = WG_RING * WG_SLOT;
+constexpr uint32_t SW_BARS = WG_RING_BYTES;
 constexpr uint32_t SW_TOTAL = SW_BARS + 24 * 8 + 16;
 static_assert(SW_TOTAL <= 232448, "shared memory budget");
 
 struct WgPart { uint32_t slot_off, gs; uint16_t n, tm_col; uint8_t ws, pad[3]; };
-struct WgSeg { int32_t param, offset, stride_m, stride_n; uint16_t tm_col, count; };
+struct WgSeg { int32_t param, offset, stride_m, stride_n; uint16_t tm_col, count; uint8_t m0, m_n, pad[2]; };   // rows [m0, m0 + m_n) are flushed (m_n = 0: all 128)
 struct WgJob {
   uint32_t p_slot_off, p_gs, p_col0;
   uint8_t p_ws, n_parts, n_segs, shared;   // shared: the two CTAs of a cluster stream the same Q images (multicast halves)
   uint16_t splits, cl0;    // clusters [cl0, cl0 + splits) work on this job pair; entry 2p / 2p+1 = cluster rank 0 / 1
   WgPart q[3];
   WgSeg seg[4];
+  // optional second product on the same stage: D2[m][n] = sum_s P2[s][m] * Q[p2_q][s][p2_qcol0 + n].  P2 is a narrow image
+  // (16 columns of per-sample head gradients); the MMA still has M = 128, rows past the image's width are never flushed.
+  uint32_t p2_slot_off, p2_gs;
+  uint16_t p2_n, p2_tm_col, p2_qcol0;
+  uint8_t p2_on, p2_ws, p2_q, pad2[3];
 };
 __constant__ WgJob c_wg_jobs[WG_MAX_JOBS];
 
@@ -1045,13 +1050,16 @@ struct WgArgs {
   const uint8_t *ws_fwd, *ws_bwd;
   float *d_params[NNB_NUM_PARAMS];
   int n_tiles, n_jobs;
+  long long *trace;  // debug (nnb_debug_set_trace): globaltimer stamps per CTA at [1024 + 4*cta]: start, streaming done, flushed
 };
+
+__device__ __forceinline__ long long globaltimer_ns() { long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(192, 1) tc_wgrad_kernel(const WgArgs A) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const uint32_t sbase = smem_u32(smem);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t bar_full = sbase + SW_BARS, bar_empty = bar_full + WG_RING * 8, bar_done = bar_empty + WG_RING * 8;
+  const uint32_t bar_full = sbase + SW_BARS, bar_empty = bar_full + WG_MAX_RING * 8, bar_done = bar_empty + WG_MAX_RING * 8;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + SW_BARS + 24 * 8);
   // which job pair / split: cluster c runs entry 2p + rank of pair p
   const uint32_t rank = cluster_ctarank();
@@ -1071,8 +1079,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(192, 1) tc_wgrad_ker
   }
   const bool active = t1 > t0;
   const uint16_t mc_mask = shared ? (uint16_t)3 : (uint16_t)(1u << rank);
+  if (A.trace && threadIdx.x == 0) { A.trace[1024 + 4 * blockIdx.x] = globaltimer_ns(); A.trace[1024 + 4 * blockIdx.x + 3] = p; }
   if (threadIdx.x == 0) {
-    for (int i = 0; i < WG_RING; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, shared ? 2 : 1); }
+    for (int i = 0; i < WG_MAX_RING; ++i) { mbar_init(bar_full + 8 * i, 1); mbar_init(bar_empty + 8 * i, shared ? 2 : 1); }
     mbar_init(bar_done, 1);
     mbar_fence_init();
   }
@@ -1082,19 +1091,20 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(192, 1) tc_wgrad_ker
   cluster_sync_all();   // the peer's barriers exist before anything is multicast to them
   tc_fence_after();
   const uint32_t tmem = active ? *tmem_slot : 0;
+  // stage = P (8 row groups x 2 KB) followed by the job's Q parts; small stages get a deeper ring (latency, not bandwidth,
+  // bounds a CTA whose ring holds few bytes).  Both CTAs of a shared pair have the same geometry.
   uint32_t q_off[3];
-  {
-    uint32_t o = WG_GROUPS * 2048;
-    for (int q = 0; q < J.n_parts; ++q) { q_off[q] = o; o += WG_GROUPS * J.q[q].gs; }
-  }
+  uint32_t bytes = WG_GROUPS * 2048;
+  for (int q = 0; q < J.n_parts; ++q) { q_off[q] = bytes; bytes += WG_GROUPS * J.q[q].gs; }
+  const uint32_t p2_off = bytes;
+  if (J.p2_on) bytes += WG_GROUPS * J.p2_gs;
+  const uint32_t n_slots = min((uint32_t)WG_MAX_RING, WG_RING_BYTES / bytes);
   if (!active) {
     // nothing to do (fewer rays than splits): fall through to the closing cluster barrier
   } else if (warp == 4) {
     // producer: lane 0 arms the barrier, then lanes 0..(copies-1) each issue one bulk copy.  In a shared pair each rank
     // fetches half of the row groups of every Q part and multicasts them to both CTAs.
     uint32_t slot = 0, phase = 0;
-    uint32_t bytes = WG_GROUPS * 2048;
-    for (int q = 0; q < J.n_parts; ++q) bytes += WG_GROUPS * J.q[q].gs;
     const uint8_t *pbase = (J.p_ws ? A.ws_bwd : A.ws_fwd) + J.p_slot_off + (J.p_col0 >> 3) * 128;
     const size_t pstride = J.p_ws ? BWD_TILE_BYTES : FWD_TILE_BYTES;
     const bool p_contig = (J.p_gs == 2048);
@@ -1107,7 +1117,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(192, 1) tc_wgrad_ker
           mbar_arrive_expect_tx(bar_full + 8 * slot, bytes);
         }
         __syncwarp();
-        const uint32_t dst = sbase + SW_RING + slot * WG_SLOT;
+        const uint32_t dst = sbase + SW_RING + slot * bytes;
         if (lane < n_pcopies) {
           if (p_contig) bulk_g2s(dst, pbase + (size_t)t * pstride + (size_t)(WG_GROUPS * sub) * 2048, WG_GROUPS * 2048, bar_full + 8 * slot);
           else bulk_g2s(dst + lane * 2048, pbase + (size_t)t * pstride + (size_t)(WG_GROUPS * sub + lane) * J.p_gs, 2048, bar_full + 8 * slot);
@@ -1117,9 +1127,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(192, 1) tc_wgrad_ker
           const uint8_t *srcp = qb + (size_t)(WG_GROUPS * sub + qg0) * J.q[q].gs;
           if (shared) bulk_g2s_mc(dst + q_off[q] + qg0 * J.q[q].gs, srcp, qgn * J.q[q].gs, bar_full + 8 * slot, mc_mask);
           else bulk_g2s(dst + q_off[q], srcp, qgn * J.q[q].gs, bar_full + 8 * slot);
+        } else if (lane == n_pcopies + J.n_parts && J.p2_on) {
+          const uint8_t *pb = (J.p2_ws ? A.ws_bwd + (size_t)t * BWD_TILE_BYTES : A.ws_fwd + (size_t)t * FWD_TILE_BYTES) + J.p2_slot_off;
+          bulk_g2s(dst + p2_off, pb + (size_t)(WG_GROUPS * sub) * J.p2_gs, WG_GROUPS * J.p2_gs, bar_full + 8 * slot);
         }
         __syncwarp();
-        if (++slot == WG_RING) { slot = 0; phase ^= 1; }
+        if (++slot == n_slots) { slot = 0; phase ^= 1; }
       }
   } else if (warp == 5) {
     if (elect_one()) {
@@ -1131,22 +1144,26 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(192, 1) tc_wgrad_ker
         qtm[q] = tmem + (q < J.n_parts ? J.q[q].tm_col : 0);
       }
       const int n_parts = J.n_parts;
+      const bool p2_on = J.p2_on != 0;
+      const uint32_t p2_gs = J.p2_gs, p2_tm = tmem + J.p2_tm_col, p2_idesc = idesc_bf16(128, p2_on ? J.p2_n : 16, 1, 1);
+      const uint32_t p2_b = p2_on ? q_off[J.p2_q] + (J.p2_qcol0 >> 3) * 128u : 0, p2_bgs = p2_on ? J.q[J.p2_q].gs : 0;
       for (int t = t0; t < t1; ++t)
         for (int sub = 0; sub < WG_SUB; ++sub) {
           mbar_wait(bar_full + 8 * slot, phase);
           tc_fence_after();
-          const uint32_t src = sbase + SW_RING + slot * WG_SLOT;
+          const uint32_t src = sbase + SW_RING + slot * bytes;
 #pragma unroll
           for (int ks = 0; ks < WG_GROUPS / 2; ++ks) {
             const uint64_t pd = desc_mnmajor(src + ks * 4096, 2048);
 #pragma unroll
             for (int q = 0; q < 3; ++q)
               if (q < n_parts) umma(qtm[q], pd, desc_mnmajor(src + q_off[q] + ks * 2 * qgs[q], qgs[q]), qn_idesc[q], accum);
+            if (p2_on) umma(p2_tm, desc_mnmajor(src + p2_off + ks * 2 * p2_gs, p2_gs), desc_mnmajor(src + p2_b + ks * 2 * p2_bgs, p2_bgs), p2_idesc, accum);
             accum = 1;
           }
           if (shared) umma_commit_mc(bar_empty + 8 * slot, mc_mask);   // the slot is free once BOTH consumers are done
           else umma_commit(bar_empty + 8 * slot);
-          if (++slot == WG_RING) { slot = 0; phase ^= 1; }
+          if (++slot == n_slots) { slot = 0; phase ^= 1; }
         }
       umma_commit(bar_done);
     }
@@ -1155,32 +1172,49 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(192, 1) tc_wgrad_ker
     // flush: thread = output row m (lane of TMEM), red.add into the fp32 gradient tensors
     mbar_wait(bar_done, 0);
     tc_fence_after();
+    if (A.trace && threadIdx.x == 0) A.trace[1024 + 4 * blockIdx.x + 1] = globaltimer_ns();
     const int m = warp * 32 + lane;
     for (int sgi = 0; sgi < J.n_segs; ++sgi) {
       const WgSeg sg = J.seg[sgi];
+      if (sg.m_n && (warp * 32 + 32 <= sg.m0 || warp * 32 >= sg.m0 + sg.m_n)) continue;   // no row of this warp (warp-uniform)
+      const bool row_on = !sg.m_n || (m >= sg.m0 && m < sg.m0 + sg.m_n);   // the TMEM loads below stay warp-wide
       float *dst = A.d_params[sg.param] + sg.offset + (size_t)m * sg.stride_m;
+      // rows of 256-wide weights are 16-byte aligned: four columns per reduction instead of one
+      const bool vec4 = sg.stride_n == 1 && (sg.count & 31) == 0 && (sg.stride_m & 3) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
       for (int c0 = 0; c0 < sg.count; c0 += 32) {
         uint32_t v[32];
         tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + sg.tm_col + c0, v);
         tmem_ld_wait();
+        if (!row_on) continue;
+        if (vec4) {
 #pragma unroll
-        for (int k = 0; k < 32; ++k)
-          if (c0 + k < sg.count) atomicAdd(dst + (size_t)(c0 + k) * sg.stride_n, __uint_as_float(v[k]));
+          for (int k = 0; k < 32; k += 4)
+            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + c0 + k), "f"(__uint_as_float(v[k])),
+                         "f"(__uint_as_float(v[k + 1])), "f"(__uint_as_float(v[k + 2])), "f"(__uint_as_float(v[k + 3]))
+                         : "memory");
+        } else {
+#pragma unroll
+          for (int k = 0; k < 32; ++k)
+            if (c0 + k < sg.count) atomicAdd(dst + (size_t)(c0 + k) * sg.stride_n, __uint_as_float(v[k]));
+        }
       }
     }
   }
   tc_fence_before();
   __syncthreads();
+  if (A.trace && threadIdx.x == 0) A.trace[1024 + 4 * blockIdx.x + 2] = globaltimer_ns();
   if (warp == 5 && active) tmem_dealloc(tmem, 512);
   cluster_sync_all();   // neither CTA leaves while the other may still signal its barriers
 }
 
 struct WgPlan { std::vector<WgJob> jobs; int n_ctas = 0; };
 
-// Job pairs (entry 2p = cluster rank 0, 2p+1 = rank 1).  Cluster counts are proportional to the bytes a pair streams per
-// ray (the kernel is memory-bound) and sum to 148 = one 2-CTA cluster per SM pair:
-//   7 x {15,15,15,14,14,14,14} (256-wide layers + fc_feature, 136 KB/ray) + 16 (layers1.0, 152 KB) + 9 (layers0.0, 88 KB)
-//   + 7 (fc_density, 68 KB) + 11 (rgb_layers.0, 104 KB) + 4 (fc_rgb, 36 KB)
+// Job pairs (entry 2p = cluster rank 0, 2p+1 = rank 1).  The kernel keeps one CTA per SM (512 TMEM columns, 184 KB of
+// shared memory), so 74 two-CTA clusters are resident at once: the cluster counts sum to 74 and are proportional to the
+// bytes a pair streams per ray (the kernel is memory-bound), so that every cluster starts at t = 0 and ends together:
+//   7 x 8 (256-wide layers; fc_feature, which also carries fc_density's product) + 8 (layers1.0) + 4 (layers0.0)
+//   + 4 (rgb_layers.0) + 2 (fc_rgb).  A CTA's share of a saturated memory system follows the bytes its ring keeps in flight,
+//   hence the counts follow (bytes per ray / ring bytes), not bytes alone (tools/trace_wgrad.py prints the finish times).
 WgPlan build_wg_plan() {
   WgPlan P;
   int n_clusters = 0;
@@ -1195,7 +1229,7 @@ WgPlan build_wg_plan() {
     P.jobs.push_back(J1);
   };
   int big_i = 0;
-  const int big_clusters[7] = {15, 15, 15, 14, 14, 14, 14};
+  const int big_clusters[7] = {8, 8, 8, 8, 8, 8, 8};
   for (int L = 0; L < 8; ++L) {
     WgJob H[2];
     for (int h = 0; h < 2; ++h) {
@@ -1228,7 +1262,7 @@ WgPlan build_wg_plan() {
       }
       H[h] = J;
     }
-    push_pair(H[0], H[1], 1, L == 0 ? 9 : (L == 4 ? 16 : big_clusters[big_i++]));
+    push_pair(H[0], H[1], 1, L == 0 ? 4 : (L == 4 ? 8 : big_clusters[big_i++]));
   }
   {  // fc_feature
     WgJob H[2];
@@ -1241,22 +1275,15 @@ WgPlan build_wg_plan() {
       J.n_segs = 2;
       J.seg[0] = seg(P_FEAT, 128 * h * 256, 256, 1, 0, 256);
       J.seg[1] = seg(P_FEAT + 1, 128 * h, 1, 1, 256 + 27, 1);
+      // fc_density weight rides along: sum_s d_raw_den[s] * H7[s][128h + n] (row 3 of the 16-column head-gradient image)
+      J.p2_on = 1; J.p2_ws = 1; J.p2_slot_off = BW_DSMALL; J.p2_gs = 256;
+      J.p2_q = 0; J.p2_qcol0 = (uint16_t)(128 * h); J.p2_n = 128; J.p2_tm_col = 288;
+      J.n_segs = 3;
+      J.seg[2] = seg(P_DEN, 128 * h, 0, 1, 288, 128);
+      J.seg[2].m0 = 3; J.seg[2].m_n = 1;
       H[h] = J;
     }
     push_pair(H[0], H[1], 1, big_clusters[big_i++]);
-  }
-  {  // fc_density weight: sum_s H7[s][m] * d_raw_den[s]
-    WgJob H[2];
-    for (int h = 0; h < 2; ++h) {
-      WgJob J{};
-      J.p_ws = 0; J.p_slot_off = FW_H + 7 * 65536u; J.p_gs = 4096; J.p_col0 = 128 * h;
-      J.n_parts = 1;
-      J.q[0] = part(1, BW_DSMALL, 256, 16, 0);
-      J.n_segs = 1;
-      J.seg[0] = seg(P_DEN, 128 * h, 1, 1, 3, 1);
-      H[h] = J;
-    }
-    push_pair(H[0], H[1], 1, 7);
   }
   {  // rgb_layers.0: input [feat(256), dir_enc(27)]; one 128-row block, the two ranks split the rays
     WgJob J{};
@@ -1268,7 +1295,7 @@ WgPlan build_wg_plan() {
     J.seg[0] = seg(P_RGB0, 0, 283, 1, 0, 256);
     J.seg[1] = seg(P_RGB0, 256, 283, 1, 256, 27);
     J.seg[2] = seg(P_RGB0 + 1, 0, 1, 1, 256 + 27, 1);
-    push_pair(J, J, 0, 11);
+    push_pair(J, J, 0, 4);
   }
   {  // fc_rgb weight (3,128): sum_s Hc[s][m] * d_raw_rgb[s][c]
     WgJob J{};
@@ -1277,7 +1304,7 @@ WgPlan build_wg_plan() {
     J.q[0] = part(1, BW_DSMALL, 256, 16, 0);
     J.n_segs = 1;
     J.seg[0] = seg(P_RGB, 0, 1, 128, 0, 3);
-    push_pair(J, J, 0, 4);
+    push_pair(J, J, 0, 2);
   }
   P.n_ctas = 2 * n_clusters;
   return P;
@@ -1497,6 +1524,7 @@ int nnb_tc_render_bwd(const nnb_render_cfg *cfg, const float *const *params, con
   NNB_CHECK_LAUNCH();
   WgArgs W{};
   W.ws_fwd = B.ws_fwd; W.ws_bwd = B.ws_bwd;
+  W.trace = g_trace;
   for (int i = 0; i < NNB_NUM_PARAMS; ++i) W.d_params[i] = d_params[i];
   W.n_tiles = R; W.n_jobs = (int)wg_plan().jobs.size();
   tc_wgrad_kernel<<<wg_plan().n_ctas, 192, SW_TOTAL, s>>>(W);

@@ -148,7 +148,7 @@ def test_tc_full_size_properties_cfg2():
     assert torch.equal(rgb_p, rgb[perm]) and torch.equal(dist_p, dist[perm]) and torch.equal(w_p, w[perm])
     assert torch.equal(dd_p, dd)   # d.grad is scattered back through the index: same rows, same bits
     for a, b in zip(dp, dp_p):
-        assert max_err(b, a) <= 1e-5 * float(a.abs().max()) + 1e-9
+        assert max_err(b, a) <= 5e-5 * float(a.abs().max()) + 1e-9   # fp32 sums over 524,288 samples in another order
     # (3) linearity in the upstream gradient
     _, _, _, dd2, do2, dp2 = run(scale=2.0)
     assert torch.equal(dd2, 2 * dd)              # per-ray gradients: no cross-CTA accumulation, bit for bit
