@@ -108,8 +108,12 @@ class Loss(nn.Module):
             loss_dist_1st, loss_dist_2nd = self.get_weight_dist_loss(t_list)
         else:
             loss_dist_1st, loss_dist_2nd = zero, zero
-        pc_loss = self.get_pc_loss(X, Y) if weights['pc_weight'] != 0.0 else zero
-        rgb_s_loss = self.get_rgb_s_loss(rgb_pc1, rgb_pc1_proj, valid_points) if weights['rgb_s_weight'] != 0.0 else zero
+        # 'pc_loss_pre' / 'rgb_s_loss_pre': the same two calls, already made by the trainer on its reference-frame stream
+        pc_loss, rgb_s_loss = kwargs.get('pc_loss_pre'), kwargs.get('rgb_s_loss_pre')
+        if pc_loss is None:
+            pc_loss = self.get_pc_loss(X, Y) if weights['pc_weight'] != 0.0 else zero
+        if rgb_s_loss is None:
+            rgb_s_loss = self.get_rgb_s_loss(rgb_pc1, rgb_pc1_proj, valid_points) if weights['rgb_s_weight'] != 0.0 else zero
         if weights['depth_consistency_weight'] != 0.0:
             depth_consistency_loss = self.get_depth_consistency_loss(d1_proj, d2, d2_proj, d1)
         else:

@@ -7,6 +7,7 @@ C-ABI kernels:  pose exp-map, 4x4 inverse, distortion, fused ray gather, ray gen
 point-cloud back-projection, reprojection sampling and the loss kernels.  Multi-GPU: every rank draws the same
 global ray batch and takes its contiguous shard; gradients are averaged with ONE flat NCCL allreduce (parallel.py).
 """
+import contextlib
 import logging
 
 import torch
@@ -26,6 +27,8 @@ class Trainer(object):
         self.model = model
         self.optimizer = optimizer
         self.device = device
+        self.fork_geometry = True   # train_step_graphed: reference-frame branch as a parallel branch of the graph
+        self._geom_stream = None    # set while train_step_graphed warms up and captures: forks the reference-frame branch
         self.optimizer_pose = optimizer_pose
         self.pose_param_net = pose_param_net
         self.focal_net = focal_net
@@ -143,11 +146,19 @@ class Trainer(object):
             static['img.ref_idxs_dev'] = data['img.ref_idxs'].reshape(1).to(dev)
         params = [p for m in self._all_nets() for p in m.parameters() if p.requires_grad]
 
+        geom = torch.cuda.Stream() if self.fork_geometry else None
+
         def body():
             for p in params:
                 p.grad = None
-            ld = self.compute_loss(static, it=it, epoch=epoch, scheduling_start=scheduling_start)
-            ld['loss'].backward()
+            self._geom_stream = geom
+            try:
+                ld = self.compute_loss(static, it=it, epoch=epoch, scheduling_start=scheduling_start)
+                ld['loss'].backward()
+                if geom is not None:
+                    torch.cuda.current_stream().wait_stream(geom)   # nothing of the branch is left unjoined when capture ends
+            finally:
+                self._geom_stream = None
             return ld
 
         warn = getattr(torch.autograd.graph, 'set_warn_on_accumulate_grad_stream_mismatch', None)
@@ -260,6 +271,70 @@ class Trainer(object):
         pixels, rgb_gt, depth_sel = _ops.GatherRays.apply(ray_idx_local, img[0], depth_raw[0, 0], ss_in, h, w)
         rgb_gt = rgb_gt.unsqueeze(0)
 
+        # The reference-frame branch (point clouds, Chamfer, reprojection: model/training.py:318-372) depends on the depth maps,
+        # poses and distortion parameters only, not on the rendered rays.  It is issued BEFORE the render so that, when a second
+        # stream is set (train_step_graphed), its many small launches become a parallel branch of the captured graph and run
+        # beside the persistent render kernels, in the forward and (autograd replays each node on its forward stream) the
+        # backward pass.  Neither branch draws random numbers, so the RNG order (randperm, then rand) is unchanged.
+        geom = self._geom_stream if use_ref_imgs else None
+        if use_ref_imgs:
+            main_stream = torch.cuda.current_stream() if geom is not None else None
+            if geom is not None:
+                geom.wait_stream(main_stream)
+            with (torch.cuda.stream(geom) if geom is not None else contextlib.nullcontext()):
+                ref_idx_i = int(ref_idx)
+                c2w_ref = self.pose_param_net(ref_idx_i, ref_idx_dev)
+                ss_ref = self.distortion_net.scale_shift(ref_idx_i, ref_idx_dev) if self.distortion_net is not None else None
+                if self.detach_ref_img:
+                    c2w_ref = c2w_ref.detach()
+                    ss_ref = ss_ref.detach() if ss_ref is not None else None
+                if img_idx_i < (num_cams - 1):
+                    d1_raw, d2_raw, ss1, ss2 = depth_raw, depth_ref_raw, ss_in, ss_ref
+                    img1, img2 = img, ref_img
+                    # ref_Rt @ inverse(world_mat) with inverse(world_mat) == c2w (model/training.py:329)
+                    Rt_rel_12 = _ops.Mat4Inverse.apply(c2w_ref) @ c2w
+                else:
+                    d1_raw, d2_raw, ss1, ss2 = depth_ref_raw, depth_raw, ss_ref, ss_in
+                    img1, img2 = ref_img, img
+                    Rt_rel_12 = world_mat[0] @ c2w_ref                 # world_mat @ inverse(ref_Rt) (model/training.py:344)
+                R_rel_12 = Rt_rel_12[:3, :3]
+                t_rel_12 = Rt_rel_12[:3, 3]
+                scale1 = ss1[0] if ss1 is not None else None
+
+                ratio = self.pc_ratio
+                h4, w4 = int(h_depth / ratio), int(w_depth / ratio)
+                pc1 = _ops.Backproject.apply(d1_raw, ss1, camera_mat, h4, w4, nl)   # (P,3)
+                pc2 = _ops.Backproject.apply(d2_raw, ss2, camera_mat, h4, w4, nl)
+
+                if weights['rgb_s_weight'] != 0.0:
+                    img1r = _ops.resize_bilinear(img1[0], h4, w4)
+                    img2r = _ops.resize_bilinear(img2[0], h4, w4)
+                    pc1_in = pc1.detach() if self.detach_rgbs_scale else pc1
+                    rgb_pc1, rgb_pc1_proj, valid = _ops.Reproject.apply(img1r, img2r, pc1_in, R_rel_12, t_rel_12, camera_mat, nl)
+                    kwargs['rgb_pc1'] = rgb_pc1.view(batch_size, h4, w4, 3)
+                    kwargs['rgb_pc1_proj'] = rgb_pc1_proj.view(batch_size, h4, w4, 3)
+                    kwargs['valid_points'] = valid.view(batch_size, h4, w4, 1)
+                if self.scale_pcs and scale1 is not None:
+                    pc1 = pc1 / scale1
+                    pc2 = pc2 / scale1
+                kwargs['X'] = (pc1 @ R_rel_12.transpose(0, 1) + t_rel_12).unsqueeze(0)
+                kwargs['Y'] = pc2.unsqueeze(0)
+                kwargs['sample_resolution'] = (h4, w4)
+                kwargs['rt_12'] = Rt_rel_12.unsqueeze(0)
+                if weights['t_cycle_weight'] != 0.0:
+                    world_mat_gt = torch.inverse(pose_gt).unsqueeze(0)
+                    ref_Rt_gt = torch.inverse(ref_pose_gt).unsqueeze(0)
+                    if img_idx_i < (num_cams - 1):
+                        kwargs['rt_12_gt'] = ref_Rt_gt @ torch.inverse(world_mat_gt)
+                    else:
+                        kwargs['rt_12_gt'] = world_mat_gt @ torch.inverse(ref_Rt_gt)
+                if geom is not None:
+                    # the two losses of this branch are evaluated here, on its stream (model/losses.py:111-112)
+                    if weights['pc_weight'] != 0.0:
+                        kwargs['pc_loss_pre'] = self.loss.get_pc_loss(kwargs['X'], kwargs['Y'])
+                    if weights['rgb_s_weight'] != 0.0:
+                        kwargs['rgb_s_loss_pre'] = self.loss.get_rgb_s_loss(kwargs['rgb_pc1'], kwargs['rgb_pc1_proj'], kwargs['valid_points'])
+
         out_dict = None
         if render_model:
             renderer = self.model.renderer
@@ -281,54 +356,8 @@ class Trainer(object):
         else:
             rendered_rgb = rendered_depth = gt_depth = None
 
-        if use_ref_imgs:
-            ref_idx_i = int(ref_idx)
-            c2w_ref = self.pose_param_net(ref_idx_i, ref_idx_dev)
-            ss_ref = self.distortion_net.scale_shift(ref_idx_i, ref_idx_dev) if self.distortion_net is not None else None
-            if self.detach_ref_img:
-                c2w_ref = c2w_ref.detach()
-                ss_ref = ss_ref.detach() if ss_ref is not None else None
-            if img_idx_i < (num_cams - 1):
-                d1_raw, d2_raw, ss1, ss2 = depth_raw, depth_ref_raw, ss_in, ss_ref
-                img1, img2 = img, ref_img
-                # ref_Rt @ inverse(world_mat) with inverse(world_mat) == c2w (model/training.py:329)
-                Rt_rel_12 = _ops.Mat4Inverse.apply(c2w_ref) @ c2w
-            else:
-                d1_raw, d2_raw, ss1, ss2 = depth_ref_raw, depth_raw, ss_ref, ss_in
-                img1, img2 = ref_img, img
-                Rt_rel_12 = world_mat[0] @ c2w_ref                 # world_mat @ inverse(ref_Rt) (model/training.py:344)
-            R_rel_12 = Rt_rel_12[:3, :3]
-            t_rel_12 = Rt_rel_12[:3, 3]
-            scale1 = ss1[0] if ss1 is not None else None
-
-            ratio = self.pc_ratio
-            h4, w4 = int(h_depth / ratio), int(w_depth / ratio)
-            pc1 = _ops.Backproject.apply(d1_raw, ss1, camera_mat, h4, w4, nl)   # (P,3)
-            pc2 = _ops.Backproject.apply(d2_raw, ss2, camera_mat, h4, w4, nl)
-
-            if weights['rgb_s_weight'] != 0.0:
-                img1r = _ops.resize_bilinear(img1[0], h4, w4)
-                img2r = _ops.resize_bilinear(img2[0], h4, w4)
-                pc1_in = pc1.detach() if self.detach_rgbs_scale else pc1
-                rgb_pc1, rgb_pc1_proj, valid = _ops.Reproject.apply(img1r, img2r, pc1_in, R_rel_12, t_rel_12, camera_mat, nl)
-                kwargs['rgb_pc1'] = rgb_pc1.view(batch_size, h4, w4, 3)
-                kwargs['rgb_pc1_proj'] = rgb_pc1_proj.view(batch_size, h4, w4, 3)
-                kwargs['valid_points'] = valid.view(batch_size, h4, w4, 1)
-            if self.scale_pcs and scale1 is not None:
-                pc1 = pc1 / scale1
-                pc2 = pc2 / scale1
-            kwargs['X'] = (pc1 @ R_rel_12.transpose(0, 1) + t_rel_12).unsqueeze(0)
-            kwargs['Y'] = pc2.unsqueeze(0)
-            kwargs['sample_resolution'] = (h4, w4)
-            kwargs['rt_12'] = Rt_rel_12.unsqueeze(0)
-            if weights['t_cycle_weight'] != 0.0:
-                world_mat_gt = torch.inverse(pose_gt).unsqueeze(0)
-                ref_Rt_gt = torch.inverse(ref_pose_gt).unsqueeze(0)
-                if img_idx_i < (num_cams - 1):
-                    kwargs['rt_12_gt'] = ref_Rt_gt @ torch.inverse(world_mat_gt)
-                else:
-                    kwargs['rt_12_gt'] = world_mat_gt @ torch.inverse(ref_Rt_gt)
-
+        if geom is not None:
+            main_stream.wait_stream(geom)
         if render_model and self.detach_gt_depth:
             gt_depth = gt_depth.detach()
         loss_dict = self.loss(rendered_rgb, rgb_gt, rendered_depth, gt_depth, **kwargs)
