@@ -247,6 +247,14 @@ int nnb_chamfer_err_fwd(const float *X, int n, const float *Y, const int64_t *id
 int nnb_chamfer_err_bwd(const float *X, int n, const float *Y, const int64_t *idx, const float *g_loss,
                         float *d_X, float *d_Y, void *stream);
 
+/* The clouds the Chamfer term compares: model/training.py:394-399.  X = (pc1 / s) R^T + t, Y = pc2 / s with R, t the
+ * rotation and translation of the row-major 4x4 Rt (relative pose) and s = scale[0] (scale == NULL: no division).
+ * Backward overwrites d_pc1 (n1,3), d_pc2 (n2,3), d_Rt (16; last row zero) and d_scale (1). */
+int nnb_align_clouds_fwd(const float *pc1, int n1, const float *pc2, int n2, const float *Rt, const float *scale,
+                         float *X, float *Y, void *stream);
+int nnb_align_clouds_bwd(const float *pc1, int n1, const float *pc2, int n2, const float *Rt, const float *scale,
+                         const float *dX, const float *dY, float *d_pc1, float *d_pc2, float *d_Rt, float *d_scale, void *stream);
+
 /* ------------------------------------------------------------------------------------------
  * Step glue
  * ---------------------------------------------------------------------------------------- */

@@ -188,6 +188,100 @@ __global__ void chamfer_err_bwd_kernel(const float *__restrict__ X, int n, const
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// The two clouds as the Chamfer term sees them (model/training.py:394-399): X = (pc1 / s) R^T + t, Y = pc2 / s.
+// One launch forward; one launch backward that also reduces dR, dt and ds (block partial sums, then 13 atomics per block).
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void align_clouds_fwd_kernel(const float *__restrict__ pc1, int n1, const float *__restrict__ pc2, int n2,
+                                        const float *__restrict__ Rt, const float *__restrict__ scale, float *__restrict__ X,
+                                        float *__restrict__ Y) {
+  const float s = scale ? scale[0] : 1.0f;
+  float R[9], t[3];
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) R[3 * r + c] = Rt[4 * r + c];
+    t[r] = Rt[4 * r + 3];
+  }
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n1 + n2; i += gridDim.x * blockDim.x) {
+    if (i < n1) {
+      // same operation order as the reference: divide, then the (1x3)(3x3) product accumulated left to right, then + t
+      const float q0 = pc1[3 * i] / s, q1 = pc1[3 * i + 1] / s, q2 = pc1[3 * i + 2] / s;
+#pragma unroll
+      for (int r = 0; r < 3; ++r) X[3 * i + r] = fmaf(q2, R[3 * r + 2], fmaf(q1, R[3 * r + 1], q0 * R[3 * r])) + t[r];
+    } else {
+      const int j = i - n1;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) Y[3 * j + c] = pc2[3 * j + c] / s;
+    }
+  }
+}
+
+// acc[0..8] = dR (row-major 3x3), acc[9..11] = dt, acc[12] = ds
+__global__ void __launch_bounds__(256) align_clouds_bwd_kernel(const float *__restrict__ pc1, int n1, const float *__restrict__ pc2,
+                                                               int n2, const float *__restrict__ Rt, const float *__restrict__ scale,
+                                                               const float *__restrict__ dX, const float *__restrict__ dY,
+                                                               float *__restrict__ d_pc1, float *__restrict__ d_pc2,
+                                                               float *__restrict__ d_Rt, float *__restrict__ d_scale) {
+  const float s = scale ? scale[0] : 1.0f, inv = 1.0f / s;
+  float R[9];
+#pragma unroll
+  for (int r = 0; r < 3; ++r)
+#pragma unroll
+    for (int c = 0; c < 3; ++c) R[3 * r + c] = Rt[4 * r + c];
+  float acc[13];
+#pragma unroll
+  for (int k = 0; k < 13; ++k) acc[k] = 0.0f;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n1 + n2; i += gridDim.x * blockDim.x) {
+    if (i < n1) {
+      const float p[3] = {pc1[3 * i], pc1[3 * i + 1], pc1[3 * i + 2]};
+      const float g[3] = {dX[3 * i], dX[3 * i + 1], dX[3 * i + 2]};
+      float dq[3];
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        dq[c] = g[0] * R[c] + g[1] * R[3 + c] + g[2] * R[6 + c];   // R^T dX_i
+        d_pc1[3 * i + c] = dq[c] * inv;
+      }
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) acc[3 * r + c] += g[r] * (p[c] * inv);
+        acc[9 + r] += g[r];
+      }
+      acc[12] -= (dq[0] * p[0] + dq[1] * p[1] + dq[2] * p[2]) * inv * inv;
+    } else {
+      const int j = i - n1;
+      float dot = 0.0f;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const float g = dY[3 * j + c];
+        d_pc2[3 * j + c] = g * inv;
+        dot += g * pc2[3 * j + c];
+      }
+      acc[12] -= dot * inv * inv;
+    }
+  }
+  __shared__ float part[8][13];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < 13; ++k) {
+    float v = acc[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) part[warp][k] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < 13) {
+    float v = 0.0f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) v += part[w][threadIdx.x];
+    const int k = threadIdx.x;
+    if (k < 9) atomicAdd(d_Rt + 4 * (k / 3) + (k % 3), v);
+    else if (k < 12) atomicAdd(d_Rt + 4 * (k - 9) + 3, v);
+    else if (d_scale) atomicAdd(d_scale, v);
+  }
+}
+
 extern "C" {
 
 size_t nnb_chamfer_workspace_bytes(int n_src, int n_dst) {
@@ -264,6 +358,31 @@ int nnb_chamfer_err_bwd(const float *X, int n, const float *Y, const int64_t *id
   const int cap = nnb_sm_count() * 8;
   if (g > cap) g = cap;
   chamfer_err_bwd_kernel<<<g, 256, 0, nnb_stream(stream)>>>(X, n, Y, idx, 1.0f / (float)n, g_loss, d_X, d_Y);
+  NNB_CHECK_LAUNCH();
+  return 0;
+}
+
+int nnb_align_clouds_fwd(const float *pc1, int n1, const float *pc2, int n2, const float *Rt, const float *scale, float *X, float *Y,
+                         void *stream) {
+  if (!pc1 || !pc2 || !Rt || !X || !Y || n1 <= 0 || n2 <= 0) return NNB_ERR_BAD_ARG;
+  int g = nnb_cdiv(n1 + n2, 256);
+  const int cap = nnb_sm_count() * 8;
+  if (g > cap) g = cap;
+  align_clouds_fwd_kernel<<<g, 256, 0, nnb_stream(stream)>>>(pc1, n1, pc2, n2, Rt, scale, X, Y);
+  NNB_CHECK_LAUNCH();
+  return 0;
+}
+
+int nnb_align_clouds_bwd(const float *pc1, int n1, const float *pc2, int n2, const float *Rt, const float *scale, const float *dX,
+                         const float *dY, float *d_pc1, float *d_pc2, float *d_Rt, float *d_scale, void *stream) {
+  if (!pc1 || !pc2 || !Rt || !dX || !dY || !d_pc1 || !d_pc2 || !d_Rt || n1 <= 0 || n2 <= 0 || (scale && !d_scale)) return NNB_ERR_BAD_ARG;
+  cudaStream_t s = nnb_stream(stream);
+  NNB_CUDA(cudaMemsetAsync(d_Rt, 0, 16 * sizeof(float), s));
+  if (d_scale) NNB_CUDA(cudaMemsetAsync(d_scale, 0, sizeof(float), s));
+  int g = nnb_cdiv(n1 + n2, 256 * 4);
+  const int cap = nnb_sm_count();
+  if (g > cap) g = cap;
+  align_clouds_bwd_kernel<<<g, 256, 0, s>>>(pc1, n1, pc2, n2, Rt, scale, dX, dY, d_pc1, d_pc2, d_Rt, d_scale);
   NNB_CHECK_LAUNCH();
   return 0;
 }

@@ -78,6 +78,8 @@ SIGNATURES = {
     "nnb_chamfer_nn": [_p, _i, _p, _i, _p, _p, _p, C.c_size_t, _p],
     "nnb_chamfer_err_fwd": [_p, _i, _p, _p, _p, _p],
     "nnb_chamfer_err_bwd": [_p, _i, _p, _p, _p, _p, _p, _p],
+    "nnb_align_clouds_fwd": [_p, _i, _p, _i, _p, _p, _p, _p, _p],
+    "nnb_align_clouds_bwd": [_p, _i, _p, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p],
     "nnb_adam_step": [_p, _p, _p, _p, _sz, _f, _f, _f, _f, _i, _p],
 }
 _RESTYPE = {"nnb_error_string": C.c_char_p, "nnb_launch_count": C.c_ulonglong, "nnb_render_workspace_bytes": C.c_size_t, "nnb_pack_weights_bytes": C.c_size_t, "nnb_chamfer_workspace_bytes": C.c_size_t,

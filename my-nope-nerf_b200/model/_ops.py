@@ -474,6 +474,30 @@ class ChamferErr(torch.autograd.Function):
         return dX.reshape(ctx.shp[0]), dY.reshape(ctx.shp[1]), None
 
 
+class AlignClouds(torch.autograd.Function):
+    """X = (pc1 / scale) @ R.T + t, Y = pc2 / scale (model/training.py:394-399) with Rt the 4x4 relative pose; scale may be None."""
+
+    @staticmethod
+    def forward(ctx, pc1, pc2, Rt, scale):
+        pc1, pc2, Rt = f32(pc1).reshape(-1, 3), f32(pc2).reshape(-1, 3), f32(Rt).reshape(4, 4)
+        sc = f32(scale).reshape(1) if scale is not None else None
+        X, Y = torch.empty_like(pc1), torch.empty_like(pc2)
+        call("nnb_align_clouds_fwd", ptr(pc1), pc1.shape[0], ptr(pc2), pc2.shape[0], ptr(Rt), ptr(sc), ptr(X), ptr(Y), stream())
+        ctx.save_for_backward(pc1, pc2, Rt, sc)
+        ctx.scale_shape = scale.shape if scale is not None else None
+        return X, Y
+
+    @staticmethod
+    def backward(ctx, dX, dY):
+        pc1, pc2, Rt, sc = ctx.saved_tensors
+        d1, d2 = torch.empty_like(pc1), torch.empty_like(pc2)
+        dRt = _new(Rt, 4, 4)
+        dsc = _new(Rt, 1) if sc is not None else None
+        call("nnb_align_clouds_bwd", ptr(pc1), pc1.shape[0], ptr(pc2), pc2.shape[0], ptr(Rt), ptr(sc), ptr(f32(dX).reshape(-1, 3)),
+             ptr(f32(dY).reshape(-1, 3)), ptr(d1), ptr(d2), ptr(dRt), ptr(dsc), stream())
+        return d1, d2, dRt, (dsc.reshape(ctx.scale_shape) if sc is not None else None)
+
+
 def adam_step(param, grad, exp_avg, exp_avg_sq, lr, beta1, beta2, eps, step):
     call("nnb_adam_step", ptr(param), ptr(grad), ptr(exp_avg), ptr(exp_avg_sq), param.numel(), float(lr), float(beta1), float(beta2),
          float(eps), int(step), stream())

@@ -26,6 +26,7 @@ class Loss(nn.Module):
         self.check_nan = True
         # data-parallel context (set by Trainer): the Chamfer SOURCE points are sharded across ranks
         self.dp = None
+        self._weight_vectors = {}   # (weights of the active terms, device) -> device vector, built once per schedule phase
 
     # -- individual terms (reference method names) ----------------------------------------------
     def get_rgb_full_loss(self, rgb_values, rgb_gt, rgb_loss_type='l2'):
@@ -121,10 +122,20 @@ class Loss(nn.Module):
         t_cycle_loss = self.get_t_cycle_loss(kwargs['rt_12'], kwargs['rt_12_gt']) if weights['t_cycle_weight'] != 0.0 else zero
         rgb_l2_mean = rgb3[2] if rgb3 is not None else zero
 
-        loss = weights['rgb_weight'] * rgb_full_loss + weights['depth_weight'] * depth_loss + \
-            weights['weight_dist_1st_loss'] * loss_dist_1st + weights['weight_dist_2nd_loss'] * loss_dist_2nd + \
-            weights['pc_weight'] * pc_loss + weights['rgb_s_weight'] * rgb_s_loss + \
-            weights['depth_consistency_weight'] * depth_consistency_loss + weights['t_cycle_weight'] * t_cycle_loss
+        # sum_k weight_k * term_k over the active terms (model/losses.py:204-208) as one stack + one dot instead of a chain of
+        # scalar multiplies and adds: two launches forward, one backward
+        named = (('rgb_weight', rgb_full_loss), ('depth_weight', depth_loss), ('weight_dist_1st_loss', loss_dist_1st),
+                 ('weight_dist_2nd_loss', loss_dist_2nd), ('pc_weight', pc_loss), ('rgb_s_weight', rgb_s_loss),
+                 ('depth_consistency_weight', depth_consistency_loss), ('t_cycle_weight', t_cycle_loss))
+        active = [(float(weights[k]), v) for k, v in named if weights[k] != 0.0]
+        if active:
+            wkey = (tuple(w for w, _ in active), str(dev))
+            wvec = self._weight_vectors.get(wkey)
+            if wvec is None:
+                wvec = self._weight_vectors[wkey] = torch.tensor(wkey[0], dtype=torch.float32, device=dev)
+            loss = torch.dot(torch.stack([v.reshape(()) for _, v in active]), wvec)
+        else:
+            loss = zero
         return {
             'loss': loss, 'loss_rgb': rgb_full_loss, 'loss_depth': depth_loss, 'l2_mean': rgb_l2_mean,
             'loss_dist_1st': loss_dist_1st, 'loss_dist_2nd': loss_dist_2nd, 'loss_pc': pc_loss,

@@ -314,11 +314,10 @@ class Trainer(object):
                     kwargs['rgb_pc1'] = rgb_pc1.view(batch_size, h4, w4, 3)
                     kwargs['rgb_pc1_proj'] = rgb_pc1_proj.view(batch_size, h4, w4, 3)
                     kwargs['valid_points'] = valid.view(batch_size, h4, w4, 1)
-                if self.scale_pcs and scale1 is not None:
-                    pc1 = pc1 / scale1
-                    pc2 = pc2 / scale1
-                kwargs['X'] = (pc1 @ R_rel_12.transpose(0, 1) + t_rel_12).unsqueeze(0)
-                kwargs['Y'] = pc2.unsqueeze(0)
+                # X = (pc1 / scale1) @ R^T + t, Y = pc2 / scale1 in one launch (model/training.py:394-399)
+                Xa, Ya = _ops.AlignClouds.apply(pc1, pc2, Rt_rel_12, scale1 if self.scale_pcs else None)
+                kwargs['X'] = Xa.unsqueeze(0)
+                kwargs['Y'] = Ya.unsqueeze(0)
                 kwargs['sample_resolution'] = (h4, w4)
                 kwargs['rt_12'] = Rt_rel_12.unsqueeze(0)
                 if weights['t_cycle_weight'] != 0.0:

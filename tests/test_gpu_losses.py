@@ -239,3 +239,39 @@ def test_backproject_and_reproject_vs_oracle():
     assert_close(ssd.grad, ss.grad, 1e-3, 1e-5, "d scale/shift")
     assert_close(Rd.grad, R_rel.grad, 1e-3, 1e-5, "d R_rel")
     assert_close(td.grad, t_rel.grad, 1e-3, 1e-5, "d t_rel")
+
+
+@pytest.mark.parametrize("n1,n2,use_scale", [(1, 1, True), (777, 1030, True), (28830, 28830, True), (500, 333, False)])
+def test_align_clouds_vs_reference_expression(n1, n2, use_scale):
+    """X = (pc1 / s) @ R^T + t, Y = pc2 / s: the reference's own expression (model/training.py:394-399) evaluated by
+    torch in fp64 on the CPU is the checker, forward and all four gradients."""
+    from model import _ops
+    g = torch.Generator().manual_seed(3 + n1)
+    pc1 = torch.randn(n1, 3, generator=g) * 2 + torch.tensor([0.0, 0.0, 4.0])
+    pc2 = torch.randn(n2, 3, generator=g) * 2 + torch.tensor([0.0, 0.0, 4.0])
+    A = torch.linalg.qr(torch.randn(3, 3, generator=g))[0]
+    Rt = torch.eye(4)
+    Rt[:3, :3] = A
+    Rt[:3, 3] = torch.randn(3, generator=g) * 0.1
+    s = torch.tensor(1.3)
+    wX, wY = torch.randn(n1, 3, generator=g), torch.randn(n2, 3, generator=g)
+
+    a1, a2, aRt, asc = [t.double().requires_grad_(True) for t in (pc1, pc2, Rt, s)]
+    q1, q2 = (a1 / asc, a2 / asc) if use_scale else (a1, a2)
+    Xr = q1 @ aRt[:3, :3].transpose(0, 1) + aRt[:3, 3]
+    ((Xr * wX.double()).sum() + (q2 * wY.double()).sum()).backward()
+
+    b1, b2, bRt, bsc = [t.to(dev()).requires_grad_(True) for t in (pc1, pc2, Rt, s)]
+    X, Y = _ops.AlignClouds.apply(b1, b2, bRt, bsc if use_scale else None)
+    ((X * wX.to(dev())).sum() + (Y * wY.to(dev())).sum()).backward()
+    assert_close(X, Xr.float(), 1e-5, 1e-6, "X")
+    assert_close(Y, q2.float(), 1e-5, 1e-6, "Y")
+    assert_close(b1.grad, a1.grad.float(), 1e-5, 1e-6, "d pc1")
+    assert_close(b2.grad, a2.grad.float(), 1e-5, 1e-6, "d pc2")
+    tol = 2e-5 * float(aRt.grad.abs().max()) + 1e-6      # fp32 sums over the points
+    assert_close(bRt.grad, aRt.grad.float(), 1e-4, tol, "d Rt")
+    assert float(bRt.grad[3].abs().max()) == 0.0
+    if use_scale:
+        assert_close(bsc.grad, asc.grad.float(), 1e-4, 2e-5 * float(asc.grad.abs()) + 1e-6, "d scale")
+    else:
+        assert bsc.grad is None
