@@ -253,26 +253,8 @@ class Trainer(object):
         else:
             camera_mat = camera_mat_gt
 
-        # ray choice: same draw as the reference (model/training.py:277); ranks draw the SAME global batch
-        if self.fixed_ray_idx is not None:
-            ray_idx = self.fixed_ray_idx.to(device)
-        else:
-            ray_idx = torch.randperm(h * w, device=device)[:n_points]
-            if data.get('img.dpt') is None:
-                depth_mask_flat = torch.flatten(depth_mask)
-                while not depth_mask_flat[ray_idx].any():
-                    print('No valid depths found, resampling...')
-                    ray_idx = torch.randperm(h * w, device=device)[:n_points]
-        n_global = ray_idx.numel()
-        lo, hi = self.dp.shard(n_global)
-        ray_idx_local = ray_idx[lo:hi].contiguous()
-
-        # fused gather: pixels, rgb_gt and depth*scale+shift for the selected rays only
-        pixels, rgb_gt, depth_sel = _ops.GatherRays.apply(ray_idx_local, img[0], depth_raw[0, 0], ss_in, h, w)
-        rgb_gt = rgb_gt.unsqueeze(0)
-
         # The reference-frame branch (point clouds, Chamfer, reprojection: model/training.py:318-372) depends on the depth maps,
-        # poses and distortion parameters only, not on the rendered rays.  It is issued BEFORE the render so that, when a second
+        # poses and distortion parameters only, not on the rendered rays.  It is issued BEFORE the ray choice and the render so that, when a second
         # stream is set (train_step_graphed), its many small launches become a parallel branch of the captured graph and run
         # beside the persistent render kernels, in the forward and (autograd replays each node on its forward stream) the
         # backward pass.  Neither branch draws random numbers, so the RNG order (randperm, then rand) is unchanged.
@@ -333,6 +315,24 @@ class Trainer(object):
                         kwargs['pc_loss_pre'] = self.loss.get_pc_loss(kwargs['X'], kwargs['Y'])
                     if weights['rgb_s_weight'] != 0.0:
                         kwargs['rgb_s_loss_pre'] = self.loss.get_rgb_s_loss(kwargs['rgb_pc1'], kwargs['rgb_pc1_proj'], kwargs['valid_points'])
+
+        # ray choice: same draw as the reference (model/training.py:277); ranks draw the SAME global batch
+        if self.fixed_ray_idx is not None:
+            ray_idx = self.fixed_ray_idx.to(device)
+        else:
+            ray_idx = torch.randperm(h * w, device=device)[:n_points]
+            if data.get('img.dpt') is None:
+                depth_mask_flat = torch.flatten(depth_mask)
+                while not depth_mask_flat[ray_idx].any():
+                    print('No valid depths found, resampling...')
+                    ray_idx = torch.randperm(h * w, device=device)[:n_points]
+        n_global = ray_idx.numel()
+        lo, hi = self.dp.shard(n_global)
+        ray_idx_local = ray_idx[lo:hi].contiguous()
+
+        # fused gather: pixels, rgb_gt and depth*scale+shift for the selected rays only
+        pixels, rgb_gt, depth_sel = _ops.GatherRays.apply(ray_idx_local, img[0], depth_raw[0, 0], ss_in, h, w)
+        rgb_gt = rgb_gt.unsqueeze(0)
 
         out_dict = None
         if render_model:
