@@ -99,6 +99,17 @@ int nnb_raygen_bwd(const float *pixels, const float *depth, const float *camera_
                    const float *d_origin, const float *d_d_gt, float *d_depth, float *d_camera_mat,
                    float *d_world_mat, float *d_scale_mat, float *scratch16, void *stream);
 
+/* NDC ray warp, get_ndc_rays_fxfy (model/common.py:632-675) as called by Renderer.sample_ndc
+ * (model/rendering.py:169-181): focal = {camera_mat[0][0], camera_mat[1][1]}, near plane `near_` (1.0 there).
+ * origin (3,) shared camera centre, dirs (R,3) -> ndc_o (R,3), ndc_d (R,3). */
+int nnb_ndc_rays_fwd(const float *camera_mat, float near_, const float *origin, const float *dirs, int n_rays,
+                     float *ndc_o, float *ndc_d, void *stream);
+/* d_ndc_o / d_ndc_d (R,3) (either may be NULL = zero) -> d_origin_rows (R,3) per-ray gradient of the shared
+ * origin (the caller sums the rows), d_dirs (R,3), d_fxfy (2,) overwritten (gradient of the two focal entries). */
+int nnb_ndc_rays_bwd(const float *camera_mat, float near_, const float *origin, const float *dirs, int n_rays,
+                     const float *d_ndc_o, const float *d_ndc_d, float *d_origin_rows, float *d_dirs,
+                     float *d_fxfy, void *stream);
+
 /* ------------------------------------------------------------------------------------------
  * Stages 2+3 -- stratified sampling, positional encoding, NeRF MLP, alpha compositing
  * ---------------------------------------------------------------------------------------- */
@@ -142,6 +153,29 @@ int nnb_render_bwd(const nnb_render_cfg *cfg, const float *const *params_host, c
                    const float *z_vals, const float *d_rgb, const float *d_dist, const float *d_alpha_out,
                    const float *d_weights_out, float *const *d_params_host, float *d_origin, float *d_dirs,
                    void *workspace, size_t workspace_bytes, void *stream);
+
+/* Per-ray extras for the sampling branches whose rays do not share one origin (`sample_ndc`,
+ * model/rendering.py:169-181 + get_ndc_rays_fxfy model/common.py:632-675): the sample points are
+ * ray_origins[r] + dirs[r] * z while the view-direction encoding still sees -view_dirs[r].
+ * NULL members fall back to the shared `origin` / to `dirs`.  The d_* members are backward outputs
+ * ((R,3), overwritten) and are required exactly when their input is given. */
+typedef struct {
+  const float *ray_origins; /* (R,3) or NULL */
+  const float *view_dirs;   /* (R,3) or NULL */
+  float *d_ray_origins;     /* (R,3) or NULL */
+  float *d_view_dirs;       /* (R,3) or NULL */
+} nnb_ray_extras;
+
+/* nnb_render_fwd / nnb_render_bwd with the extras above (ex == NULL: identical to the plain calls). */
+int nnb_render_fwd_ex(const nnb_render_cfg *cfg, const float *const *params_host, const void *packed,
+                      const float *origin, const float *dirs, const nnb_ray_extras *ex, const float *noise,
+                      float *rgb, float *dist, float *weights, float *alpha, float *z_vals, void *workspace,
+                      size_t workspace_bytes, int save_for_backward, void *stream);
+int nnb_render_bwd_ex(const nnb_render_cfg *cfg, const float *const *params_host, const void *packed,
+                      const float *origin, const float *dirs, const nnb_ray_extras *ex, const float *weights,
+                      const float *alpha, const float *z_vals, const float *d_rgb, const float *d_dist,
+                      const float *d_alpha_out, const float *d_weights_out, float *const *d_params_host,
+                      float *d_origin, float *d_dirs, void *workspace, size_t workspace_bytes, void *stream);
 
 /* Stand-alone stage 3 (model/rendering.py:116-126,139-141), used by tests and by callers that bring
  * their own per-sample rgb/alpha.  alpha (R,S) [sigma if dist_alpha], rgb_s (R,S,3), z (R,S). */

@@ -374,11 +374,12 @@ constexpr uint32_t GS_ACT = 4096, GS_ENC = 1024, GS_AUX = 512;  // GS_AUX: strid
 struct FwdArgs {
   const uint8_t *wimg;
   const float *origin, *dirs, *noise;
+  const float *ray_o, *view;   // optional per-ray origins (R,3) / view directions (R,3) (NDC sampling); NULL: origin / dirs
   const float *w_den, *b_den, *w_rgb, *b_rgb;
   float *rgb, *dist, *weights, *alpha, *z_vals;
   int n_rays, S, n_stages;
   float near_, far_;
-  int softplus, white, use_dir;
+  int softplus, white, use_dir, dist_alpha;
   uint8_t *ws_fwd;   // SAVE: per-ray activation images (FWD_TILE_BYTES each)
   float4 *ws_s;      // SAVE: per-sample {rgb_s, raw density}
   long long *trace;  // debug: per-layer clock64 stamps of CTA 0 (nnb_debug_set_trace), else NULL
@@ -575,8 +576,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1) tc_fwd_kerne
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
           const float d = A.dirs[3 * ray + c];
-          p[c] = __fadd_rn(A.origin[c], __fmul_rn(d, z));
-          v[c] = A.use_dir ? -d : 1.0f;
+          p[c] = __fadd_rn(A.ray_o ? A.ray_o[3 * ray + c] : A.origin[c], __fmul_rn(d, z));
+          v[c] = A.use_dir ? -(A.view ? A.view[3 * ray + c] : d) : 1.0f;
         }
         if (SAVE && valid) write_encodings<true>(enc_row, aux_row, row < 8, gtile + FW_ENC + (row >> 3) * GS_ENC + (row & 7) * 16,
                                                  gtile + FW_AUX + (row >> 3) * GS_AUX + (row & 7) * 16, p, v);
@@ -640,7 +641,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1) tc_fwd_kerne
             const float raw = (ds0 + ds1) + (ds2 + ds3) + sm_small[0];
             raw_den = raw;
             const float d = A.softplus ? (raw > 20.f ? raw : log1pf(expf(raw))) : fmaxf(raw, 0.f);
-            alpha = 1.f - expf(-d);
+            if (!A.dist_alpha) {
+              alpha = 1.f - expf(-d);
+            } else if (row == A.S - 1) {
+              alpha = 1.f;   // model/rendering.py:122
+            } else {
+              // model/rendering.py:116-121: alpha = 1 - exp(-sigma * (z[i+1] - z[i]))
+              const float zn = z_sample(row + 1, A.S, A.near_, A.far_, A.noise ? A.noise + (size_t)ray * A.S : nullptr);
+              alpha = 1.f - expf(__fmul_rn(-d, __fsub_rn(zn, z)));
+            }
           }
           fence_async_smem();
           tc_fence_before();
@@ -745,11 +754,13 @@ struct BwdArgs {
   uint8_t *ws_bwd;           // dY images (output)
   const float4 *ws_s;        // per-sample {rgb_s, raw}
   const float *origin, *dirs, *alpha, *z_vals;
+  const float *ray_o, *view;   // as in FwdArgs
   const float *d_rgb, *d_dist, *d_alpha_out, *d_weights_out;
   const float *w_rgb;
   float *d_origin, *d_dirs, *d_b_den, *d_b_rgb;   // d_origin / d_b_*: atomically accumulated
+  float *d_ray_o, *d_view;     // per-ray gradients when ray_o / view are given
   int n_rays, n_stages;
-  int softplus, white, use_dir;
+  int softplus, white, use_dir, dist_alpha;
 };
 
 __device__ __forceinline__ uint4 ld_global_v4(const void *p) {
@@ -878,7 +889,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1) tc_bwd_kerne
       float dalpha = g * T - G / beta;
       if (A.d_alpha_out && valid) dalpha += A.d_alpha_out[m];
       const float dact = A.softplus ? (sv.w > 20.f ? 1.f : 1.f / (1.f + expf(-sv.w))) : (sv.w > 0.f ? 1.f : 0.f);
-      const float dr_den = dalpha * (1.f - alpha) * dact;
+      float dr_den = dalpha * (1.f - alpha) * dact;
+      if (A.dist_alpha) dr_den = (row == 127) ? 0.f : dr_den * __fsub_rn(A.z_vals[m + 1], z);   // d alpha / d sigma = delta * exp(-sigma delta)
       const float dr0 = w * g0 * sv.x * (1.f - sv.x), dr1 = w * g1 * sv.y * (1.f - sv.y), dr2 = w * g2 * sv.z * (1.f - sv.z);
       {
         const uint32_t ds = sbase + SB_DSMALL + t * 4096u + (row >> 3) * 256u + (row & 7) * 16u;
@@ -921,8 +933,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1) tc_bwd_kerne
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
         const float d = A.dirs[3 * ray + c];
-        xp[c] = __fadd_rn(A.origin[c], __fmul_rn(d, z));
-        xv[c] = -d;
+        xp[c] = __fadd_rn(A.ray_o ? A.ray_o[3 * ray + c] : A.origin[c], __fmul_rn(d, z));
+        xv[c] = -(A.view ? A.view[3 * ray + c] : d);
       }
       // ---- the chain: 12 accumulator epilogues
       const uint8_t kind[12] = {EPI_DIR, EPI_FEAT, EPI_MASK, EPI_MASK, EPI_MASK, EPI_MASK, EPI_ENC, EPI_MASK, EPI_MASK, EPI_MASK, EPI_MASK, EPI_ENC};
@@ -983,19 +995,32 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1) tc_bwd_kerne
       // ---- per-ray reductions: d_dirs, and the CTA-level accumulators (d_origin, head biases)
       float r[10];
       r[0] = d_p[0]; r[1] = d_p[1]; r[2] = d_p[2];
-      r[3] = z * d_p[0] - d_v[0]; r[4] = z * d_p[1] - d_v[1]; r[5] = z * d_p[2] - d_v[2];
+      r[3] = z * d_p[0]; r[4] = z * d_p[1]; r[5] = z * d_p[2];
+      if (!A.view) { r[3] -= d_v[0]; r[4] -= d_v[1]; r[5] -= d_v[2]; }
       r[6] = dr_den; r[7] = dr0; r[8] = dr1; r[9] = dr2;
 #pragma unroll
       for (int k = 0; k < 10; ++k) {
         r[k] = warp_sum(r[k]);
         if (lane == 0) scan[8 + 4 * k + q] = r[k];
       }
+      if (A.view) {   // separate view directions (NDC sampling): their gradient is its own output
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          const float sv_ = warp_sum(-d_v[k]);
+          if (lane == 0) scan[48 + 4 * k + q] = sv_;
+        }
+      }
       named_bar_sync(1 + t, 128);
       if (row == 0 && valid) {
         float sres[10];
 #pragma unroll
         for (int k = 0; k < 10; ++k) sres[k] = scan[8 + 4 * k] + scan[9 + 4 * k] + scan[10 + 4 * k] + scan[11 + 4 * k];
-        acc_origin[0] += sres[0]; acc_origin[1] += sres[1]; acc_origin[2] += sres[2];
+        if (A.d_ray_o) { A.d_ray_o[3 * ray] = sres[0]; A.d_ray_o[3 * ray + 1] = sres[1]; A.d_ray_o[3 * ray + 2] = sres[2]; }
+        else { acc_origin[0] += sres[0]; acc_origin[1] += sres[1]; acc_origin[2] += sres[2]; }
+        if (A.view && A.d_view) {
+#pragma unroll
+          for (int k = 0; k < 3; ++k) A.d_view[3 * ray + k] = scan[48 + 4 * k] + scan[49 + 4 * k] + scan[50 + 4 * k] + scan[51 + 4 * k];
+        }
         A.d_dirs[3 * ray] = sres[3]; A.d_dirs[3 * ray + 1] = sres[4]; A.d_dirs[3 * ray + 2] = sres[5];
         acc_bias[0] += sres[6]; acc_bias[1] += sres[7]; acc_bias[2] += sres[8]; acc_bias[3] += sres[9];
       }
@@ -1458,10 +1483,10 @@ size_t nnb_tc_workspace_bytes(const nnb_render_cfg *cfg, int save) {
 }
 
 int nnb_tc_render_fwd(const nnb_render_cfg *cfg, const float *const *params, const void *packed, const float *origin,
-                      const float *dirs, const float *noise, float *rgb, float *dist, float *weights, float *alpha, float *z_vals,
+                      const float *dirs, const nnb_ray_extras *ex, const float *noise, float *rgb, float *dist, float *weights, float *alpha, float *z_vals,
                       void *ws, size_t ws_bytes, int save, cudaStream_t s) {
   if (!packed || !params || !origin || !dirs || !rgb || !dist) return NNB_ERR_BAD_ARG;
-  if (cfg->n_samples != 128 || cfg->dist_alpha) return NNB_ERR_UNSUPPORTED;  // tile = one ray of 128 samples
+  if (cfg->n_samples != 128) return NNB_ERR_UNSUPPORTED;  // tile = one ray of 128 samples
   if (cfg->n_rays <= 0) return 0;
   if (save) {
     if (!ws || ws_bytes < nnb_tc_workspace_bytes(cfg, 1)) return NNB_ERR_WORKSPACE;
@@ -1472,11 +1497,12 @@ int nnb_tc_render_fwd(const nnb_render_cfg *cfg, const float *const *params, con
   FwdArgs A{};
   A.wimg = static_cast<const uint8_t *>(packed);
   A.origin = origin; A.dirs = dirs; A.noise = noise;
+  A.ray_o = ex ? ex->ray_origins : nullptr; A.view = ex ? ex->view_dirs : nullptr;
   A.w_den = params[P_DEN]; A.b_den = params[P_DEN + 1]; A.w_rgb = params[P_RGB]; A.b_rgb = params[P_RGB + 1];
   A.rgb = rgb; A.dist = dist; A.weights = weights; A.alpha = alpha; A.z_vals = z_vals;
   A.n_rays = cfg->n_rays; A.S = cfg->n_samples; A.n_stages = (int)fwd_groups().size();
   A.near_ = cfg->near_; A.far_ = cfg->far_;
-  A.softplus = cfg->occ_softplus; A.white = cfg->white_bkgd; A.use_dir = cfg->use_dir;
+  A.softplus = cfg->occ_softplus; A.white = cfg->white_bkgd; A.use_dir = cfg->use_dir; A.dist_alpha = cfg->dist_alpha;
   A.trace = g_trace;
   if (save) {
     A.ws_fwd = static_cast<uint8_t *>(ws);
@@ -1493,12 +1519,13 @@ int nnb_tc_render_fwd(const nnb_render_cfg *cfg, const float *const *params, con
 }
 
 int nnb_tc_render_bwd(const nnb_render_cfg *cfg, const float *const *params, const void *packed, const float *origin,
-                      const float *dirs, const float *weights, const float *alpha, const float *z_vals, const float *d_rgb,
+                      const float *dirs, const nnb_ray_extras *ex, const float *weights, const float *alpha, const float *z_vals, const float *d_rgb,
                       const float *d_dist, const float *d_alpha_out, const float *d_weights_out, float *const *d_params,
                       float *d_origin, float *d_dirs, void *ws, size_t ws_bytes, cudaStream_t s) {
   (void)weights;
   if (!packed || !params || !origin || !dirs || !alpha || !z_vals || !d_params || !d_origin || !d_dirs) return NNB_ERR_BAD_ARG;
-  if (cfg->n_samples != 128 || cfg->dist_alpha) return NNB_ERR_UNSUPPORTED;
+  if (cfg->n_samples != 128) return NNB_ERR_UNSUPPORTED;
+  if (ex && ((ex->ray_origins && !ex->d_ray_origins) || (ex->view_dirs && !ex->d_view_dirs))) return NNB_ERR_BAD_ARG;
   if (!ws || ws_bytes < nnb_tc_workspace_bytes(cfg, 1)) return NNB_ERR_WORKSPACE;
   int e = ensure_tables();
   if (e) return e;
@@ -1511,11 +1538,12 @@ int nnb_tc_render_bwd(const nnb_render_cfg *cfg, const float *const *params, con
   B.ws_fwd = w8; B.ws_bwd = w8 + ws_fwd_bytes(R);
   B.ws_s = reinterpret_cast<const float4 *>(w8 + ws_fwd_bytes(R) + ws_bwd_bytes(R));
   B.origin = origin; B.dirs = dirs; B.alpha = alpha; B.z_vals = z_vals;
+  if (ex) { B.ray_o = ex->ray_origins; B.view = ex->view_dirs; B.d_ray_o = ex->ray_origins ? ex->d_ray_origins : nullptr; B.d_view = ex->d_view_dirs; }
   B.d_rgb = d_rgb; B.d_dist = d_dist; B.d_alpha_out = d_alpha_out; B.d_weights_out = d_weights_out;
   B.w_rgb = params[P_RGB];
   B.d_origin = d_origin; B.d_dirs = d_dirs; B.d_b_den = d_params[P_DEN + 1]; B.d_b_rgb = d_params[P_RGB + 1];
   B.n_rays = R; B.n_stages = (int)bwd_groups().size();
-  B.softplus = cfg->occ_softplus; B.white = cfg->white_bkgd; B.use_dir = cfg->use_dir;
+  B.softplus = cfg->occ_softplus; B.white = cfg->white_bkgd; B.use_dir = cfg->use_dir; B.dist_alpha = cfg->dist_alpha;
   const int n_pairs = (R + 1) / 2;
   int grid = n_pairs < nnb_sm_count() ? n_pairs : nnb_sm_count();
   grid = (grid + 1) & ~1;                       // 2-CTA clusters

@@ -262,6 +262,68 @@ __global__ void backproject_bwd_kernel(const float *__restrict__ depth_img, int 
   if (threadIdx.x == 0) { atomicAdd(d_ss, a); atomicAdd(d_ss + 1, b); }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// NDC ray warp (model/common.py:632-675), one thread per ray; op order of the reference, each op rounded.
+//   t = -(near + oz) / dz;  p = o + t d;  A = px / pz;  B = py / pz;  gx = -1 / (1 / fx)
+//   o' = (gx A, gy B, 1 + 2 near / pz);  d' = (gx (dx/dz - A), gy (dy/dz - B), 1 - o'z)
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void ndc_rays_fwd_kernel(const float *__restrict__ K, float near_, const float *__restrict__ origin,
+                                    const float *__restrict__ dirs, int n, float *__restrict__ no, float *__restrict__ nd) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float gx = __fdiv_rn(-1.f, __fdiv_rn(1.f, K[0])), gy = __fdiv_rn(-1.f, __fdiv_rn(1.f, K[5]));
+  const float ox = origin[0], oy = origin[1], oz = origin[2];
+  const float dx = dirs[3 * i], dy = dirs[3 * i + 1], dz = dirs[3 * i + 2];
+  const float t = __fdiv_rn(-__fadd_rn(near_, oz), dz);
+  const float px = __fadd_rn(ox, __fmul_rn(t, dx)), py = __fadd_rn(oy, __fmul_rn(t, dy)), pz = __fadd_rn(oz, __fmul_rn(t, dz));
+  const float A = __fdiv_rn(px, pz), B = __fdiv_rn(py, pz);
+  const float o2 = __fadd_rn(1.f, __fdiv_rn(__fmul_rn(2.f, near_), pz));
+  no[3 * i] = __fmul_rn(gx, A);
+  no[3 * i + 1] = __fmul_rn(gy, B);
+  no[3 * i + 2] = o2;
+  nd[3 * i] = __fmul_rn(gx, __fsub_rn(__fdiv_rn(dx, dz), A));
+  nd[3 * i + 1] = __fmul_rn(gy, __fsub_rn(__fdiv_rn(dy, dz), B));
+  nd[3 * i + 2] = __fsub_rn(1.f, o2);
+}
+
+__global__ void ndc_rays_bwd_kernel(const float *__restrict__ K, float near_, const float *__restrict__ origin,
+                                    const float *__restrict__ dirs, int n, const float *__restrict__ g_no,
+                                    const float *__restrict__ g_nd, float *__restrict__ d_o_rows, float *__restrict__ d_dirs,
+                                    float *__restrict__ d_fxfy) {
+  __shared__ float red[32];
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  float gfx = 0.f, gfy = 0.f;
+  if (i < n) {
+    const float gx = __fdiv_rn(-1.f, __fdiv_rn(1.f, K[0])), gy = __fdiv_rn(-1.f, __fdiv_rn(1.f, K[5]));
+    const float ox = origin[0], oy = origin[1], oz = origin[2];
+    const float dx = dirs[3 * i], dy = dirs[3 * i + 1], dz = dirs[3 * i + 2];
+    const float t = -(near_ + oz) / dz;
+    const float px = ox + t * dx, py = oy + t * dy, pz = oz + t * dz;
+    const float A = px / pz, B = py / pz, rx = dx / dz, ry = dy / dz;
+    const float go0 = g_no ? g_no[3 * i] : 0.f, go1 = g_no ? g_no[3 * i + 1] : 0.f, go2 = g_no ? g_no[3 * i + 2] : 0.f;
+    const float gd0 = g_nd ? g_nd[3 * i] : 0.f, gd1 = g_nd ? g_nd[3 * i + 1] : 0.f, gd2 = g_nd ? g_nd[3 * i + 2] : 0.f;
+    const float gA = gx * (go0 - gd0), gB = gy * (go1 - gd1), grx = gx * gd0, gry = gy * gd1;
+    // d gx / d fx = -1 (gx = -1/(1/fx))
+    gfx = -(go0 * A + gd0 * (rx - A));
+    gfy = -(go1 * B + gd1 * (ry - B));
+    const float go2t = go2 - gd2;
+    const float ipz = 1.f / pz;
+    const float gpx = gA * ipz, gpy = gB * ipz;
+    const float gpz = -(go2t * 2.f * near_ + gA * px + gB * py) * ipz * ipz;
+    const float gt = gpx * dx + gpy * dy + gpz * dz;
+    const float idz = 1.f / dz;
+    d_o_rows[3 * i] = gpx;
+    d_o_rows[3 * i + 1] = gpy;
+    d_o_rows[3 * i + 2] = gpz - gt * idz;
+    d_dirs[3 * i] = t * gpx + grx * idz;
+    d_dirs[3 * i + 1] = t * gpy + gry * idz;
+    d_dirs[3 * i + 2] = t * gpz - gt * t * idz - (grx * dx + gry * dy) * idz * idz;
+  }
+  gfx = block_sum(gfx, red);
+  gfy = block_sum(gfy, red);
+  if (threadIdx.x == 0) { atomicAdd(d_fxfy, gfx); atomicAdd(d_fxfy + 1, gfy); }
+}
+
 static inline int grid_for(int n, int threads) {
   int g = nnb_cdiv(n, threads);
   const int cap = nnb_sm_count() * 8;
@@ -342,6 +404,26 @@ int nnb_backproject_bwd(const float *depth_img, int h, int w, int h4, int w4, co
   if (!depth_img || !camera_mat || !clamped || !d_pc || !d_scale_shift) return NNB_ERR_BAD_ARG;
   NNB_CUDA(cudaMemsetAsync(d_scale_shift, 0, 2 * sizeof(float), nnb_stream(stream)));
   backproject_bwd_kernel<<<grid_for(h4 * w4, 256), 256, 0, nnb_stream(stream)>>>(depth_img, h, w, h4, w4, camera_mat, clamped, d_pc, d_scale_shift);
+  NNB_CHECK_LAUNCH();
+  return 0;
+}
+
+int nnb_ndc_rays_fwd(const float *camera_mat, float near_, const float *origin, const float *dirs, int n_rays, float *ndc_o,
+                     float *ndc_d, void *stream) {
+  if (!camera_mat || !origin || !dirs || !ndc_o || !ndc_d || n_rays < 0) return NNB_ERR_BAD_ARG;
+  if (n_rays == 0) return 0;
+  ndc_rays_fwd_kernel<<<nnb_cdiv(n_rays, 256), 256, 0, nnb_stream(stream)>>>(camera_mat, near_, origin, dirs, n_rays, ndc_o, ndc_d);
+  NNB_CHECK_LAUNCH();
+  return 0;
+}
+
+int nnb_ndc_rays_bwd(const float *camera_mat, float near_, const float *origin, const float *dirs, int n_rays, const float *d_ndc_o,
+                     const float *d_ndc_d, float *d_origin_rows, float *d_dirs, float *d_fxfy, void *stream) {
+  if (!camera_mat || !origin || !dirs || !d_origin_rows || !d_dirs || !d_fxfy || n_rays < 0) return NNB_ERR_BAD_ARG;
+  NNB_CUDA(cudaMemsetAsync(d_fxfy, 0, 2 * sizeof(float), nnb_stream(stream)));
+  if (n_rays == 0) return 0;
+  ndc_rays_bwd_kernel<<<nnb_cdiv(n_rays, 256), 256, 0, nnb_stream(stream)>>>(camera_mat, near_, origin, dirs, n_rays, d_ndc_o, d_ndc_d,
+                                                                            d_origin_rows, d_dirs, d_fxfy);
   NNB_CHECK_LAUNCH();
   return 0;
 }

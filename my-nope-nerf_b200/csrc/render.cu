@@ -11,10 +11,10 @@ int nnb_composite_bwd_launch(const float *, const float *, const float *, int, i
 // tensor-core path (mlp_tc.cu)
 size_t nnb_tc_workspace_bytes(const nnb_render_cfg *cfg, int save);
 int nnb_tc_render_fwd(const nnb_render_cfg *cfg, const float *const *params, const void *packed, const float *origin,
-                      const float *dirs, const float *noise, float *rgb, float *dist, float *weights, float *alpha, float *z_vals,
+                      const float *dirs, const nnb_ray_extras *ex, const float *noise, float *rgb, float *dist, float *weights, float *alpha, float *z_vals,
                       void *ws, size_t ws_bytes, int save, cudaStream_t s);
 int nnb_tc_render_bwd(const nnb_render_cfg *cfg, const float *const *params, const void *packed, const float *origin,
-                      const float *dirs, const float *weights, const float *alpha, const float *z_vals, const float *d_rgb,
+                      const float *dirs, const nnb_ray_extras *ex, const float *weights, const float *alpha, const float *z_vals, const float *d_rgb,
                       const float *d_dist, const float *d_alpha_out, const float *d_weights_out, float *const *d_params,
                       float *d_origin, float *d_dirs, void *ws, size_t ws_bytes, cudaStream_t s);
 
@@ -106,12 +106,13 @@ int dgrad(long long M, int N, int ncols, const float *dY, int lddy, const float 
   return sgemm_launch<true, false>(M, ncols, N, dY, lddy, W, ldw, dX, lddx, de, 1, s);
 }
 
-int fp32_forward_chunk(const nnb_render_cfg *cfg, const float *const *P, const float *origin, const float *dirs, const float *noise,
+int fp32_forward_chunk(const nnb_render_cfg *cfg, const float *const *P, const float *origin, const float *dirs, const float *ray_o,
+                       const float *view, const float *noise,
                        int R, Fp32Buffers &b, float *rgb, float *dist, float *weights, float *alpha, float *z_vals, cudaStream_t s) {
   const int S = cfg->n_samples;
   const long long M = (long long)R * S;
   float *z = z_vals ? z_vals : b.z;
-  encode_fwd_kernel<<<(unsigned)((M + 63) / 64), 256, 0, s>>>(origin, dirs, noise, M, S, cfg->near_, cfg->far_, cfg->use_dir, b.X0, b.Hs,
+  encode_fwd_kernel<<<(unsigned)((M + 63) / 64), 256, 0, s>>>(origin, dirs, ray_o, view, noise, M, S, cfg->near_, cfg->far_, cfg->use_dir, b.X0, b.Hs,
                                                             b.Fc, z);
   NNB_CHECK_LAUNCH();
   RET(linear_fwd(M, 256, 63, b.X0, 64, P[P_L0], P[P_L0 + 1], b.H0, 256, 1, s));
@@ -148,12 +149,20 @@ size_t nnb_render_workspace_bytes(const nnb_render_cfg *cfg, int save_for_backwa
 int nnb_render_fwd(const nnb_render_cfg *cfg, const float *const *params_host, const void *packed, const float *origin,
                    const float *dirs, const float *noise, float *rgb, float *dist, float *weights, float *alpha, float *z_vals,
                    void *workspace, size_t workspace_bytes, int save_for_backward, void *stream) {
+  return nnb_render_fwd_ex(cfg, params_host, packed, origin, dirs, nullptr, noise, rgb, dist, weights, alpha, z_vals, workspace,
+                           workspace_bytes, save_for_backward, stream);
+}
+
+int nnb_render_fwd_ex(const nnb_render_cfg *cfg, const float *const *params_host, const void *packed, const float *origin,
+                      const float *dirs, const nnb_ray_extras *ex, const float *noise, float *rgb, float *dist, float *weights,
+                      float *alpha, float *z_vals, void *workspace, size_t workspace_bytes, int save_for_backward, void *stream) {
+  const float *ray_o = ex ? ex->ray_origins : nullptr, *view = ex ? ex->view_dirs : nullptr;
   if (!cfg || !params_host || !origin || !dirs || !rgb || !dist || !workspace) return NNB_ERR_BAD_ARG;
   if (cfg->n_rays <= 0 || cfg->n_samples < 2 || cfg->n_samples > 256) return NNB_ERR_BAD_ARG;
   if (workspace_bytes < nnb_render_workspace_bytes(cfg, save_for_backward)) return NNB_ERR_WORKSPACE;
   cudaStream_t s = nnb_stream(stream);
   if (cfg->precision == NNB_PREC_BF16)
-    return nnb_tc_render_fwd(cfg, params_host, packed, origin, dirs, noise, rgb, dist, weights, alpha, z_vals, workspace,
+    return nnb_tc_render_fwd(cfg, params_host, packed, origin, dirs, ex, noise, rgb, dist, weights, alpha, z_vals, workspace,
                              workspace_bytes, save_for_backward, s);
   if (cfg->precision != NNB_PREC_FP32) return NNB_ERR_UNSUPPORTED;
   const int S = cfg->n_samples;
@@ -161,14 +170,15 @@ int nnb_render_fwd(const nnb_render_cfg *cfg, const float *const *params_host, c
   if (save_for_backward) {
     if (!weights || !alpha || !z_vals) return NNB_ERR_BAD_ARG;
     carve_save(static_cast<float *>(workspace), (size_t)cfg->n_rays * S, b);
-    return fp32_forward_chunk(cfg, params_host, origin, dirs, noise, cfg->n_rays, b, rgb, dist, weights, alpha, z_vals, s);
+    return fp32_forward_chunk(cfg, params_host, origin, dirs, ray_o, view, noise, cfg->n_rays, b, rgb, dist, weights, alpha, z_vals, s);
   }
   const int rc = cfg->n_rays < FP32_RENDER_CHUNK ? cfg->n_rays : FP32_RENDER_CHUNK;
   carve_nosave(static_cast<float *>(workspace), (size_t)rc * S, b);
   for (int r0 = 0; r0 < cfg->n_rays; r0 += rc) {
     const int r = cfg->n_rays - r0 < rc ? cfg->n_rays - r0 : rc;
     const size_t o = (size_t)r0 * S;
-    RET(fp32_forward_chunk(cfg, params_host, origin, dirs + 3 * (size_t)r0, noise ? noise + o : nullptr, r, b, rgb + 3 * (size_t)r0,
+    RET(fp32_forward_chunk(cfg, params_host, origin, dirs + 3 * (size_t)r0, ray_o ? ray_o + 3 * (size_t)r0 : nullptr,
+                           view ? view + 3 * (size_t)r0 : nullptr, noise ? noise + o : nullptr, r, b, rgb + 3 * (size_t)r0,
                            dist + r0, weights ? weights + o : nullptr, alpha ? alpha + o : nullptr, z_vals ? z_vals + o : nullptr, s));
   }
   return 0;
@@ -178,11 +188,21 @@ int nnb_render_bwd(const nnb_render_cfg *cfg, const float *const *params_host, c
                    const float *dirs, const float *weights, const float *alpha, const float *z_vals, const float *d_rgb,
                    const float *d_dist, const float *d_alpha_out, const float *d_weights_out, float *const *d_params_host,
                    float *d_origin, float *d_dirs, void *workspace, size_t workspace_bytes, void *stream) {
+  return nnb_render_bwd_ex(cfg, params_host, packed, origin, dirs, nullptr, weights, alpha, z_vals, d_rgb, d_dist, d_alpha_out,
+                           d_weights_out, d_params_host, d_origin, d_dirs, workspace, workspace_bytes, stream);
+}
+
+int nnb_render_bwd_ex(const nnb_render_cfg *cfg, const float *const *params_host, const void *packed, const float *origin,
+                      const float *dirs, const nnb_ray_extras *ex, const float *weights, const float *alpha, const float *z_vals,
+                      const float *d_rgb, const float *d_dist, const float *d_alpha_out, const float *d_weights_out,
+                      float *const *d_params_host, float *d_origin, float *d_dirs, void *workspace, size_t workspace_bytes,
+                      void *stream) {
+  if (ex && ((ex->ray_origins && !ex->d_ray_origins) || (ex->view_dirs && !ex->d_view_dirs))) return NNB_ERR_BAD_ARG;
   if (!cfg || !params_host || !d_params_host || !origin || !dirs || !z_vals || !d_origin || !d_dirs || !workspace) return NNB_ERR_BAD_ARG;
   if (workspace_bytes < nnb_render_workspace_bytes(cfg, 1)) return NNB_ERR_WORKSPACE;
   cudaStream_t s = nnb_stream(stream);
   if (cfg->precision == NNB_PREC_BF16)
-    return nnb_tc_render_bwd(cfg, params_host, packed, origin, dirs, weights, alpha, z_vals, d_rgb, d_dist, d_alpha_out,
+    return nnb_tc_render_bwd(cfg, params_host, packed, origin, dirs, ex, weights, alpha, z_vals, d_rgb, d_dist, d_alpha_out,
                              d_weights_out, d_params_host, d_origin, d_dirs, workspace, workspace_bytes, s);
   if (cfg->precision != NNB_PREC_FP32) return NNB_ERR_UNSUPPORTED;
   const int R = cfg->n_rays, S = cfg->n_samples;
@@ -247,7 +267,8 @@ int nnb_render_bwd(const nnb_render_cfg *cfg, const float *const *params_host, c
   RET(dgrad(M, 256, 63, b.G1, 256, P[P_L0], 63, b.Genc, 64, nullptr, 0, 1, s));
   // encoding + sampling backward -> d_origin, d_dirs
   const int threads = ((S + 31) / 32) * 32;
-  encode_bwd_kernel<<<R, threads, 0, s>>>(b.X0, b.Genc, 64, b.Gdir, 32, dirs, z_vals, S, cfg->use_dir, d_origin, d_dirs);
+  encode_bwd_kernel<<<R, threads, 0, s>>>(b.X0, b.Genc, 64, b.Gdir, 32, dirs, ex ? ex->view_dirs : nullptr, z_vals, S, cfg->use_dir, d_origin,
+                                          d_dirs, (ex && ex->ray_origins) ? ex->d_ray_origins : nullptr, ex ? ex->d_view_dirs : nullptr);
   NNB_CHECK_LAUNCH();
   (void)weights; (void)alpha; (void)origin;
   return 0;

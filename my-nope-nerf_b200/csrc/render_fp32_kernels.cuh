@@ -15,6 +15,7 @@
 // coalesced to X0 (ld 64) and to the skip columns of Hs (ld 320); also z and the per-sample copy of the
 // view-direction encoding into Fc[:, 256:288].
 __global__ void __launch_bounds__(256) encode_fwd_kernel(const float *__restrict__ origin, const float *__restrict__ dirs,
+                                                         const float *__restrict__ ray_o, const float *__restrict__ view,
                                                          const float *__restrict__ noise, long long M, int S, float near_,
                                                          float far_, int use_dir, float *__restrict__ X0,
                                                          float *__restrict__ Hs, float *__restrict__ Fc,
@@ -32,7 +33,7 @@ __global__ void __launch_bounds__(256) encode_fwd_kernel(const float *__restrict
       const float z = z_sample(s, S, near_, far_, noise ? noise + ray * S : nullptr);
       if (c == 0 && zout) zout[m] = z;
       const float d = dirs[3 * ray + c];
-      const float x = __fadd_rn(origin[c], __fmul_rn(d, z));
+      const float x = __fadd_rn(ray_o ? ray_o[3 * ray + c] : origin[c], __fmul_rn(d, z));
       enc[ls][c] = x;
       float f = 1.0f;
 #pragma unroll
@@ -44,7 +45,7 @@ __global__ void __launch_bounds__(256) encode_fwd_kernel(const float *__restrict
         f *= 2.0f;
       }
       if (c == 0) enc[ls][63] = 0.f;
-      const float v = use_dir ? -d : 1.0f;  // view direction = -ray (model/rendering.py:195-198)
+      const float v = use_dir ? -(view ? view[3 * ray + c] : d) : 1.0f;  // view direction = -ray (model/rendering.py:195-198)
       denc[ls][c] = v;
       f = 1.0f;
 #pragma unroll
@@ -176,8 +177,9 @@ __global__ void colsum_kernel(const float *__restrict__ dY, long long M, int N, 
 // Also the view-direction encoding: gdir = sum over the ray's samples of Gdir[m*ldgd + 0..26].
 __global__ void encode_bwd_kernel(const float *__restrict__ X0, const float *__restrict__ Genc, int ldg,
                                   const float *__restrict__ Gdir, int ldgd, const float *__restrict__ dirs,
-                                  const float *__restrict__ z, int S, int use_dir, float *__restrict__ d_origin,
-                                  float *__restrict__ d_dirs) {
+                                  const float *__restrict__ view, const float *__restrict__ z, int S, int use_dir,
+                                  float *__restrict__ d_origin, float *__restrict__ d_dirs, float *__restrict__ d_ray_o,
+                                  float *__restrict__ d_view) {
   __shared__ float red[32];
   __shared__ float gd[32];
   const long long ray = blockIdx.x;
@@ -225,7 +227,7 @@ __global__ void encode_bwd_kernel(const float *__restrict__ X0, const float *__r
     for (int c = 0; c < 3; ++c) {
       float gdir = 0.f;
       if (use_dir && Gdir) {
-        const float v = -dirs[3 * ray + c];
+        const float v = -(view ? view[3 * ray + c] : dirs[3 * ray + c]);
         float acc = gd[c];
         float f = 1.0f;
 #pragma unroll
@@ -237,8 +239,10 @@ __global__ void encode_bwd_kernel(const float *__restrict__ X0, const float *__r
         }
         gdir = -acc;  // v = -d
       }
-      d_dirs[3 * ray + c] = dd[c] + gdir;
-      atomicAdd(d_origin + c, o[c]);
+      if (view) { d_dirs[3 * ray + c] = dd[c]; if (d_view) d_view[3 * ray + c] = gdir; }
+      else d_dirs[3 * ray + c] = dd[c] + gdir;
+      if (d_ray_o) d_ray_o[3 * ray + c] = o[c];
+      else atomicAdd(d_origin + c, o[c]);
     }
   }
 }

@@ -28,7 +28,13 @@ class RenderCfg(C.Structure):
                 ("precision", C.c_int)]
 
 
+class RayExtras(C.Structure):
+    """nnb_ray_extras: per-ray origins / view directions of the NDC sampling branch and their backward outputs."""
+    _fields_ = [("ray_origins", C.c_void_p), ("view_dirs", C.c_void_p), ("d_ray_origins", C.c_void_p), ("d_view_dirs", C.c_void_p)]
+
+
 _p, _i, _f, _sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
+_exp = C.POINTER(RayExtras)
 _cfgp = C.POINTER(RenderCfg)
 _pp = C.POINTER(C.c_void_p)
 
@@ -52,6 +58,10 @@ SIGNATURES = {
     "nnb_render_workspace_bytes": [_cfgp, _i],
     "nnb_render_fwd": [_cfgp, _pp, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _i, _p],
     "nnb_render_bwd": [_cfgp, _pp, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _pp, _p, _p, _p, _sz, _p],
+    "nnb_render_fwd_ex": [_cfgp, _pp, _p, _p, _p, _exp, _p, _p, _p, _p, _p, _p, _p, _sz, _i, _p],
+    "nnb_render_bwd_ex": [_cfgp, _pp, _p, _p, _p, _exp, _p, _p, _p, _p, _p, _p, _p, _pp, _p, _p, _p, _sz, _p],
+    "nnb_ndc_rays_fwd": [_p, _f, _p, _p, _i, _p, _p, _p],
+    "nnb_ndc_rays_bwd": [_p, _f, _p, _p, _i, _p, _p, _p, _p, _p, _p],
     "nnb_composite_fwd": [_p, _p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p],
     "nnb_composite_bwd": [_p, _p, _p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p],
     "nnb_mlp_points_workspace_bytes": [C.c_longlong],

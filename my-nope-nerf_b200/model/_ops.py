@@ -189,11 +189,20 @@ def _workspace(device, nbytes, tag):
     return buf
 
 
-def render_nograd(cfg, params, packed, origin, dirs, noise, want_aux=True):
-    """Forward only (eval / render loops).  Returns rgb, dist, weights, alpha, z (aux None if not wanted)."""
+def _extras(ray_o, view, d_ray_o=None, d_view=None):
+    def v(t):
+        return ptr(t).value if t is not None else None
+    return K.RayExtras(v(ray_o), v(view), v(d_ray_o), v(d_view))
+
+
+def render_nograd(cfg, params, packed, origin, dirs, noise, want_aux=True, ray_o=None, view=None):
+    """Forward only (eval / render loops).  Returns rgb, dist, weights, alpha, z (aux None if not wanted).
+    ray_o / view: per-ray origins and view directions of the NDC branch (nnb_ray_extras)."""
     R, S = cfg.n_rays, cfg.n_samples
     dev = dirs.device
     origin, dirs = f32(origin), f32(dirs)
+    ray_o = f32(ray_o) if ray_o is not None else None
+    view = f32(view) if view is not None else None
     noise = f32(noise).reshape(R, S) if noise is not None else None
     params = [f32(p) for p in params]
     rgb, dist = torch.empty(R, 3, device=dev), torch.empty(R, device=dev)
@@ -203,8 +212,13 @@ def render_nograd(cfg, params, packed, origin, dirs, noise, want_aux=True):
     nbytes = workspace_bytes(cfg, 0)
     ws = _workspace(dev, nbytes, "render_eval")
     parr = K.param_ptr_array(params)
-    call("nnb_render_fwd", C.byref(cfg), parr, ptr(packed), ptr(origin), ptr(dirs), ptr(noise), ptr(rgb), ptr(dist), ptr(w), ptr(a),
-         ptr(z), ptr(ws), nbytes, 0, stream())
+    if ray_o is None and view is None:
+        call("nnb_render_fwd", C.byref(cfg), parr, ptr(packed), ptr(origin), ptr(dirs), ptr(noise), ptr(rgb), ptr(dist), ptr(w), ptr(a),
+             ptr(z), ptr(ws), nbytes, 0, stream())
+    else:
+        ex = _extras(ray_o, view)
+        call("nnb_render_fwd_ex", C.byref(cfg), parr, ptr(packed), ptr(origin), ptr(dirs), C.byref(ex), ptr(noise), ptr(rgb), ptr(dist),
+             ptr(w), ptr(a), ptr(z), ptr(ws), nbytes, 0, stream())
     return rgb, dist, w, a, z
 
 
@@ -250,6 +264,79 @@ class RenderRays(torch.autograd.Function):
              opt(g_dist), opt(g_a), opt(g_w), garr, ptr(d_origin), ptr(d_dirs), ptr(ctx.ws), ctx.nbytes, stream())
         ctx.ws = None
         return (None, None, d_origin, d_dirs, None) + tuple(grads)
+
+
+class RenderRaysEx(torch.autograd.Function):
+    """RenderRays with per-ray origins and separate view directions (the `sample_ndc` branch, model/rendering.py:169-181):
+    points = ray_o[r] + dirs[r] * z, view-direction encoding of -view[r]."""
+
+    @staticmethod
+    def forward(ctx, cfg, packed, ray_o, dirs, view, noise, *params):
+        R, S = cfg.n_rays, cfg.n_samples
+        dev = dirs.device
+        ray_o, dirs, view = f32(ray_o), f32(dirs), f32(view)
+        noise = f32(noise).reshape(R, S) if noise is not None else None
+        params = [f32(p) for p in params]
+        rgb, dist = torch.empty(R, 3, device=dev), torch.empty(R, device=dev)
+        w, a, z = torch.empty(R, S, device=dev), torch.empty(R, S, device=dev), torch.empty(R, S, device=dev)
+        nbytes = workspace_bytes(cfg, 1)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        parr = K.param_ptr_array(params)
+        ex = _extras(ray_o, view)
+        call("nnb_render_fwd_ex", C.byref(cfg), parr, ptr(packed), ptr(ray_o), ptr(dirs), C.byref(ex), ptr(noise), ptr(rgb), ptr(dist),
+             ptr(w), ptr(a), ptr(z), ptr(ws), nbytes, 1, stream())
+        ctx.cfg, ctx.packed, ctx.ws, ctx.nbytes = cfg, packed, ws, nbytes
+        ctx.save_for_backward(ray_o, dirs, view, w, a, z, *params)
+        ctx.mark_non_differentiable(z)
+        return rgb, dist, w, a, z
+
+    @staticmethod
+    def backward(ctx, g_rgb, g_dist, g_w, g_a, g_z):
+        ray_o, dirs, view, w, a, z, *params = ctx.saved_tensors
+        cfg = ctx.cfg
+        dev = dirs.device
+        flat = torch.zeros(sum(p.numel() for p in params), device=dev)
+        grads, o = [], 0
+        for p in params:
+            grads.append(flat[o:o + p.numel()].view_as(p))
+            o += p.numel()
+        d_origin, d_dirs = torch.empty(3, device=dev), torch.empty_like(dirs)
+        d_ray_o, d_view = torch.empty_like(ray_o), torch.empty_like(view)
+        parr, garr = K.param_ptr_array(params), K.param_ptr_array(grads)
+        ex = _extras(ray_o, view, d_ray_o, d_view)
+
+        def opt(g):
+            return ptr(f32(g)) if g is not None else None
+        call("nnb_render_bwd_ex", C.byref(cfg), parr, ptr(ctx.packed), ptr(ray_o), ptr(dirs), C.byref(ex), ptr(w), ptr(a), ptr(z),
+             opt(g_rgb), opt(g_dist), opt(g_a), opt(g_w), garr, ptr(d_origin), ptr(d_dirs), ptr(ctx.ws), ctx.nbytes, stream())
+        ctx.ws = None
+        return (None, None, d_ray_o, d_dirs, d_view, None) + tuple(grads)
+
+
+class NdcRays(torch.autograd.Function):
+    """get_ndc_rays_fxfy (model/common.py:632-675) with focal = camera_mat[0,0], camera_mat[1,1] (model/rendering.py:171-173).
+    camera_mat (1,4,4) or (4,4), origin (3,), dirs (R,3) -> ndc_o (R,3), ndc_d (R,3)."""
+
+    @staticmethod
+    def forward(ctx, camera_mat, origin, dirs, near):
+        cm, origin, dirs = f32(camera_mat).reshape(4, 4), f32(origin), f32(dirs)
+        R = dirs.shape[0]
+        no, nd = torch.empty_like(dirs), torch.empty_like(dirs)
+        call("nnb_ndc_rays_fwd", ptr(cm), float(near), ptr(origin), ptr(dirs), R, ptr(no), ptr(nd), stream())
+        ctx.save_for_backward(cm, origin, dirs)
+        ctx.near, ctx.cm_shape = float(near), camera_mat.shape
+        return no, nd
+
+    @staticmethod
+    def backward(ctx, g_no, g_nd):
+        cm, origin, dirs = ctx.saved_tensors
+        R = dirs.shape[0]
+        d_rows, d_dirs, d_f = torch.empty_like(dirs), torch.empty_like(dirs), torch.empty(2, device=dirs.device)
+        call("nnb_ndc_rays_bwd", ptr(cm), ctx.near, ptr(origin), ptr(dirs), R, ptr(f32(g_no)) if g_no is not None else None,
+             ptr(f32(g_nd)) if g_nd is not None else None, ptr(d_rows), ptr(d_dirs), ptr(d_f), stream())
+        d_cm = torch.zeros(16, device=dirs.device)
+        d_cm[0], d_cm[5] = d_f[0], d_f[1]
+        return d_cm.view(ctx.cm_shape), d_rows.sum(0), d_dirs, None
 
 
 class Composite(torch.autograd.Function):

@@ -1,4 +1,4 @@
-"""Renderer -- drop-in for the reference's model/rendering.py (`nope_nerf` technique, `uniform` sampling).
+"""Renderer -- drop-in for the reference's model/rendering.py (`nope_nerf` technique, `uniform` and `ndc` sampling).
 
 forward(pixels, depth, camera_mat, world_mat, scale_mat, rendering_technique, add_noise=True, eval_=False, it=...)
 returns the reference's dict: rgb (1,R,3), z_vals (R,S), normal, depth_pred, depth_gt, alpha (R,S).
@@ -48,9 +48,10 @@ class Renderer(nn.Module):
     def _prec(self):
         return _cabi.PREC_BF16 if self.precision == 'bf16' else _cabi.PREC_FP32
 
-    def _cfg(self, n_rays, n_samples):
+    def _cfg(self, n_rays, n_samples, depth_range=None):
         c = self.cfg
-        return _ops.make_cfg(n_rays, n_samples, c['depth_range'][0], c['depth_range'][1],
+        dr = depth_range if depth_range is not None else c['depth_range']
+        return _ops.make_cfg(n_rays, n_samples, dr[0], dr[1],
                              self.model.occ_activation == 'softplus', c['dist_alpha'], c['white_background'],
                              c['use_ray_dir'], self._prec())
 
@@ -66,8 +67,9 @@ class Renderer(nn.Module):
     def nope_nerf(self, pixels, depth, camera_mat, world_mat, scale_mat, add_noise=False, it=100000, eval_=False,
                   noise=None, lazy_mask=False):
         cfg = self.cfg
-        if cfg['sample_option'] != 'uniform':
-            raise NotImplementedError("sample_option=%r: the NDC branch is a 'next' row (SURVEY.md 8f rank 2)" % cfg['sample_option'])
+        ndc = cfg['sample_option'] == 'ndc'
+        if cfg['sample_option'] not in ('uniform', 'ndc'):
+            raise ValueError("unknown sample_option %r" % (cfg['sample_option'],))
         if cfg['normal_loss'] and not eval_:
             raise NotImplementedError("normal_loss needs the second-order path ('next' row, SURVEY.md 8f rank 3)")
         batch_size, n_points, _ = pixels.shape
@@ -76,6 +78,14 @@ class Renderer(nn.Module):
         S = cfg['num_points'] - cfg['outside_steps']
         origin, dirs, nrm, d_gt, mask = _ops.RayGen.apply(pixels, depth, camera_mat, world_mat, scale_mat,
                                                           cfg['normalise_ray'])
+        ray_o = view = None
+        dr = None
+        if ndc:
+            # model/rendering.py:92-93,169-181: rays warped to NDC (near plane 1.0), samples on [0, 1] without jitter;
+            # the view-direction encoding keeps the world-space ray.
+            ray_o, ndc_d = _ops.NdcRays.apply(camera_mat, origin, dirs, 1.0)
+            view, dirs = dirs, ndc_d
+            add_noise, noise, dr = False, None, (0., 1.)
         if add_noise and noise is None:
             # same draw, shape and generator as the reference (model/rendering.py:190)
             noise = torch.rand(batch_size, n_points, S, device=pixels.device)
@@ -90,14 +100,19 @@ class Renderer(nn.Module):
             step = MAX_TRAIN_RAYS_FP32 if self._prec() == _cabi.PREC_FP32 else n_points
             for r0 in range(0, n_points, step):
                 r1 = min(n_points, r0 + step)
-                rc = self._cfg(r1 - r0, S)
+                rc = self._cfg(r1 - r0, S, dr)
                 nz = None if noise is None else noise.reshape(n_points, S)[r0:r1]
-                outs.append(_ops.RenderRays.apply(rc, packed, origin, dirs[r0:r1], nz, *params))
+                if ndc:
+                    outs.append(_ops.RenderRaysEx.apply(rc, packed, ray_o[r0:r1], dirs[r0:r1], view[r0:r1], None, *params))
+                else:
+                    outs.append(_ops.RenderRays.apply(rc, packed, origin, dirs[r0:r1], nz, *params))
             rgb, dist, w, alpha, z = [torch.cat(t, 0) if len(outs) > 1 else t[0] for t in zip(*outs)]
         else:
-            rc = self._cfg(n_points, S)
+            rc = self._cfg(n_points, S, dr)
             rgb, dist, w, alpha, z = _ops.render_nograd(rc, [p.detach() for p in params], packed, origin.detach(),
-                                                        dirs.detach(), None if noise is None else noise.reshape(n_points, S))
+                                                        dirs.detach(), None if noise is None else noise.reshape(n_points, S),
+                                                        ray_o=None if ray_o is None else ray_o.detach(),
+                                                        view=None if view is None else view.detach())
         if eval_ and cfg['normalise_ray']:  # model/rendering.py:144-148
             dist = dist / nrm
             d_gt = d_gt / nrm
@@ -107,6 +122,9 @@ class Renderer(nn.Module):
             depth_pred, depth_gt = dist[mask], d_gt[mask]
         else:
             depth_pred, depth_gt = dist, d_gt
+        if ndc:  # model/rendering.py:158-159
+            depth_gt = 1 - 1 / depth_gt
+            d_gt = 1 - 1 / d_gt
         return {
             'rgb': rgb.reshape(batch_size, -1, 3), 'z_vals': z, 'normal': None,
             'depth_pred': depth_pred, 'depth_gt': depth_gt, 'alpha': alpha,

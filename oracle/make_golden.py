@@ -220,14 +220,73 @@ def render_and_step_vectors(ref, cfg):
     return out
 
 
+def variant_vectors(ref, cfg0):
+    """Renderer.forward on the non-default branches: the LLFF configuration (configs/LLFF/fern.yaml:
+    sample_option ndc + dist_alpha + depth_range [0,1]), dist_alpha with uniform sampling, and white background + relu
+    density + use_ray_dir False.  Forward outputs, and gradients of a probed scalar w.r.t. the MLP, world_mat, camera_mat."""
+    import copy
+    out = {"torch_version": torch.__version__}
+    scene = syn.make_scene("tiny")
+    n, h, w = scene["n"], scene["h"], scene["w"]
+    R = 48
+    sd = syn.init_mlp_state(42)
+    g = torch.Generator().manual_seed(21)
+    ray_idx = torch.randperm(h * w, generator=g)[:R]
+    noise = torch.rand(1, R, 128, generator=g)
+    pr, pd = torch.randn(1, R, 3, generator=g) / R, torch.randn(R, generator=g) / R
+    r0, t0 = syn.init_pose_params(n)
+    pose_net = ref.model.LearnPose(n, True, True, cfg0, init_c2w=scene["poses_gt"].clone())
+    with torch.no_grad():
+        pose_net.r.copy_(r0)
+        pose_net.t.copy_(t0)
+    world_mat0 = torch.inverse(pose_net(1)).unsqueeze(0).detach()
+    _, p_full = ref.common.arange_pixels((h, w))
+    p = p_full[:, ray_idx]
+    depth_sel = scene["depths"][1].reshape(1, -1, 1)[:, ray_idx].clone()
+    variants = {
+        "llff": dict(rendering=dict(sample_option="ndc", dist_alpha=True, depth_range=[0.0, 1.0])),
+        "dist_alpha_uniform": dict(rendering=dict(dist_alpha=True)),
+        "white_relu_nodir": dict(rendering=dict(white_background=True, use_ray_dir=False), model=dict(occ_activation="relu")),
+    }
+    out["inputs"] = {"ray_idx": ray_idx, "noise": noise, "pixels": p, "depth": depth_sel, "world_mat": world_mat0,
+                     "camera_mat": scene["camera_mat"], "probe_rgb": pr, "probe_dist": pd}
+    for name, over in variants.items():
+        cfg = copy.deepcopy(cfg0)
+        for sec, kv in over.items():
+            cfg[sec].update(kv)
+        nerf, renderer, net = build_ref_model(ref, cfg, sd)
+        wm = world_mat0.clone().requires_grad_(True)
+        cm = scene["camera_mat"].clone().requires_grad_(True)
+        with injected_draws(noise=noise):
+            o = renderer(p, depth_sel, cm, wm, scene["scale_mat"], "nope_nerf", add_noise=True, eval_=False)
+        ((o["rgb"] * pr).sum() + (o["depth_pred"] * pd[:o["depth_pred"].shape[0]]).sum()).backward()
+        with torch.no_grad():
+            o_ev = renderer(p, depth_sel, scene["camera_mat"], world_mat0, scene["scale_mat"], "nope_nerf", add_noise=False, eval_=True)
+        out[name] = {"override": over,
+                     "train": {k: (v.detach().clone() if torch.is_tensor(v) else v) for k, v in o.items()},
+                     "eval": {k: (v.detach().clone() if torch.is_tensor(v) else v) for k, v in o_ev.items()},
+                     "grad_world_mat": wm.grad.clone(), "grad_camera_mat": cm.grad.clone(),
+                     "mlp_grad_stats": {k: flat_stats(v.grad) for k, v in nerf.named_parameters()},
+                     "mlp_grads": {k: v.grad.clone() for k, v in nerf.named_parameters()
+                                   if k in ("layers0.0.weight", "fc_density.weight", "fc_density.bias", "fc_rgb.weight", "rgb_layers.0.bias")}}
+        print(name, float(o["rgb"].sum()), float(o["depth_pred"].sum()))
+    return out
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
+    if "--variants-only" in sys.argv:
+        ref = ref_harness.load_reference()
+        torch.set_num_threads(max(1, os.cpu_count() or 1))
+        torch.save(variant_vectors(ref, syn.default_cfg()), os.path.join(OUT, "render_variants.pt"))
+        return
     ref = ref_harness.load_reference()
     cfg = syn.default_cfg()
     torch.set_num_threads(max(1, os.cpu_count() or 1))
     torch.save(stage_vectors(ref, cfg), os.path.join(OUT, "stages.pt"))
     torch.save(loss_vectors(ref, cfg), os.path.join(OUT, "losses.pt"))
     torch.save(render_and_step_vectors(ref, cfg), os.path.join(OUT, "render_step.pt"))
+    torch.save(variant_vectors(ref, cfg), os.path.join(OUT, "render_variants.pt"))
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

@@ -191,9 +191,24 @@ def composite(alpha, rgb, z, dist_alpha=False, white_background=False):
     return out_rgb, out_dist, w, alpha
 
 
+def ndc_rays(fxfy, near, rays_o, rays_d):
+    """get_ndc_rays_fxfy, model/common.py:632-675 (same op order).  rays_o, rays_d (...,3) -> NDC origin, direction."""
+    t = -(near + rays_o[..., 2]) / rays_d[..., 2]
+    rays_o = rays_o + t[..., None] * rays_d
+    ox_oz = rays_o[..., 0] / rays_o[..., 2]
+    oy_oz = rays_o[..., 1] / rays_o[..., 2]
+    o0 = -1. / (1 / fxfy[0]) * ox_oz
+    o1 = -1. / (1 / fxfy[1]) * oy_oz
+    o2 = 1. + 2. * near / rays_o[..., 2]
+    d0 = -1. / (1 / fxfy[0]) * (rays_d[..., 0] / rays_d[..., 2] - ox_oz)
+    d1 = -1. / (1 / fxfy[1]) * (rays_d[..., 1] / rays_d[..., 2] - oy_oz)
+    d2 = 1 - o2
+    return torch.stack([o0, o1, o2], -1), torch.stack([d0, d1, d2], -1)
+
+
 def render(P, pixels, depth, camera_mat, world_mat, scale_mat, cfg_r, noise=None, eval_=False,
            occ_activation="softplus", chunk=64000):
-    """The `nope_nerf` volume renderer, default `uniform` sampling branch.
+    """The `nope_nerf` volume renderer: `uniform` sampling branch (default) and `ndc` (model/rendering.py:92-93,169-181).
     model/rendering.py:36-168.  `cfg_r` is the `rendering` config section.
     pixels (1,R,2), depth (1,R,1).  `noise` replaces the reference's internal torch.rand draw
     (model/rendering.py:190) so both sides see the same jitter; None = add_noise False.
@@ -204,8 +219,16 @@ def render(P, pixels, depth, camera_mat, world_mat, scale_mat, cfg_r, noise=None
     o, d, nrm, d_gt, mask = ray_setup(pixels, depth, camera_mat, world_mat, scale_mat,
                                       normalise_ray=cfg_r["normalise_ray"])
     R = d.shape[0]
-    z = stratified_z(R, S, near, far, noise, dtype=pixels.dtype)
-    pts = (o.reshape(1, 1, 3) + d.unsqueeze(1) * z.unsqueeze(-1)).reshape(-1, 3)
+    ndc = cfg_r.get("sample_option", "uniform") == "ndc"
+    if ndc:
+        # model/rendering.py:169-181: focal from camera_mat, near plane 1.0, samples on [0,1], no jitter
+        focal = torch.cat([camera_mat[:, 0, 0], camera_mat[:, 1, 1]])
+        o_s, d_s = ndc_rays(focal, 1.0, o.reshape(1, 3).expand(R, 3), d)
+        z = stratified_z(R, S, 0.0, 1.0, None, dtype=pixels.dtype)
+        pts = (o_s.unsqueeze(1) + d_s.unsqueeze(1) * z.unsqueeze(-1)).reshape(-1, 3)
+    else:
+        z = stratified_z(R, S, near, far, noise, dtype=pixels.dtype)
+        pts = (o.reshape(1, 1, 3) + d.unsqueeze(1) * z.unsqueeze(-1)).reshape(-1, 3)
     view = (-d).unsqueeze(1).expand(R, S, 3).reshape(-1, 3)
     if not cfg_r["use_ray_dir"]:
         view = torch.ones_like(view)
@@ -224,6 +247,9 @@ def render(P, pixels, depth, camera_mat, world_mat, scale_mat, cfg_r, noise=None
         depth_pred, depth_gt = dist[mask], d_gt[mask]
     else:
         depth_pred, depth_gt = dist, d_gt
+    if ndc:  # model/rendering.py:158-159
+        depth_gt = 1 - 1 / depth_gt
+        d_gt = 1 - 1 / d_gt
     return {
         "rgb": rgb.reshape(1, -1, 3), "z_vals": z, "normal": None,
         "depth_pred": depth_pred, "depth_gt": depth_gt, "alpha": alpha,

@@ -190,3 +190,55 @@ def test_tc_render_chunking_invariance_cfg4_slice():
 
     whole = render(R)
     assert torch.equal(render(4097), whole) and torch.equal(render(333), whole)
+
+
+@pytest.mark.parametrize("precision", ["bf16", "fp32"])
+@pytest.mark.parametrize("dist_alpha", [False, True])
+def test_per_ray_origins_and_view_dirs_vs_oracle(dist_alpha, precision):
+    """nnb_render_fwd_ex / nnb_render_bwd_ex (nnb_ray_extras: the NDC branch's per-ray origins and separate view directions),
+    with and without dist_alpha (model/rendering.py:116-122), forward and every gradient, against the oracle
+    (bf16 path: the bf16-emulating oracle, 5e-2 relative L2; fp32 path: the fp32 oracle, 2e-3)."""
+    from model import _cabi, _ops
+    from oracle import nope_oracle as O
+    from oracle.bf16_emulation import mlp_forward_bf16emu
+    R = 40
+    g = torch.Generator().manual_seed(300 + int(dist_alpha))
+    ro = torch.randn(R, 3, generator=g) * 0.3
+    d = torch.nn.functional.normalize(torch.randn(R, 3, generator=g) + torch.tensor([0., 0., -2.]), dim=-1)
+    vw = torch.nn.functional.normalize(torch.randn(R, 3, generator=g), dim=-1)
+    noise = torch.rand(R, 128, generator=g)
+    sd = syn.init_mlp_state(42)
+    p_rgb, p_dist = torch.randn(R, 3, generator=g) / R, torch.randn(R, generator=g) / R
+    mlp = mlp_forward_bf16emu if precision == "bf16" else O.mlp_forward
+
+    ro_, d_, vw_ = ro.clone().requires_grad_(True), d.clone().requires_grad_(True), vw.clone().requires_grad_(True)
+    P = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    z = O.stratified_z(R, 128, 0.01, 10.0, noise)
+    pts = (ro_.unsqueeze(1) + d_.unsqueeze(1) * z.unsqueeze(-1)).reshape(-1, 3)
+    view = (-vw_).unsqueeze(1).expand(R, 128, 3).reshape(-1, 3)
+    rgb_s, dens = mlp(P, pts, view, "softplus", dist_alpha)
+    rgb, dist, w, alpha = O.composite(dens.reshape(R, 128), rgb_s.reshape(R, 128, 3), z, dist_alpha=dist_alpha)
+    ((rgb * p_rgb).sum() + (dist * p_dist).sum()).backward()
+
+    prec = _cabi.PREC_BF16 if precision == "bf16" else _cabi.PREC_FP32
+    rc = _ops.make_cfg(R, 128, 0.01, 10.0, 1, int(dist_alpha), 0, 1, prec)
+    params = [sd[k].to(dev()).requires_grad_(True) for k in _cabi.PARAM_ORDER]
+    packed = _ops.pack_weights([p.detach() for p in params]) if precision == "bf16" else None
+    rod, dd, vd = ro.to(dev()).requires_grad_(True), d.to(dev()).requires_grad_(True), vw.to(dev()).requires_grad_(True)
+    rgb2, dist2, w2, a2, z2 = _ops.RenderRaysEx.apply(rc, packed, rod, dd, vd, noise.to(dev()), *params)
+    ((rgb2 * p_rgb.to(dev())).sum() + (dist2 * p_dist.to(dev())).sum()).backward()
+    torch.cuda.synchronize()
+    assert torch.equal(z2.cpu(), z)
+    ftol = 1e-2 if precision == "bf16" else 2e-4
+    errs = dict(rgb=max_err(rgb2, rgb), alpha=max_err(a2, alpha), weights=max_err(w2, w), dist=max_err(dist2, dist) / 10.0)
+    print("extras fwd dist_alpha=%s %s: %s" % (dist_alpha, precision, {k: "%.2e" % e for k, e in errs.items()}))
+    assert max(errs.values()) <= ftol, errs
+    gtol = 5e-2 if precision == "bf16" else 2e-3
+    gerr = {k: _rel_l2(p.grad, P[k].grad) for k, p in zip(_cabi.PARAM_ORDER, params)}
+    gerr["d_ray_o"], gerr["d_dirs"], gerr["d_view"] = _rel_l2(rod.grad, ro_.grad), _rel_l2(dd.grad, d_.grad), _rel_l2(vd.grad, vw_.grad)
+    print("extras bwd dist_alpha=%s %s: worst rel-L2 %.3e" % (dist_alpha, precision, max(gerr.values())), {k: "%.1e" % e for k, e in gerr.items()})
+    assert max(gerr.values()) <= gtol, gerr
+    # forward-only entry point gives the same numbers
+    rgb3, dist3, _, _, _ = _ops.render_nograd(rc, [p.detach() for p in params], packed, rod.detach(), dd.detach(), noise.to(dev()),
+                                              ray_o=rod.detach(), view=vd.detach())
+    assert max_err(rgb3, rgb2) <= (1e-6 if precision == "fp32" else 0.0) and max_err(dist3, dist2) <= (1e-5 if precision == "fp32" else 0.0)

@@ -1,5 +1,6 @@
 """Pins the CPU oracle (oracle/nope_oracle.py) against fixtures produced by the reference itself
 (oracle/make_golden.py).  CPU only.  Tolerances: fp32 paths 1e-5 relative (north_star)."""
+import pytest
 import torch
 
 from oracle import nope_oracle as O
@@ -163,3 +164,40 @@ def test_train_step_loss_and_grads(golden):
         if "mlp_grads" in rec:
             for k, v in rec["mlp_grads"].items():
                 close(P[k].grad, v, rtol=1e-4, atol=1e-6)
+
+
+def _variant_cfg(over):
+    import copy
+    cfg = copy.deepcopy(syn.default_cfg())
+    for sec, kv in over.items():
+        cfg[sec].update(kv)
+    return cfg
+
+
+@pytest.mark.parametrize("name", ["llff", "dist_alpha_uniform", "white_relu_nodir"])
+def test_render_variants(golden, name):
+    """Non-default renderer branches against the reference's own Renderer: NDC sampling + dist_alpha
+    (configs/LLFF/fern.yaml), dist_alpha with uniform sampling, white background + relu density + use_ray_dir False."""
+    g = golden("render_variants")
+    i, v = g["inputs"], g[name]
+    cfg = _variant_cfg(v["override"])
+    scene = syn.make_scene("tiny")
+    P = _params(True)
+    wm = i["world_mat"].clone().requires_grad_(True)
+    cm = i["camera_mat"].clone().requires_grad_(True)
+    tr = O.render(P, i["pixels"], i["depth"], cm, wm, scene["scale_mat"], cfg["rendering"], noise=i["noise"][0], eval_=False,
+                  occ_activation=cfg["model"]["occ_activation"])
+    for k in ("rgb", "z_vals", "depth_pred", "depth_gt", "alpha"):
+        assert tr[k].shape == v["train"][k].shape, k
+        close(tr[k].detach(), v["train"][k], atol=2e-6)
+    ((tr["rgb"] * i["probe_rgb"]).sum() + (tr["depth_pred"] * i["probe_dist"][:tr["depth_pred"].shape[0]]).sum()).backward()
+    close(wm.grad, v["grad_world_mat"], rtol=1e-3, atol=1e-6)
+    close(cm.grad, v["grad_camera_mat"], rtol=1e-3, atol=1e-6)
+    for k, st in v["mlp_grad_stats"].items():
+        gr = P[k].grad
+        close(torch.stack([gr.sum(), gr.abs().sum(), (gr * gr).sum()]), st, rtol=1e-4, atol=1e-6)
+    with torch.no_grad():
+        ev = O.render(_params(), i["pixels"], i["depth"], i["camera_mat"], i["world_mat"], scene["scale_mat"], cfg["rendering"],
+                      noise=None, eval_=True, occ_activation=cfg["model"]["occ_activation"])
+    for k in ("rgb", "z_vals", "depth_pred", "depth_gt", "alpha"):
+        close(ev[k], v["eval"][k], atol=2e-6)
