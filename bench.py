@@ -296,6 +296,17 @@ def extras(dev, cfg, scene, tr, precision):
     ms = med_ms(lambda: _ops.chamfer_nn(a, b), 5)
     out["cfg5_chamfer_100k_ms_per_direction"] = ms
     out["cfg5_chamfer_gpairs_per_s"] = 1e10 / ms / 1e6
+    out["cfg5_chamfer_order"] = "clouds in random order (every 256-point stage spans the scene: no stage can be skipped)"
+    # back-projected depth clouds in raster order, second cloud moved by a small rigid offset
+    hh, ww = 250, 400
+    v, u = torch.meshgrid(torch.linspace(-0.75, 0.75, hh), torch.linspace(-1, 1, ww), indexing="ij")
+    zz = 2.0 + 0.3 * torch.sin(3 * u) * torch.cos(2 * v)
+    a2 = torch.stack([u * zz, v * zz, -zz], -1).reshape(-1, 3)
+    b2 = (a2 + torch.tensor([0.013, -0.007, 0.02]) + 1e-3 * torch.randn(a2.shape, generator=g)).to(dev)
+    a2 = a2.to(dev)
+    ms = med_ms(lambda: _ops.chamfer_nn(a2, b2), 5)
+    out["cfg5_chamfer_100k_raster_ms_per_direction"] = ms
+    out["cfg5_chamfer_raster_gpairs_per_s"] = 1e10 / ms / 1e6
     return out
 
 

@@ -16,7 +16,7 @@
 size_t nnb_chamfer_tc_workspace_bytes(int n_src, int n_dst);
 size_t nnb_chamfer_tc_norm2_offset(int n_src, int n_dst);
 int nnb_chamfer_tc_bound(const float *src, int n_src, const float *dst, int n_dst, unsigned int *bound, unsigned int *stats, void *workspace,
-                         unsigned long long *best_init, unsigned long long *best, cudaStream_t s);
+                         unsigned long long *best_init, unsigned long long *best, int use_f16, cudaStream_t s);
 
 #define CH_THREADS 128
 #define CH_SPT 4      // sources per thread
@@ -325,10 +325,10 @@ int nnb_chamfer_nn(const float *src, int n_src, const float *dst, int n_dst, int
     NNB_CHECK_LAUNCH();
     chamfer_nn_kernel<true><<<dim3(gx, gy), CH_THREADS, 0, s>>>(src, n_src, dst, n_dst, per, bound, qqmax, best, nullptr, nullptr);
   } else if (g_chamfer_pass1_cuda_cores == 0) {
-    const int rc = nnb_chamfer_tc_bound(src, n_src, dst, n_dst, bound, tc_stats, tc_ws, best, best, s);
+    const int rc = nnb_chamfer_tc_bound(src, n_src, dst, n_dst, bound, tc_stats, tc_ws, best, best, 1, s);
     if (rc) return rc;
   } else {
-    const int rc = nnb_chamfer_tc_bound(src, n_src, dst, n_dst, bound, tc_stats, tc_ws, best, nullptr, s);
+    const int rc = nnb_chamfer_tc_bound(src, n_src, dst, n_dst, bound, tc_stats, tc_ws, best, nullptr, 0, s);
     if (rc) return rc;
     chamfer_nn_kernel<true><<<dim3(gx, gy), CH_THREADS, 0, s>>>(src, n_src, dst, n_dst, per, bound, tc_stats + 1, best, tc_norm2, tc_stats);
   }

@@ -123,7 +123,7 @@ def chamfer_pass1(request):
     K.lib().nnb_debug_chamfer_pass1(old)
 
 
-@pytest.mark.parametrize("n,m", [(1, 1), (5, 4099), (3000, 2000), (28830, 28830)])
+@pytest.mark.parametrize("n,m", [(1, 1), (5, 4099), (3000, 2000), (28830, 28830), (60000, 700)])
 def test_chamfer_indices_bit_exact_vs_oracle(n, m, chamfer_pass1):
     from model import _ops
     from oracle import nope_oracle as O

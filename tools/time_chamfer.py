@@ -11,6 +11,15 @@ g = torch.Generator().manual_seed(0)
 a = torch.rand(P, 3, generator=g)
 a = torch.stack([(a[:, 0] * 2 - 1) * 2, (a[:, 1] * 1.5 - 0.75) * 2, -(1.5 + a[:, 2])], 1).to(dev)
 b = (a + 0.01 * torch.randn(P, 3, generator=g).to(dev))[torch.randperm(P, generator=g).to(dev)]
+if "--raster" in sys.argv:
+    # back-projected depth maps in raster order (what the training step feeds): two smooth surfaces a small rigid offset apart
+    hh = int(round((P / 1.2) ** 0.5))
+    ww = (P + hh - 1) // hh
+    v, u = torch.meshgrid(torch.linspace(-0.75, 0.75, hh), torch.linspace(-1, 1, ww), indexing="ij")
+    zz = 2.0 + 0.3 * torch.sin(3 * u) * torch.cos(2 * v)
+    a = torch.stack([u * zz, v * zz, -zz], -1).reshape(-1, 3)[:P]
+    b = (a + torch.tensor([0.013, -0.007, 0.02]) + 1e-3 * torch.randn(a.shape, generator=g)).to(dev)
+    a = a.to(dev)
 for mode, name in ((0, "tcgen05 both"), (2, "tcgen05 + cc exact"), (1, "cuda cores both")):
     K.lib().nnb_debug_chamfer_pass1(mode)
     for _ in range(3):
