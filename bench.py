@@ -27,6 +27,9 @@ import torch  # noqa: E402
 import synthetic_scene as syn  # noqa: E402
 
 FLOP_PER_RAY_TRAIN = 455_737_344  # 3,560,448 FLOP/sample x 128 (fwd + bwd, padding/recompute not counted)
+# weight gradient: bytes it must read per ray = saved operand images X (H0..H7, feature, Hc, enc, aux: 647,168 B) + dY images
+# (8 trunk, feature, Hc, heads: 626,688 B), each once
+WGRAD_BYTES_PER_RAY = 647_168 + 626_688
 RAYS_PER_GPU = 4096
 METRIC = "training rays/sec (fwd+bwd, 128 samples/ray)"
 
@@ -125,8 +128,10 @@ def run_b200(args):
     for i in range(n):
         b = syn.make_batch(scene, i, i + 1 if i < n - 1 else i - 1)
         host_batches.append({k: (v.pin_memory() if torch.is_tensor(v) else v) for k, v in b.items()})
-    dev_batches = [{k: (v.to(dev) if torch.is_tensor(v) and k not in ("img.idx", "img.ref_idxs") else v) for k, v in b.items()}
-                   for b in host_batches]
+    # `value` leg: the sequence lives in HBM (model.ResidentScene); a step's batch is a dict of views
+    import model as mdl
+    resident = mdl.ResidentScene(host_batches, dev)
+    dev_batches = [resident.batch(i, i + 1 if i < n - 1 else i - 1) for i in range(n)]
 
     def sync_all():
         torch.cuda.synchronize()
@@ -209,8 +214,19 @@ def run_b200(args):
     # per-entry-point device time over a few extra (untimed) steps: roofline of the dominant stage
     _cabi.profile = {}
     prof_steps = min(3, args.steps)
+    import ctypes
+    bwd_ms = (ctypes.c_float * 2)()
+    split = [0.0, 0.0]
+    if args.precision == "bf16":
+        _cabi.lib().nnb_debug_bwd_timing(1, None)
     for it in range(prof_steps):
         tr.train_step(dev_batches[it % n], it=it, epoch=0, scheduling_start=sched)
+        if args.precision == "bf16":
+            _cabi.lib().nnb_debug_bwd_timing(1, bwd_ms)      # CUDA events around the two backward kernels of this step
+            split[0] += bwd_ms[0] / prof_steps
+            split[1] += bwd_ms[1] / prof_steps
+    if args.precision == "bf16":
+        _cabi.lib().nnb_debug_bwd_timing(0, None)
     _cabi.profile_flush()
     prof = {k: v[0] / prof_steps for k, v in _cabi.profile.items()}
     _cabi.profile = None
@@ -219,6 +235,23 @@ def run_b200(args):
     peak_tf = pk.get("bf16_tflops_sustained", pk.get("bf16_tflops"))
     achieved_tf = FLOP_PER_RAY_TRAIN * RAYS_PER_GPU / (mlp_ms * 1e-3) / 1e12 if mlp_ms > 0 else 0.0
 
+    # per-kernel rooflines: forward and data-gradient chain against the tensor pipe (1/3 of the training FLOPs
+    # each), weight gradient against HBM (it streams every saved activation / dY image once: 1,274,880 B per ray)
+    kernels = None
+    if args.precision == "bf16" and split[0] > 0:
+        hbm = pk.get("hbm_gbs", 6650.0)
+        f_third = FLOP_PER_RAY_TRAIN / 3.0 * RAYS_PER_GPU
+        fwd_ms = prof.get("nnb_render_fwd", 0.0)
+        wg_bytes = WGRAD_BYTES_PER_RAY * RAYS_PER_GPU
+        kernels = [
+            {"kernel": "tc_fwd_kernel<save>", "ms": fwd_ms, "bound": "tensor", "achieved": f_third / fwd_ms / 1e9, "peak": peak_tf,
+             "unit": "TFLOP/s", "frac": f_third / fwd_ms / 1e9 / peak_tf},
+            {"kernel": "tc_bwd_kernel (dgrad chain)", "ms": split[0], "bound": "tensor", "achieved": f_third / split[0] / 1e9,
+             "peak": peak_tf, "unit": "TFLOP/s", "frac": f_third / split[0] / 1e9 / peak_tf},
+            {"kernel": "tc_wgrad_kernel", "ms": split[1], "bound": "hbm", "achieved": wg_bytes / split[1] / 1e6, "peak": hbm,
+             "unit": "GB/s", "frac": wg_bytes / split[1] / 1e6 / hbm,
+             "tensor_frac": f_third / split[1] / 1e9 / peak_tf},
+        ]
     rays_per_s = rays_global * args.steps / (ms * 1e-3)
     rays_per_s_e2e = rays_global * args.steps / (ms_e2e * 1e-3)
     out = {
@@ -228,7 +261,7 @@ def run_b200(args):
         "config": {"workload": "cfg2: Virtual-KITTI-shaped synthetic scene, %d frames 375x1242, %d rays/step/GPU x 128 samples, "
                                "losses rgb+depth(l1, learned scale/shift)+Chamfer(28,830 pts)+reprojection, LearnPose, 3x Adam"
                                % (n, RAYS_PER_GPU),
-                   "global_rays": rays_global, "parallelism": "dp%d" % world, "precision": args.precision,
+                   "global_rays": rays_global, "resident_scene_bytes": resident.nbytes(), "parallelism": "dp%d" % world, "precision": args.precision,
                    "step": "eager launches" if args.no_graph else "CUDA graph replay (compute_loss + backward) + eager Adam",
                    "l2_policy": "working set per step (activation workspace %.1f GB) exceeds the 126 MB L2; no explicit flush"
                                 % (13.0e3 * RAYS_PER_GPU * 128 / 1e9 if args.precision == "fp32" else 1.31e6 * RAYS_PER_GPU / 1e9)},
@@ -243,7 +276,8 @@ def run_b200(args):
                      "traffic": 11.12e9 if args.precision == "bf16" else None, "traffic_unit": "B per step (ncu)",
                      "kernel": "nnb_render_fwd + nnb_render_bwd (sampling+encoding+MLP+compositing, fwd and bwd)",
                      "kernel_ms_per_step": mlp_ms, "peak_source": "%s bf16 sustained" % pk_kind,
-                     "algorithmic_flop_per_step": FLOP_PER_RAY_TRAIN * RAYS_PER_GPU},
+                     "algorithmic_flop_per_step": FLOP_PER_RAY_TRAIN * RAYS_PER_GPU,
+                     "kernels": kernels},
         "stages_ms_per_step": {k: round(v, 4) for k, v in sorted(prof.items(), key=lambda kv: -kv[1])},
     }
     if world == 1:

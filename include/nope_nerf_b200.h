@@ -203,6 +203,10 @@ int nnb_pack_weights(const float *const *params_host, void *packed, void *stream
 /* Debug aid: device buffer (>= 64 int64) that receives per-layer clock64 stamps of CTA 0 / first ray pair of
  * the following tensor-core forward launches; NULL switches it off. */
 int nnb_debug_set_trace(void *buf);
+/* Measurement hook: on != 0 makes every later tensor-core nnb_render_bwd record CUDA events around its two kernels (data-gradient
+ * chain, weight gradient) on the call's stream; ms2 != NULL (HOST pointer, 2 floats) first reads the last recorded pair
+ * {dgrad ms, wgrad ms} (synchronises on that call).  Do not enable while capturing a CUDA graph. */
+int nnb_debug_bwd_timing(int on, float *ms2);
 
 /* ------------------------------------------------------------------------------------------
  * Stage 4 -- rgb / depth / reprojection losses

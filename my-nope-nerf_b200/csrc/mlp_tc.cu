@@ -1440,6 +1440,9 @@ const std::vector<uint4> &bwd_groups() {
 }
 
 long long *g_trace = nullptr;
+// debug timing of the two backward kernels (nnb_debug_bwd_timing): events around tc_bwd_kernel and tc_wgrad_kernel
+int g_bwd_timing = 0;
+cudaEvent_t g_bwd_ev[3] = {nullptr, nullptr, nullptr};
 std::once_flag g_tables_once;
 int g_tables_err = 0;
 
@@ -1548,8 +1551,14 @@ int nnb_tc_render_bwd(const nnb_render_cfg *cfg, const float *const *params, con
   int grid = n_pairs < nnb_sm_count() ? n_pairs : nnb_sm_count();
   grid = (grid + 1) & ~1;                       // 2-CTA clusters
   if (grid > (nnb_sm_count() & ~1)) grid = nnb_sm_count() & ~1;
+  if (g_bwd_timing) {
+    for (int i = 0; i < 3; ++i)
+      if (!g_bwd_ev[i]) NNB_CUDA(cudaEventCreate(&g_bwd_ev[i]));
+    NNB_CUDA(cudaEventRecord(g_bwd_ev[0], s));
+  }
   tc_bwd_kernel<<<grid, 320, SB_TOTAL, s>>>(B);
   NNB_CHECK_LAUNCH();
+  if (g_bwd_timing) NNB_CUDA(cudaEventRecord(g_bwd_ev[1], s));
   WgArgs W{};
   W.ws_fwd = B.ws_fwd; W.ws_bwd = B.ws_bwd;
   W.trace = g_trace;
@@ -1557,12 +1566,23 @@ int nnb_tc_render_bwd(const nnb_render_cfg *cfg, const float *const *params, con
   W.n_tiles = R; W.n_jobs = (int)wg_plan().jobs.size();
   tc_wgrad_kernel<<<wg_plan().n_ctas, 192, SW_TOTAL, s>>>(W);
   NNB_CHECK_LAUNCH();
+  if (g_bwd_timing) NNB_CUDA(cudaEventRecord(g_bwd_ev[2], s));
   return 0;
 }
 
 extern "C" {
 /* debug: device buffer of >= 64 int64 receiving clock64 stamps of CTA 0 / pair 0 of the next forward launches */
 int nnb_debug_set_trace(void *buf) { g_trace = static_cast<long long *>(buf); return 0; }
+
+int nnb_debug_bwd_timing(int on, float *ms2) {
+  if (ms2 && g_bwd_ev[2]) {   // read the last timed backward (synchronises on its last event)
+    NNB_CUDA(cudaEventSynchronize(g_bwd_ev[2]));
+    NNB_CUDA(cudaEventElapsedTime(ms2, g_bwd_ev[0], g_bwd_ev[1]));
+    NNB_CUDA(cudaEventElapsedTime(ms2 + 1, g_bwd_ev[1], g_bwd_ev[2]));
+  }
+  g_bwd_timing = on;
+  return 0;
+}
 
 size_t nnb_pack_weights_bytes(void) { return (size_t)fwd_schedule().bytes + (size_t)bwd_schedule().bytes; }
 

@@ -69,6 +69,7 @@ SIGNATURES = {
     "nnb_pack_weights_bytes": [],
     "nnb_pack_weights": [_pp, _p, _p],
     "nnb_debug_set_trace": [_p],
+    "nnb_debug_bwd_timing": [_i, C.POINTER(C.c_float)],
     "nnb_rgb_loss_fwd": [_p, _p, _i, _p, _p],
     "nnb_rgb_loss_bwd": [_p, _p, _i, _p, _p, _p],
     "nnb_depth_l1_fwd": [_p, _p, _p, _i, _p, _p],

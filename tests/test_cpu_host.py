@@ -210,3 +210,25 @@ def test_data_parallel_plumbing_gloo_world2(tmp_path):
     port = 29500 + (os.getpid() % 2000)
     mp.spawn(_gloo_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
     assert os.path.exists(tmp_path / "ok0") and os.path.exists(tmp_path / "ok1")
+
+
+def test_resident_scene_schema_on_cpu():
+    """ResidentScene is plain tensor bookkeeping: on the CPU device it must reproduce the batch schema and the
+    reference-frame rule of dataloading/dataset.py:295-301."""
+    import random
+    sys.path.insert(0, PKG)
+    from model.scene import ResidentScene
+    scene = syn.make_scene("tiny")
+    n = scene["n"]
+    rs = ResidentScene([syn.make_batch(scene, i) for i in range(n)], torch.device("cpu"), random_ref=2)
+    rng = random.Random(0)
+    for f in range(n):
+        for _ in range(4):
+            r = rs.ref_index(f, rng)
+            assert (r == f - 1) if f == n - 1 else (f + 1 <= r <= min(f + 2, n - 1))
+    b, hb = rs.batch(2, 3), syn.make_batch(scene, 2, 3)
+    assert set(b) == set(hb)
+    for k, v in hb.items():
+        assert torch.equal(b[k].reshape(v.shape), v), k
+    with pytest.raises(ValueError):
+        ResidentScene([syn.make_batch(scene, 0), syn.make_batch(scene, 2)], torch.device("cpu"))

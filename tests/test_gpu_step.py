@@ -179,3 +179,39 @@ def test_graphed_step_matches_eager_step(golden):
             assert abs(a[k] - b[k]) <= 1e-5 + 2e-4 * abs(a[k]), (k, a[k], b[k])
     for a, b in zip(p0, p1):
         assert_close(b, a, 1e-3, 1e-5, "parameter after graphed steps")
+
+
+def test_resident_scene_batches_match_host_batches(golden):
+    """ResidentScene: batches built from device-resident frames are the same tensors as the host
+    batches, and a graphed step on them gives the same losses as the eager step on the host batch."""
+    import model as mdl
+    g = golden("render_step")
+    cfg = syn.default_cfg()
+    scene = syn.make_scene("tiny")
+    R = syn.SHAPES["tiny"][3]
+    n = scene["n"]
+    rs = mdl.ResidentScene([syn.make_batch(scene, i) for i in reversed(range(n))], dev())
+    assert rs.n_frames == n and rs.nbytes() > 0
+    for f in (0, n - 1):
+        ref = rs.ref_index(f)
+        assert ref == (f + 1 if f < n - 1 else f - 1)          # random_ref = 1 (dataloading/dataset.py:295-301)
+        hb, db = syn.make_batch(scene, f, ref), rs.batch(f)
+        assert set(hb) == set(db), (sorted(hb), sorted(db))
+        for k, v in hb.items():
+            assert torch.equal(db[k].cpu().reshape(v.shape), v), k
+            if k not in ("img.idx", "img.ref_idxs"):
+                assert db[k].is_cuda and db[k].data_ptr() >= rs.data[{"img.ref_imgs": "img", "img.ref_dpts": "img.dpt",
+                                                                     "img.ref_pose_gt": "img.pose_gt"}.get(k, k)].data_ptr()  # a view
+    sched = cfg["training"]["scheduling_start"]
+    out = []
+    for resident in (False, True):
+        tr, nerf, pose, dist = _trainer(cfg, scene, g["step_setup"], "l1", R)
+        tr.fixed_ray_idx, tr.fixed_noise = g["render"]["ray_idx"].to(dev()), g["render"]["noise"].to(dev())
+        ls = []
+        for it, f in enumerate([0, 1, n - 1]):
+            b = rs.batch(f) if resident else syn.make_batch(scene, f, f + 1 if f < n - 1 else f - 1)
+            ld = (tr.train_step_graphed if resident else tr.train_step)(b, it=it, epoch=0, scheduling_start=sched)
+            ls.append(float(ld["loss"]))
+        out.append(ls)
+    for a, b in zip(*out):
+        assert abs(a - b) <= 1e-5 + 2e-4 * abs(a), out
