@@ -200,6 +200,13 @@ int nnb_mlp_points_fwd(const float *const *params_host, const float *pts, const 
 size_t nnb_pack_weights_bytes(void);
 int nnb_pack_weights(const float *const *params_host, void *packed, void *stream);
 
+/* OfficialStaticNerf.gradient (model/official_nerf.py:46-58): grad (M,3) = -d raw_density / d p at explicit points (the
+ * surface normals of the phong renderer, model/rendering.py:255-260, and of normal_loss, :127-135), fp32 path.
+ * raw_out (M,) optional: fc_density output before the activation.  Forward only w.r.t. the parameters (no second order). */
+size_t nnb_mlp_points_grad_workspace_bytes(long long n_points);
+int nnb_mlp_points_density_grad(const float *const *params_host, const float *pts, long long n_points, float *grad,
+                                float *raw_out, void *workspace, size_t workspace_bytes, void *stream);
+
 /* Debug aid: device buffer (>= 64 int64) that receives per-layer clock64 stamps of CTA 0 / first ray pair of
  * the following tensor-core forward launches; NULL switches it off. */
 int nnb_debug_set_trace(void *buf);

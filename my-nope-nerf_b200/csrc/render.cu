@@ -313,4 +313,57 @@ int nnb_mlp_points_fwd(const float *const *P, const float *pts, const float *vie
   return 0;
 }
 
+// Workspace of nnb_mlp_points_density_grad: saved activations + two gradient buffers for one chunk of points.
+#define POINTS_GRAD_CHUNK (1 << 17)
+size_t nnb_mlp_points_grad_workspace_bytes(long long n_points) {
+  const size_t m = n_points < POINTS_GRAD_CHUNK ? (n_points > 0 ? n_points : 1) : POINTS_GRAD_CHUNK;
+  return m * (kSaveFloats + kBwdFloats) * sizeof(float);
+}
+
+// OfficialStaticNerf.gradient (model/official_nerf.py:46-58): grad (M,3) = -d fc_density(trunk(p)) / d p  (raw density, before
+// the activation; grad_outputs = ones), optionally also the raw density.  fp32 CUDA-core path: trunk forward with saved
+// activations, then the data-gradient chain only (no weight gradients).
+int nnb_mlp_points_density_grad(const float *const *P, const float *pts, long long n_points, float *grad, float *raw_out,
+                                void *workspace, size_t workspace_bytes, void *stream) {
+  if (!P || !pts || !grad || !workspace || n_points <= 0) return NNB_ERR_BAD_ARG;
+  if (workspace_bytes < nnb_mlp_points_grad_workspace_bytes(n_points)) return NNB_ERR_WORKSPACE;
+  cudaStream_t s = nnb_stream(stream);
+  const long long chunk = n_points < POINTS_GRAD_CHUNK ? n_points : POINTS_GRAD_CHUNK;
+  Fp32Buffers b;
+  carve_save(static_cast<float *>(workspace), (size_t)chunk, b);
+  for (long long m0 = 0; m0 < n_points; m0 += chunk) {
+    const long long M = n_points - m0 < chunk ? n_points - m0 : chunk;
+    encode_points_fwd_kernel<<<ew_grid(M * 3), 256, 0, s>>>(pts + 3 * m0, nullptr, M, b.X0, b.Hs, b.Fc);
+    NNB_CHECK_LAUNCH();
+    RET(linear_fwd(M, 256, 63, b.X0, 64, P[P_L0], P[P_L0 + 1], b.H0, 256, 1, s));
+    RET(linear_fwd(M, 256, 256, b.H0, 256, P[P_L1], P[P_L1 + 1], b.H1, 256, 1, s));
+    RET(linear_fwd(M, 256, 256, b.H1, 256, P[P_L2], P[P_L2 + 1], b.H2, 256, 1, s));
+    RET(linear_fwd(M, 256, 256, b.H2, 256, P[P_L3], P[P_L3 + 1], b.Hs, 320, 1, s));
+    RET(linear_fwd(M, 256, 319, b.Hs, 320, P[P_L4], P[P_L4 + 1], b.H3, 256, 1, s));
+    RET(linear_fwd(M, 256, 256, b.H3, 256, P[P_L5], P[P_L5 + 1], b.H4, 256, 1, s));
+    RET(linear_fwd(M, 256, 256, b.H4, 256, P[P_L6], P[P_L6 + 1], b.H5, 256, 1, s));
+    RET(linear_fwd(M, 256, 256, b.H5, 256, P[P_L7], P[P_L7 + 1], b.H8, 256, 1, s));
+    if (raw_out) {
+      head_density_fwd_kernel<<<ew_grid(M * 32), 256, 0, s>>>(b.H8, M, P[P_DEN], P[P_DEN + 1], 1, 1, raw_out + m0, b.alpha_mlp);
+      NNB_CHECK_LAUNCH();
+    }
+    // d_raw = 1 -> G0 = relu'(H8) * w_density
+    fill_kernel<<<ew_grid(M), 256, 0, s>>>(b.d_alpha, M, 1.0f);
+    NNB_CHECK_LAUNCH();
+    RET(dgrad(M, 1, 256, b.d_alpha, 1, P[P_DEN], 256, b.G0, 256, b.H8, 256, 0, s));
+    RET(dgrad(M, 256, 256, b.G0, 256, P[P_L7], 256, b.G1, 256, b.H5, 256, 0, s));
+    RET(dgrad(M, 256, 256, b.G1, 256, P[P_L6], 256, b.G0, 256, b.H4, 256, 0, s));
+    RET(dgrad(M, 256, 256, b.G0, 256, P[P_L5], 256, b.G1, 256, b.H3, 256, 0, s));
+    RET(dgrad(M, 256, 256, b.G1, 256, P[P_L4], 319, b.G0, 256, b.Hs, 320, 0, s));
+    RET(dgrad(M, 256, 63, b.G1, 256, P[P_L4] + 256, 319, b.Genc, 64, nullptr, 0, 0, s));
+    RET(dgrad(M, 256, 256, b.G0, 256, P[P_L3], 256, b.G1, 256, b.H2, 256, 0, s));
+    RET(dgrad(M, 256, 256, b.G1, 256, P[P_L2], 256, b.G0, 256, b.H1, 256, 0, s));
+    RET(dgrad(M, 256, 256, b.G0, 256, P[P_L1], 256, b.G1, 256, b.H0, 256, 0, s));
+    RET(dgrad(M, 256, 63, b.G1, 256, P[P_L0], 63, b.Genc, 64, nullptr, 0, 1, s));
+    encode_points_bwd_kernel<<<ew_grid(M * 3), 256, 0, s>>>(b.X0, b.Genc, M, -1.0f, grad + 3 * m0);
+    NNB_CHECK_LAUNCH();
+  }
+  return 0;
+}
+
 }  // extern "C"

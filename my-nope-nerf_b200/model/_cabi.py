@@ -66,6 +66,8 @@ SIGNATURES = {
     "nnb_composite_bwd": [_p, _p, _p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p],
     "nnb_mlp_points_workspace_bytes": [C.c_longlong],
     "nnb_mlp_points_fwd": [_pp, _p, _p, C.c_longlong, _i, _i, _p, _p, _p, _sz, _p],
+    "nnb_mlp_points_grad_workspace_bytes": [C.c_longlong],
+    "nnb_mlp_points_density_grad": [_pp, _p, C.c_longlong, _p, _p, _p, _sz, _p],
     "nnb_pack_weights_bytes": [],
     "nnb_pack_weights": [_pp, _p, _p],
     "nnb_debug_set_trace": [_p],
@@ -94,7 +96,7 @@ SIGNATURES = {
     "nnb_adam_step": [_p, _p, _p, _p, _sz, _f, _f, _f, _f, _i, _p],
 }
 _RESTYPE = {"nnb_error_string": C.c_char_p, "nnb_launch_count": C.c_ulonglong, "nnb_render_workspace_bytes": C.c_size_t, "nnb_pack_weights_bytes": C.c_size_t, "nnb_chamfer_workspace_bytes": C.c_size_t,
-            "nnb_mlp_points_workspace_bytes": C.c_size_t}
+            "nnb_mlp_points_workspace_bytes": C.c_size_t, "nnb_mlp_points_grad_workspace_bytes": C.c_size_t}
 
 _lib = None
 launch_count = 0  # number of C-ABI calls that launch kernels (bench.py reports it)

@@ -611,6 +611,21 @@ def mlp_points(params, pts, viewdirs, occ_softplus, dist_alpha):
     return rgb, dens.reshape(M, 1)
 
 
+def mlp_points_density_grad(params, pts, want_raw=False):
+    """-d fc_density(trunk(p)) / d p at explicit points (OfficialStaticNerf.gradient, model/official_nerf.py:46-58).
+    pts (M,3) -> grad (M,3) [, raw density (M,)]."""
+    pts = f32(pts.detach()).reshape(-1, 3)
+    M = pts.shape[0]
+    dev = pts.device
+    params = [f32(p.detach()) for p in params]
+    grad = torch.empty(M, 3, device=dev)
+    raw = torch.empty(M, device=dev) if want_raw else None
+    nbytes = int(K.lib().nnb_mlp_points_grad_workspace_bytes(M))
+    ws = _workspace(dev, nbytes, "mlp_points_grad")
+    call("nnb_mlp_points_density_grad", K.param_ptr_array(params), ptr(pts), M, ptr(grad), ptr(raw), ptr(ws), nbytes, stream())
+    return (grad, raw) if want_raw else grad
+
+
 def pack_weights(params):
     """bf16 tile images of the 24 tensors for the tcgen05 path (refreshed whenever the fp32 masters change)."""
     nbytes = int(K.lib().nnb_pack_weights_bytes())

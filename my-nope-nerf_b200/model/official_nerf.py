@@ -66,7 +66,15 @@ class OfficialStaticNerf(nn.Module):
         return (rgb, dens) if return_addocc else rgb
 
     def infer_occ(self, p):
-        raise NotImplementedError("infer_occ/gradient (normal loss, phong renderer) are 'next' rows (SURVEY.md 8f rank 3)")
+        """model/official_nerf.py:60-67 -> (x, density).  The 256-wide trunk feature `x` never leaves the kernels; only the raw
+        density (before the activation) is returned, `x` is None.  Forward only."""
+        with torch.no_grad():
+            _, raw = _ops.mlp_points_density_grad(self.param_list(), p.reshape(-1, 3), want_raw=True)
+        return None, raw.reshape(-1, 1)
 
     def gradient(self, p, it):
-        raise NotImplementedError("infer_occ/gradient (normal loss, phong renderer) are 'next' rows (SURVEY.md 8f rank 3)")
+        """model/official_nerf.py:46-58: -d raw_density / d p, shape (M,1,3).  First order only (the reference builds the graph
+        for `normal_loss`, which is not supported here)."""
+        with torch.no_grad():
+            g = _ops.mlp_points_density_grad(self.param_list(), p.reshape(-1, 3))
+        return g.unsqueeze(1)

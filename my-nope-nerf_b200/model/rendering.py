@@ -9,7 +9,7 @@ loss stack consume the dense tensors + mask without the reference's boolean-inde
 import torch
 import torch.nn as nn
 
-from . import _cabi, _ops
+from . import _cabi, _ops, geometry
 
 # rays per fused-render call when saving for backward (bounds the activation workspace)
 MAX_TRAIN_RAYS_FP32 = 8192
@@ -36,8 +36,22 @@ class Renderer(nn.Module):
             return self.nope_nerf(pixels, depth, camera_mat, world_mat, scale_mat, it=it, add_noise=add_noise,
                                   eval_=eval_, noise=noise, lazy_mask=lazy_mask)
         if rendering_technique == 'phong_renderer':
-            raise NotImplementedError("phong_renderer is a 'next' row (SURVEY.md 8f rank 3), off the hot path")
+            return self.phong_renderer(pixels, camera_mat, world_mat, scale_mat, it=it)
         raise ValueError("unknown rendering technique %r" % (rendering_technique,))
+
+    def phong_renderer(self, pixels, camera_mat, world_mat, scale_mat, it):
+        """model/rendering.py:203-271: sphere-traced surface, normals from the density gradient, phong shading (geometry.py)."""
+        with torch.no_grad():
+            ones = torch.ones(1, pixels.shape[1], 1, device=pixels.device)
+            origin, dirs, _, _, _ = _ops.RayGen.apply(pixels, ones, camera_mat, world_mat, scale_mat, True)
+        return geometry.phong_render(self, origin, dirs, it=it)
+
+    def ray_marching(self, ray0, ray_direction, model, c=None, tau=0.5, n_steps=[128, 129], n_secant_steps=8,
+                     depth_range=[0., 2.4], max_points=3500000, rad=1.0):
+        """Reference signature (model/rendering.py:274): ray0 (1,R,3) repeated camera centre, ray_direction (1,R,3) -> (1,R)."""
+        return geometry.ray_marching(model, ray0[0, 0], ray_direction[0], tau=0.5, n_steps=int(n_steps[0]),
+                                     n_secant_steps=n_secant_steps, depth_range=depth_range, max_points=max_points,
+                                     rad=rad).unsqueeze(0)
 
     def to(self, device):
         new = super().to(device)

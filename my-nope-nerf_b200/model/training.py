@@ -379,4 +379,10 @@ class Trainer(object):
             out = self.model.renderer(pixels.unsqueeze(0), torch.ones(1, h * w, 1, device=self.device), camera_mat, world_mat,
                                       scale_mat, self.rendering_technique, add_noise=False, eval_=True, it=it)
         rgb = out['rgb'].view(h, w, 3)
+        if self.vis_geo:
+            # model/training.py:146-163: the phong-shaded geometry image is what the reference returns when vis_geo is on
+            with torch.no_grad():
+                geo = self.model(pixels.unsqueeze(0), None, camera_mat, world_mat, scale_mat, 'phong_renderer', add_noise=False,
+                                 eval_mode=True, it=it, depth_img=depth_input, img_size=(h, w))['rgb']
+            rgb = geo.view(h, w, 3)
         return (rgb * 255).to(torch.uint8).cpu().numpy()

@@ -273,8 +273,56 @@ def variant_vectors(ref, cfg0):
     return out
 
 
+def geometry_state(sd):
+    """Random-init weights put the whole field on one side of the occupancy threshold (raw density 0.096 +- 0.004): scale the
+    density head so that the field crosses tau = 0.5 inside the sphere (raw = 0 <=> occupancy 0.5)."""
+    sd = {k: v.clone() for k, v in sd.items()}
+    sd["fc_density.weight"] = sd["fc_density.weight"] * 200.0
+    sd["fc_density.bias"] = torch.tensor([0.86])
+    return sd
+
+
+def geometry_vectors(ref, cfg):
+    """OfficialStaticNerf.gradient, Renderer.ray_marching (+ secant) and Renderer.phong_renderer of the
+    reference on a field with surfaces (geometry_state)."""
+    out = {"torch_version": torch.__version__}
+    scene = syn.make_scene("tiny")
+    h, w = scene["h"], scene["w"]
+    sd = geometry_state(syn.init_mlp_state(42))
+    nerf, renderer, net = build_ref_model(ref, cfg, sd)
+    g = torch.Generator().manual_seed(31)
+    pts = (torch.rand(300, 3, generator=g) - 0.5) * 6
+    grad = nerf.gradient(pts.clone(), 0).detach()
+    with torch.no_grad():
+        _, raw = nerf.infer_occ(pts)
+        occ = nerf(pts, only_occupancy=True)
+    out["gradient"] = {"pts": pts, "grad": grad, "raw": raw, "occ": occ}
+    R = 96
+    ray_idx = torch.randperm(h * w, generator=g)[:R]
+    _, p_full = ref.common.arange_pixels((h, w))
+    p = p_full[:, ray_idx]
+    world_mat = torch.inverse(scene["poses_gt"][1]).unsqueeze(0)
+    cam_w = ref.common.origin_to_world(R, scene["camera_mat"], world_mat, scene["scale_mat"])
+    pix_w = ref.common.image_points_to_world(p, scene["camera_mat"], world_mat, scene["scale_mat"])
+    rv = pix_w - cam_w
+    rv = rv / rv.norm(2, 2).unsqueeze(-1)
+    nerf.eval()
+    with torch.no_grad():
+        d_i = renderer.ray_marching(cam_w, rv, nerf, n_secant_steps=8, n_steps=[512, 513], rad=cfg["rendering"]["radius"])
+    ph = renderer.phong_renderer(p, scene["camera_mat"], world_mat, scene["scale_mat"], 0)
+    out["phong"] = {"pixels": p, "world_mat": world_mat, "camera_world": cam_w[0, 0].clone(), "ray_dirs": rv[0].clone(), "d_i": d_i,
+                    "rgb": ph["rgb"].detach(), "rgb_surf": ph["rgb_surf"].detach()}
+    print("geometry: %d of %d rays hit a surface, %d start occupied" % (int(torch.isfinite(d_i).sum() - (d_i == 0).sum()), R, int((d_i == 0).sum())))
+    return out
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
+    if "--geometry-only" in sys.argv:
+        ref = ref_harness.load_reference()
+        torch.set_num_threads(max(1, os.cpu_count() or 1))
+        torch.save(geometry_vectors(ref, syn.default_cfg()), os.path.join(OUT, "geometry.pt"))
+        return
     if "--variants-only" in sys.argv:
         ref = ref_harness.load_reference()
         torch.set_num_threads(max(1, os.cpu_count() or 1))
@@ -287,6 +335,7 @@ def main():
     torch.save(loss_vectors(ref, cfg), os.path.join(OUT, "losses.pt"))
     torch.save(render_and_step_vectors(ref, cfg), os.path.join(OUT, "render_step.pt"))
     torch.save(variant_vectors(ref, cfg), os.path.join(OUT, "render_variants.pt"))
+    torch.save(geometry_vectors(ref, cfg), os.path.join(OUT, "geometry.pt"))
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

@@ -484,3 +484,90 @@ def train_loss(batch, P, pose, dist, cfg, ray_idx, noise, epoch=0, scheduling_st
                     rgb_loss_type=rgb_kind, depth_loss_type=ct["depth_loss_type"], **kw)
     ld["scale"], ld["shift"] = scale_in, shift_in
     return ld, out, kw
+
+
+# ----------------------------------------------------------------------------------------------
+# Geometry path: density gradient, sphere tracing, phong shading
+# ----------------------------------------------------------------------------------------------
+
+
+def occupancy(P, pts, occ_activation="softplus"):
+    """OfficialStaticNerf.forward(only_occupancy=True), model/official_nerf.py:69-85 (dist_alpha False)."""
+    _, raw = mlp_trunk(P, pts)
+    dens = F.softplus(raw) if occ_activation == "softplus" else raw.relu()
+    return 1 - torch.exp(-1.0 * dens)
+
+
+def density_gradient(P, pts):
+    """OfficialStaticNerf.gradient, model/official_nerf.py:46-58: -(d raw_density / d p), (M,1,3)."""
+    with torch.enable_grad():
+        p = pts.detach().clone().requires_grad_(True)
+        _, y = mlp_trunk(P, p)
+        g = torch.autograd.grad(y, p, torch.ones_like(y))[0]
+    return -g.detach().unsqueeze(1)
+
+
+def sphere_intersection(cam_loc, ray_directions, r=1.0):
+    """get_sphere_intersection, model/rendering.py:440-460.  cam_loc (3,), ray_directions (R,3) -> (R,2), mask (R,)."""
+    dot = ray_directions @ cam_loc
+    under = dot ** 2 - (cam_loc.norm(2) ** 2 - r ** 2)
+    mask = under > 0
+    out = torch.zeros(ray_directions.shape[0], 2)
+    out[mask] = torch.sqrt(under[mask]).unsqueeze(-1) * torch.tensor([-1.0, 1.0])
+    out[mask] -= dot[mask].unsqueeze(-1)
+    return out.clamp_min(0.0), mask
+
+
+def ray_marching(P, cam, dirs, tau=0.5, n_steps=512, n_secant_steps=8, depth_range=(0.0, 2.4), rad=1.0):
+    """Renderer.ray_marching + secant, model/rendering.py:274-419.  cam (3,), dirs (R,3) -> d (R,)."""
+    R = dirs.shape[0]
+    with torch.no_grad():
+        d_far = sphere_intersection(cam, dirs, rad)[0][:, 1]
+        u = torch.linspace(0, 1, steps=n_steps).view(1, n_steps)
+        d_prop = depth_range[0] * (1.0 - u) + d_far.view(R, 1) * u
+        p = cam.view(1, 1, 3) + dirs.unsqueeze(1) * d_prop.unsqueeze(-1)
+        val = (occupancy(P, p.reshape(-1, 3)).reshape(R, n_steps) - tau)
+        mask0 = val[:, 0] < 0
+        sign = torch.cat([torch.sign(val[:, :-1] * val[:, 1:]), torch.ones(R, 1)], dim=-1)
+        cost = sign * torch.arange(n_steps, 0, -1).float()
+        values, indices = torch.min(cost, -1)
+        ar = torch.arange(R)
+        mask = (values < 0) & (val[ar, indices] < 0) & mask0
+        hi = torch.clamp(indices + 1, max=n_steps - 1)
+        d_low, f_low = d_prop[ar, indices][mask], val[ar, indices][mask]
+        d_high, f_high = d_prop[ar, hi][mask], val[ar, hi][mask]
+        out = torch.ones(R)
+        if d_low.shape[0]:
+            dm = dirs[mask]
+            d_pred = -f_low * (d_high - d_low) / (f_high - f_low) + d_low
+            for _ in range(n_secant_steps):  # model/rendering.py:401-418
+                f_mid = occupancy(P, cam.view(1, 3) + d_pred.unsqueeze(-1) * dm).reshape(-1) - tau
+                low = f_mid < 0
+                d_low, f_low = torch.where(low, d_pred, d_low), torch.where(low, f_mid, f_low)
+                d_high, f_high = torch.where(low, d_high, d_pred), torch.where(low, f_high, f_mid)
+                d_pred = -f_low * (d_high - d_low) / (f_high - f_low) + d_low
+            out[mask] = d_pred
+        out[~mask] = float("inf")
+        out[~mask0] = 0
+    return out
+
+
+def phong(P, cam, dirs, rad):
+    """Renderer.phong_renderer, model/rendering.py:203-271 -> rgb (R,3) shaded, rgb_surf (R,3), d (R,)."""
+    d = ray_marching(P, cam, dirs, rad=rad)
+    with torch.no_grad():
+        zero_occ, pred = d == 0, torch.isfinite(d)
+        dists = torch.ones_like(d)
+        dists[pred] = d[pred]
+        dists[zero_occ] = 0.0
+        obj = pred & ~zero_occ
+        pts = cam.view(1, 3) + dirs * dists.unsqueeze(-1)
+        rgb, rgb_surf = torch.ones_like(pts), torch.zeros_like(pts)
+        if obj.any():
+            g = density_gradient(P, pts[obj])[:, 0, :]
+            n = g / g.norm(2, 1, keepdim=True)
+            light = (cam / cam.norm(2)).view(3, 1)
+            diffuse = torch.mm(n, light).clamp_min(0).repeat(1, 3) * 0.7
+            rgb[obj] = (0.3 + diffuse).clamp_max(1.0)
+            rgb_surf[obj] = mlp_forward(P, pts[obj], -dirs[obj])[0]
+    return rgb, rgb_surf, d

@@ -1,0 +1,84 @@
+"""GPU parity of the geometry path: OfficialStaticNerf.gradient / infer_occ, Renderer.ray_marching
+(+ secant) and Renderer.phong_renderer against fixtures made by the reference (tests/golden/geometry.pt,
+oracle/make_golden.py::geometry_vectors).  fp32 kernels; tolerances: field values 1e-4, input gradient 1e-3 relative to
+its scale, surface distances 1e-3 (the secant iteration divides by small occupancy differences), shaded colours 5e-3."""
+import pytest
+import torch
+
+from util import assert_close, dev, max_err, syn
+
+pytestmark = pytest.mark.gpu
+
+
+def _geometry_state():
+    sd = {k: v.clone() for k, v in syn.init_mlp_state(42).items()}
+    sd["fc_density.weight"] = sd["fc_density.weight"] * 200.0     # oracle/make_golden.py::geometry_state
+    sd["fc_density.bias"] = torch.tensor([0.86])
+    return sd
+
+
+def _renderer():
+    import model as mdl
+    cfg = syn.default_cfg()
+    nerf = mdl.OfficialStaticNerf(cfg)
+    nerf.load_state_dict(_geometry_state())
+    return cfg, nerf, mdl.Renderer(nerf, dict(cfg["rendering"], precision="fp32"), device=dev())
+
+
+def test_density_gradient_and_occupancy_vs_reference(golden):
+    g = golden("geometry")["gradient"]
+    _, nerf, _ = _renderer()
+    pts = g["pts"].to(dev())
+    grad = nerf.gradient(pts, 0)
+    assert grad.shape == g["grad"].shape
+    scale = float(g["grad"].abs().max())
+    print("density gradient max err %.3e (scale %.3e)" % (max_err(grad, g["grad"]), scale))
+    assert max_err(grad, g["grad"]) <= 1e-3 * scale
+    _, raw = nerf.infer_occ(pts)
+    assert_close(raw, g["raw"], 1e-4, 1e-4, "raw density")
+    occ = nerf(pts, only_occupancy=True)
+    assert_close(occ, g["occ"], 1e-4, 2e-5, "occupancy")
+    # more points than one chunk of the kernel: chunking must not change values
+    big = pts.repeat(500, 1)
+    gb = nerf.gradient(big, 0)
+    assert torch.equal(gb[:pts.shape[0]], gb[-pts.shape[0]:]) and max_err(gb[:pts.shape[0]], grad) == 0.0
+
+
+def test_ray_marching_and_phong_vs_reference(golden):
+    g = golden("geometry")["phong"]
+    cfg, nerf, renderer = _renderer()
+    scene = syn.make_scene("tiny")
+    cam = g["camera_world"].to(dev())
+    dirs = g["ray_dirs"].to(dev())
+    R = dirs.shape[0]
+    nerf.eval()
+    d = renderer.ray_marching(cam.view(1, 1, 3).expand(1, R, 3), dirs.unsqueeze(0), nerf, n_secant_steps=8, n_steps=[512, 513],
+                              rad=cfg["rendering"]["radius"])
+    ref = g["d_i"]
+    same_class = (torch.isfinite(d.cpu()) == torch.isfinite(ref)) & ((d.cpu() == 0) == (ref == 0))
+    assert same_class.float().mean() >= 0.98, "hit / miss / occupied classification"
+    ok = same_class & torch.isfinite(ref)
+    err = (d.cpu()[ok] - ref[ok]).abs().max()
+    print("surface distance max err %.3e over %d rays" % (float(err), int(ok.sum())))
+    assert float(err) <= 1e-3
+    out = renderer(g["pixels"].to(dev()), None, scene["camera_mat"].to(dev()), g["world_mat"].to(dev()), scene["scale_mat"].to(dev()),
+                   "phong_renderer", it=0)
+    assert set(out) == {"rgb", "normal", "rgb_surf"} and out["normal"] is None
+    m = ok[0]
+    print("phong rgb max err %.3e, surface colour max err %.3e" % (max_err(out["rgb"][0][m], g["rgb"][0][m]),
+                                                                  max_err(out["rgb_surf"][0][m], g["rgb_surf"][0][m])))
+    assert max_err(out["rgb"][0][m], g["rgb"][0][m]) <= 5e-3
+    assert max_err(out["rgb_surf"][0][m], g["rgb_surf"][0][m]) <= 5e-3
+
+
+def test_sphere_intersection_and_misses():
+    """Rays that miss the sphere or start inside occupied space (model/rendering.py:376-385 conventions: inf / 0)."""
+    from model import geometry
+    from oracle import nope_oracle as O
+    g = torch.Generator().manual_seed(4)
+    cam = torch.tensor([0.3, -0.2, 6.0])
+    dirs = torch.nn.functional.normalize(torch.randn(200, 3, generator=g) + torch.tensor([0., 0., -1.5]), dim=-1)
+    want, wmask = O.sphere_intersection(cam, dirs, 4.0)
+    got, gmask = geometry.get_sphere_intersection(cam.to(dev()), dirs.to(dev()), 4.0)
+    assert torch.equal(gmask.cpu(), wmask) and 0 < int(wmask.sum()) < 200
+    assert_close(got, want, 1e-5, 1e-5, "sphere intersections")

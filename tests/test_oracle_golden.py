@@ -201,3 +201,26 @@ def test_render_variants(golden, name):
                       noise=None, eval_=True, occ_activation=cfg["model"]["occ_activation"])
     for k in ("rgb", "z_vals", "depth_pred", "depth_gt", "alpha"):
         close(ev[k], v["eval"][k], atol=2e-6)
+
+
+def _geometry_params():
+    sd = syn.init_mlp_state(42)
+    sd = {k: v.clone() for k, v in sd.items()}
+    sd["fc_density.weight"] = sd["fc_density.weight"] * 200.0     # oracle/make_golden.py::geometry_state
+    sd["fc_density.bias"] = torch.tensor([0.86])
+    return sd
+
+
+def test_geometry_path(golden):
+    """SURVEY.md 8f rank 3 against the reference's own gradient / ray_marching / phong_renderer."""
+    g = golden("geometry")
+    P = _geometry_params()
+    gr = g["gradient"]
+    close(O.density_gradient(P, gr["pts"]), gr["grad"], rtol=1e-4, atol=1e-5)
+    with torch.no_grad():
+        close(O.occupancy(P, gr["pts"]), gr["occ"], atol=2e-6)
+    ph = g["phong"]
+    rgb, rgb_surf, d = O.phong(P, ph["camera_world"], ph["ray_dirs"], syn.default_cfg()["rendering"]["radius"])
+    close(d.unsqueeze(0), ph["d_i"], rtol=1e-4, atol=1e-5)
+    close(rgb.unsqueeze(0), ph["rgb"], rtol=1e-3, atol=1e-4)
+    close(rgb_surf.unsqueeze(0), ph["rgb_surf"], rtol=1e-3, atol=1e-4)
