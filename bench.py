@@ -110,7 +110,6 @@ def batch_bytes(b):
 
 
 def run_b200(args):
-    os.environ.setdefault("NCCL_DEBUG", "WARN")   # NCCL's version banner goes to stdout otherwise: stdout carries ONE JSON line
     from model import _cabi, parallel
     dp = parallel.init_from_env()
     world = dp.world_size
@@ -150,12 +149,7 @@ def run_b200(args):
         loss_events = [None, None]
 
         def upload(b):
-            with torch.cuda.stream(copy_stream):
-                d = {k: (v.to(dev, non_blocking=True) if torch.is_tensor(v) and k not in ("img.idx", "img.ref_idxs") else v)
-                     for k, v in b.items()}
-                ev = torch.cuda.Event()
-                ev.record(copy_stream)
-            return d, ev
+            return tr.upload_batch(b, copy_stream)   # the tensors the step reads (not img.gt_depths), on the copy stream
 
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
@@ -208,6 +202,13 @@ def run_b200(args):
     launches = _cabi.kernel_launches() + getattr(tr, "graphed_launches", 0) - l0   # eager launches + kernel nodes replayed
     # end to end: pinned host batch -> device every step, loss read back every step
     ms_e2e = timed(host_batches, args.steps, read_back=True)
+    if os.environ.get("NNB_E2E_PROBE"):   # debugging aid: where does the end-to-end leg lose time?
+        import time as _t
+        for label, fn in (("resident, no readback", lambda: timed(dev_batches, args.steps, read_back=False)),
+                          ("host batches + readback", lambda: timed(host_batches, args.steps, read_back=True))):
+            t0 = _t.perf_counter()
+            m = fn()
+            sys.stderr.write("[e2e probe] %s: %.3f ms/step device, %.3f ms/step wall\n" % (label, m / args.steps, (_t.perf_counter() - t0) * 1e3 / args.steps))
     sampler.stop_flag = True
     sampler.join(timeout=2)
 
@@ -266,7 +267,7 @@ def run_b200(args):
                    "l2_policy": "working set per step (activation workspace %.1f GB) exceeds the 126 MB L2; no explicit flush"
                                 % (13.0e3 * RAYS_PER_GPU * 128 / 1e9 if args.precision == "fp32" else 1.31e6 * RAYS_PER_GPU / 1e9)},
         "clocks": sampler.result(),
-        "e2e": {"value": rays_per_s_e2e, "unit": "rays/s", "h2d_bytes_per_step": batch_bytes(host_batches[0]),
+        "e2e": {"value": rays_per_s_e2e, "unit": "rays/s", "h2d_bytes_per_step": batch_bytes({k: v for k, v in host_batches[0].items() if k in tr.STEP_KEYS and k not in ("img.idx", "img.ref_idxs")}),
                 "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": launches,
         "roofline": {"bound": "tensor", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
@@ -285,7 +286,7 @@ def run_b200(args):
     if dp.rank == 0 and not args.no_cpu_baseline and world == 1:
         out["cpu_baseline"] = cpu_baseline(max_seconds=25.0)
     if dp.rank == 0:
-        print(json.dumps(out))
+        emit(out)
     if world > 1:
         torch.distributed.barrier()
         torch.distributed.destroy_process_group()
@@ -430,10 +431,29 @@ def run_reference(args):
                       "parallelism": "host cores"},
            "cpu_baseline": {"value": v, "unit": "rays/s", "cores": cores, "kind": "port", "sample": sample},
            "e2e": {"value": v, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(out))
+    emit(out)
+
+
+_JSON_OUT = None
+
+
+def claim_stdout():
+    """stdout carries ONE JSON line: anything a library prints to fd 1 (NCCL's version banner does, at NCCL_DEBUG=WARN/VERSION/INFO)
+    is sent to stderr instead; the JSON line goes to the saved descriptor."""
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = sys.stderr
+
+
+def emit(obj):
+    (_JSON_OUT or sys.stdout).write(json.dumps(obj) + "\n")
+    (_JSON_OUT or sys.stdout).flush()
 
 
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)

@@ -124,6 +124,23 @@ class Trainer(object):
         self._optimizer_tail()
         return slot['loss_dict']
 
+    # keys of the batch schema the training step reads (process_data_dict / process_data_reference); the DataLoader also yields
+    # `img.gt_depths` (evaluation only, model/training.py never moves it to the device)
+    STEP_KEYS = ('img', 'img.idx', 'img.dpt', 'img.depth', 'img.depth_mask', 'img.camera_mat', 'img.scale_mat', 'img.pose_gt',
+                 'img.ref_imgs', 'img.ref_dpts', 'img.ref_depths', 'img.ref_idxs', 'img.ref_pose_gt')
+
+    def upload_batch(self, data, stream=None):
+        """Host batch (pinned, as the DataLoader yields it) -> dict with the tensors the step reads on the device, copied
+        asynchronously on `stream` (default: the current stream); the two frame indices stay on the host.  Returns
+        (device_batch, event) -- make the compute stream wait on the event before the step."""
+        stream = stream or torch.cuda.current_stream()
+        with torch.cuda.stream(stream):
+            out = {k: (v.to(self.device, non_blocking=True) if torch.is_tensor(v) and k not in ('img.idx', 'img.ref_idxs') else v)
+                   for k, v in data.items() if k in self.STEP_KEYS}
+            ev = torch.cuda.Event()
+            ev.record(stream)
+        return out, ev
+
     def _all_nets(self):
         return [m for m in (self.model, self.pose_param_net, self.distortion_net, self.focal_net) if m is not None]
 
