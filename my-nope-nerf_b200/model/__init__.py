@@ -16,5 +16,5 @@ from model.distortions import Learn_Distortion
 from model.losses import Loss, Loss_Eval
 from model.extracting_images import Extract_Images
 from model.optim import FlatAdam
-from model.scene import ResidentScene
+from model.scene import ResidentScene, BatchUploader
 from model import parallel

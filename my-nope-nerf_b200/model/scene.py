@@ -63,3 +63,59 @@ class ResidentScene(object):
                 if k in self.data:
                     b[rk] = self.data[k][ref_idx:ref_idx + 1]
         return b
+
+
+class BatchUploader(object):
+    """Host -> device pipeline for batches that do not live on the device: `depth` pre-allocated sets of staging tensors, filled
+    by asynchronous copies from the (pinned) host batch on a copy stream while the previous step computes.  No per-step device
+    allocation (a growing caching-allocator pool costs a synchronising cudaMalloc per new block: measured 5 ms per step over the
+    first ~20 steps when every step staged its batch in fresh tensors).
+
+        up = BatchUploader(trainer, first_host_batch)
+        up.submit(host_batches[0])
+        for it in range(n):
+            batch = up.next()                       # compute stream now waits for the upload of step `it`
+            if it + 1 < n: up.submit(host_batches[it + 1])
+            trainer.train_step_graphed(batch, ...)
+            up.done()                               # the slot may be overwritten once this step has consumed it
+    """
+
+    def __init__(self, trainer, example, depth=2):
+        self.keys = [k for k, v in example.items() if k in trainer.STEP_KEYS and torch.is_tensor(v) and k not in ('img.idx', 'img.ref_idxs')]
+        self.device = trainer.device
+        self.stream = torch.cuda.Stream(device=self.device)
+        self.slots = [{k: torch.empty_like(example[k], device=self.device) for k in self.keys} for _ in range(depth)]
+        self.uploaded = [None] * depth      # event: H2D copies of the slot are complete
+        self.consumed = [None] * depth      # event: the step that read the slot has been issued and (when reached) finished
+        self.meta = [None] * depth
+        self.head = self.tail = 0
+
+    def nbytes(self):
+        return sum(v.numel() * v.element_size() for v in self.slots[0].values())
+
+    def submit(self, host_batch):
+        s = self.head % len(self.slots)
+        self.head += 1
+        with torch.cuda.stream(self.stream):
+            if self.consumed[s] is not None:
+                self.stream.wait_event(self.consumed[s])
+            for k in self.keys:
+                self.slots[s][k].copy_(host_batch[k], non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self.stream)
+        self.uploaded[s] = ev
+        self.meta[s] = {k: v for k, v in host_batch.items() if k in ('img.idx', 'img.ref_idxs')}
+
+    def next(self):
+        s = self.tail % len(self.slots)
+        torch.cuda.current_stream().wait_event(self.uploaded[s])
+        b = dict(self.slots[s])
+        b.update(self.meta[s])
+        return b
+
+    def done(self):
+        s = self.tail % len(self.slots)
+        self.tail += 1
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream())
+        self.consumed[s] = ev

@@ -215,3 +215,42 @@ def test_resident_scene_batches_match_host_batches(golden):
         out.append(ls)
     for a, b in zip(*out):
         assert abs(a - b) <= 1e-5 + 2e-4 * abs(a), out
+
+
+def test_batch_uploader_pipeline_matches_direct_upload(golden):
+    """BatchUploader (pre-allocated staging slots filled on a copy stream while the previous step computes) must hand the step
+    exactly the host batch: same losses as passing the host batch itself, over more steps than there are slots."""
+    import model as mdl
+    g = golden("render_step")
+    cfg = syn.default_cfg()
+    scene = syn.make_scene("tiny")
+    R = syn.SHAPES["tiny"][3]
+    n = scene["n"]
+    sched = cfg["training"]["scheduling_start"]
+    frames = [0, 1, n - 1, 2, n - 2, 0]
+    host = [{k: (v.pin_memory() if torch.is_tensor(v) else v) for k, v in syn.make_batch(scene, f, f + 1 if f < n - 1 else f - 1).items()}
+            for f in frames]
+    out = []
+    for piped in (False, True):
+        tr, nerf, pose, dist = _trainer(cfg, scene, g["step_setup"], "l1", R)
+        tr.fixed_ray_idx, tr.fixed_noise = g["render"]["ray_idx"].to(dev()), g["render"]["noise"].to(dev())
+        ls = []
+        if piped:
+            up = mdl.BatchUploader(tr, host[0])
+            assert "img.gt_depths" not in up.keys and up.nbytes() > 0
+            up.submit(host[0])
+        for it in range(len(frames)):
+            if piped:
+                b = up.next()
+                if it + 1 < len(frames):
+                    up.submit(host[it + 1])
+            else:
+                b = host[it]
+            ld = tr.train_step_graphed(b, it=it, epoch=0, scheduling_start=sched)
+            if piped:
+                up.done()
+            ls.append(ld["loss"].detach().clone())
+        torch.cuda.synchronize()
+        out.append([float(x) for x in ls])
+    for a, b in zip(*out):
+        assert abs(a - b) <= 1e-6 + 1e-5 * abs(a), out
