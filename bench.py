@@ -270,8 +270,8 @@ def run_b200(args):
         "roofline": {"bound": "tensor", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
                      "frac": achieved_tf / peak_tf if peak_tf else None,
                      # dram__bytes_read + dram__bytes_write of the three kernels behind these two entry points, ncu --set full,
-                     # 4,096 rays (profiles/r1_ncu_full_tc_kernels.txt): fwd 2.77 + dgrad 2.68 + wgrad 5.67 GB
-                     "traffic": 11.12e9 if args.precision == "bf16" else None, "traffic_unit": "B per step (ncu)",
+                     # 4,096 rays (profiles/r1b_ncu_full_tc_kernels.txt): fwd 2.772 + dgrad 2.678 + wgrad 5.377 GB
+                     "traffic": 10.83e9 if args.precision == "bf16" else None, "traffic_unit": "B per step (ncu)",
                      "kernel": "nnb_render_fwd + nnb_render_bwd (sampling+encoding+MLP+compositing, fwd and bwd)",
                      "kernel_ms_per_step": mlp_ms, "peak_source": "%s bf16 sustained" % pk_kind,
                      "algorithmic_flop_per_step": FLOP_PER_RAY_TRAIN * RAYS_PER_GPU,

@@ -481,7 +481,7 @@ __device__ __forceinline__ uint32_t gt0_mask2(uint32_t h) {
 }
 // 32 fp32 accumulator columns -> 4 chunks of 8 bf16 (optionally relu) into the operand image (+ global copy).
 // Returns the ReLU bitmask of the block: pair p (columns 2p, 2p+1) -> bit p (even column) and bit 16+p (odd column).
-template <bool RELU, bool SAVE>
+template <bool RELU, bool SAVE, bool GLOBAL = SAVE>
 __device__ __forceinline__ uint32_t store32(uint32_t saddr, uint8_t *gaddr, const uint32_t (&v)[32]) {
   uint32_t bits = 0;
 #pragma unroll
@@ -493,7 +493,7 @@ __device__ __forceinline__ uint32_t store32(uint32_t saddr, uint8_t *gaddr, cons
       w[k] = RELU ? pack_bf16_relu(a, b) : pack_bf16(a, b);
       if (RELU && SAVE) bits |= gt0_mask2(w[k]) & ((1u << (4 * g + k)) | (1u << (16 + 4 * g + k)));
     }
-    put_chunk<SAVE>(saddr + g * 128, gaddr + g * 128, w[0], w[1], w[2], w[3]);
+    put_chunk<GLOBAL>(saddr + g * 128, gaddr + g * 128, w[0], w[1], w[2], w[3]);
   }
   return bits;
 }
@@ -506,8 +506,19 @@ __device__ __forceinline__ void act_arrive(uint32_t bar, uint32_t rank) {
   else mbar_arrive_remote_relaxed(bar, 0);
 }
 
+// FWD_BULK_SAVE: the 64 KB activation images H0..H7 and `feature` leave shared memory as ONE cp.async.bulk shared -> global each
+// (issued by a lane of warp 10 once the tile's 128 row owners have published the image, tests/cuda/bulk_store_bw.cu: 43 GB/s per
+// SM) instead of 32 st.global.v4 per row owner; the next epilogue of the tile waits until the copy has read the buffer.
+// Measured on B200 (4,096 rays): parity green, forward+save 0.665 -> 0.778 ms -- while the tensor core streams its operands
+// out of the same shared memory the bulk copy drains too slowly and the row owners end up waiting for the buffer.  Off.
+#ifndef FWD_BULK_SAVE
+#define FWD_BULK_SAVE 0
+#endif
+constexpr int FWD_THREADS_SAVE = FWD_BULK_SAVE ? 352 : 320;
+
 template <bool SAVE>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1) tc_fwd_kernel(const FwdArgs A) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(352, 1) tc_fwd_kernel(const FwdArgs A) {
+  constexpr bool BULK = SAVE && FWD_BULK_SAVE;
   extern __shared__ __align__(1024) uint8_t smem[];
   const uint32_t sbase = smem_u32(smem);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -515,7 +526,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1) tc_fwd_kerne
   float *sm_scan = reinterpret_cast<float *>(smem + SM_SCAN);
   // full / empty: TC2_RING each; acc / act: one per tile (+0 / +8)
   const uint32_t bar_full = sbase + SM_BARS, bar_empty = bar_full + TC2_RING * 8, bar_acc = bar_empty + TC2_RING * 8,
-                 bar_act = bar_acc + 16;
+                 bar_act = bar_acc + 16, bar_actl = bar_act + 16, bar_sdone = bar_actl + 16;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + SM_BARS + 24 * 8);
   const uint32_t rank = cluster_ctarank();
 
@@ -526,6 +537,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1) tc_fwd_kerne
     mbar_init(bar_acc + 8, 1);
     mbar_init(bar_act, 256);       // used in the leader CTA: 128 local + 128 remote arrivals per tile
     mbar_init(bar_act + 8, 256);
+    mbar_init(bar_actl, 128);      // BULK: this CTA's 128 row owners of a tile have published an image to be saved
+    mbar_init(bar_actl + 8, 128);
+    mbar_init(bar_sdone, 1);       // BULK: the bulk store has read the image, the buffer may be overwritten
+    mbar_init(bar_sdone + 8, 1);
     mbar_fence_init();
   }
   if (threadIdx.x == 0) { sm_small[0] = A.b_den[0]; sm_small[1] = A.b_rgb[0]; sm_small[2] = A.b_rgb[1]; sm_small[3] = A.b_rgb[2]; }
@@ -552,9 +567,33 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1) tc_fwd_kerne
       full_forwarder_pair(c_fwd_groups, A.n_stages, n_iters, bar_full, lane);
     }
     __syncwarp();
+  } else if (warp == 10) {
+    // ------------------------------------------------ BULK: image saver, lane t serves tile t
+    if (BULK && lane < 2) {
+      const int t = lane;
+      uint32_t par = 0;
+      for (int it = 0; it < n_iters; ++it) {
+        const int ray = 2 * (blockIdx.x + it * gridDim.x) + t;
+        const bool valid = ray < A.n_rays;
+        uint8_t *gtile = A.ws_fwd + (size_t)(valid ? ray : 0) * FWD_TILE_BYTES;
+        for (int L = 0; L < 9; ++L) {
+          mbar_wait(bar_actl + 8 * t, par);
+          par ^= 1;
+          if (valid) {
+            bulk_s2g(gtile + (uint32_t)L * 65536u, sbase + SM_ACT + t * 65536u, 65536u);
+            bulk_commit();
+            bulk_wait_read0();
+          }
+          mbar_arrive(bar_sdone + 8 * t);
+        }
+      }
+      bulk_wait0();
+    }
+    __syncwarp();
   } else {
     // ------------------------------------------------ row owners: prologue, epilogues, heads, compositing
     const int t = warp >> 2, q = warp & 3, row = q * 32 + lane;
+    uint32_t n_img = 0;   // BULK: images of this tile handed to the saver so far
     const uint32_t act_row = sbase + SM_ACT + t * 65536u + (row >> 3) * GS_ACT + (row & 7) * 16;
     const uint32_t enc_row = sbase + SM_ENC + t * 16384u + (row >> 3) * GS_ENC + (row & 7) * 16;
     const uint32_t aux_row = sbase + SM_AUX + t * 512u + (row & 7) * 16;  // rows 0..7 write it (same ray => same values)
@@ -596,6 +635,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1) tc_fwd_kerne
         if (L < 9) {
           float ds0 = 0.f, ds1 = 0.f, ds2 = 0.f, ds3 = 0.f;
           uint32_t mw[8];
+          if (BULK && n_img > 0) mbar_wait(bar_sdone + 8 * t, (n_img - 1) & 1);   // the previous image of this buffer has been read
 #pragma unroll
           for (int c0 = 0; c0 < 256; c0 += 64) {
             uint32_t v0[32], v1[32];
@@ -624,10 +664,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1) tc_fwd_kerne
             const uint32_t dst = act_row + (c0 >> 3) * 128;
             uint8_t *gdst = sv ? gtile + (uint32_t)L * 65536u + (row >> 3) * GS_ACT + (row & 7) * 16 + (c0 >> 3) * 128 : nullptr;
             if (L != 8) {
-              if (sv) { mw[c0 >> 5] = store32<true, true>(dst, gdst, v0); mw[(c0 >> 5) + 1] = store32<true, true>(dst + 512, gdst + 512, v1); }
+              if (sv) { mw[c0 >> 5] = store32<true, true, !BULK>(dst, gdst, v0); mw[(c0 >> 5) + 1] = store32<true, true, !BULK>(dst + 512, gdst + 512, v1); }
               else { store32<true, false>(dst, nullptr, v0); store32<true, false>(dst + 512, nullptr, v1); }
             } else {
-              if (sv) { store32<false, true>(dst, gdst, v0); store32<false, true>(dst + 512, gdst + 512, v1); }
+              if (sv) { store32<false, true, !BULK>(dst, gdst, v0); store32<false, true, !BULK>(dst + 512, gdst + 512, v1); }
               else { store32<false, false>(dst, nullptr, v0); store32<false, false>(dst + 512, nullptr, v1); }
             }
           }
@@ -654,6 +694,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1) tc_fwd_kerne
           fence_async_smem();
           tc_fence_before();
           act_arrive(bar_act_t, rank);
+          if (BULK) { mbar_arrive(bar_actl + 8 * t); ++n_img; }
           if (A.trace && blockIdx.x == 0 && pair == 0 && threadIdx.x == 0) A.trace[L * 4 + 1] = clock64();
         } else {
           // rgb head: relu(rgb_layers.0) (128 wide, TMEM cols 0..127) . fc_rgb^T + b -> sigmoid
@@ -1515,7 +1556,7 @@ int nnb_tc_render_fwd(const nnb_render_cfg *cfg, const float *const *params, con
   int grid = n_pairs < nnb_sm_count() ? n_pairs : nnb_sm_count();
   grid = (grid + 1) & ~1;                       // 2-CTA clusters
   if (grid > (nnb_sm_count() & ~1)) grid = nnb_sm_count() & ~1;
-  if (save) tc_fwd_kernel<true><<<grid, 320, SM_TOTAL, s>>>(A);
+  if (save) tc_fwd_kernel<true><<<grid, FWD_THREADS_SAVE, SM_TOTAL, s>>>(A);
   else tc_fwd_kernel<false><<<grid, 320, SM_TOTAL, s>>>(A);
   NNB_CHECK_LAUNCH();
   return 0;
