@@ -223,11 +223,16 @@ __global__ void chamfer_tc_prep16_kernel(const float *__restrict__ src, int n_sr
 }
 
 // bounding box of every 256-destination stage, raw coordinates: box[st] = {min xyz, max xyz} (8 floats, 2 unused)
-__global__ void chamfer_tc_boxes_kernel(const float *__restrict__ dst, int n_dst, int n_stages, float *__restrict__ box) {
+// The last block to finish also decides whether stage lists can pay: stats[3] = 1 iff the stage boxes are selective, i.e. their
+// mean volume is below 5 % of the cloud's bounding box (axes along which the whole cloud is flat do not count).  Raster-order
+// depth clouds give ~1e-3; clouds in random order give ~1 and run the two plain sweeps (stats[5] = completion counter).
+__global__ void __launch_bounds__(128) chamfer_tc_boxes_kernel(const float *__restrict__ dst, int n_dst, int n_stages, float *__restrict__ box,
+                                                               unsigned int *__restrict__ stats) {
+  __shared__ float red[6][4];
+  __shared__ bool last;
   const int st = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-  if (st >= n_stages) return;
   float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
-  for (int j = st * 256 + lane; j < min(n_dst, st * 256 + 256); j += 32) {
+  for (int j = st * 256 + lane; st < n_stages && j < min(n_dst, st * 256 + 256); j += 32) {
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
       const float v = dst[3 * (size_t)j + c];
@@ -243,10 +248,54 @@ __global__ void chamfer_tc_boxes_kernel(const float *__restrict__ dst, int n_dst
       hi[c] = fmaxf(hi[c], __shfl_xor_sync(0xffffffffu, hi[c], o));
     }
   }
-  if (lane == 0) {
+  if (lane == 0 && st < n_stages) {
     float *b = box + 8 * (size_t)st;
     b[0] = lo[0]; b[1] = lo[1]; b[2] = lo[2]; b[3] = hi[0]; b[4] = hi[1]; b[5] = hi[2];
   }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) last = atomicAdd(stats + 5, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  // global bounding box, then the mean volume fraction of the stage boxes
+  const int t = threadIdx.x, w = t >> 5;
+  float g[6] = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY};
+  for (int k = t; k < n_stages; k += blockDim.x) {
+    const volatile float *b = box + 8 * (size_t)k;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) { g[c] = fminf(g[c], b[c]); g[3 + c] = fmaxf(g[3 + c], b[3 + c]); }
+  }
+#pragma unroll
+  for (int c = 0; c < 6; ++c) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float v = __shfl_xor_sync(0xffffffffu, g[c], o);
+      g[c] = c < 3 ? fminf(g[c], v) : fmaxf(g[c], v);
+    }
+    if (lane == 0) red[c][w] = g[c];
+  }
+  __syncthreads();
+  float G[3];
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+    G[c] = fmaxf(fmaxf(red[3 + c][0], red[3 + c][1]), fmaxf(red[3 + c][2], red[3 + c][3])) -
+           fminf(fminf(red[c][0], red[c][1]), fminf(red[c][2], red[c][3]));
+  float acc = 0.f;
+  for (int k = t; k < n_stages; k += blockDim.x) {
+    const volatile float *b = box + 8 * (size_t)k;
+    float f = 1.f;
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+      if (G[c] > 0.f) f *= fminf(fmaxf(b[3 + c] - b[c], 1e-3f * G[c]) / G[c], 1.f);
+    acc += f;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if (lane == 0) red[0][w] = acc;
+  __syncthreads();
+  if (t == 0) stats[3] = ((red[0][0] + red[0][1] + red[0][2] + red[0][3]) / (float)n_stages < 0.05f) ? 1u : 0u;
 }
 
 // One block per source block (128 sources, one per thread).  Stage st is listed iff some source s of the block has
@@ -259,6 +308,7 @@ __global__ void __launch_bounds__(128) chamfer_tc_filter_kernel(const float *__r
                                                                 int *__restrict__ list, int *__restrict__ list_cnt) {
   __shared__ float4 sp[128];
   __shared__ int warp_cnt[4], base_s;
+  if (stats[3] == 0) return;   // boxes not selective: the sweeps ignore the lists
   const int sb = blockIdx.x, t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int s = sb * 128 + t;
   const float scale = extent_scale(stats[2]);
@@ -311,6 +361,10 @@ struct CtArgs {
   int n_dst;
   // optional stage lists (chamfer_tc_filter_kernel): source block sb sweeps list[sb * n_stages + 0 .. list_cnt[sb]) only
   const int *list, *list_cnt;
+  // stats[3] (chamfer_tc_boxes_kernel): lists are honoured only when it is 1; gate_skip: this launch (the sub-sampled screen)
+  // is needed only then and returns at once otherwise
+  const unsigned int *gate;
+  int gate_skip;
 };
 
 // EXACT = false: bound[s] = min_j a(s, j) + |s - c|^2.
@@ -322,6 +376,9 @@ struct CtArgs {
 template <bool EXACT, bool F16>
 __global__ void __launch_bounds__(320, 1) chamfer_tc_kernel(const CtArgs A) {
   constexpr uint32_t STAGE = F16 ? 8192u : CT_STAGE, ABYTES = F16 ? 4096u : 8192u, GS = F16 ? 256u : 512u;
+  const bool gate_on = A.gate && *A.gate != 0;
+  if (A.gate_skip && !gate_on) return;
+  const int *const list = gate_on ? A.list : nullptr;
   extern __shared__ __align__(1024) uint8_t smem[];
   const uint32_t sbase = smem_u32(smem);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -344,12 +401,12 @@ __global__ void __launch_bounds__(320, 1) chamfer_tc_kernel(const CtArgs A) {
   auto item_range = [&](int item, int &sb, int &k0, int &k1) {
     sb = item / A.n_splits;
     const int sp = item % A.n_splits;
-    const int cnt = A.list ? A.list_cnt[sb] : A.n_stages;
+    const int cnt = list ? A.list_cnt[sb] : A.n_stages;
     k0 = sp * A.stages_per_split;
     k1 = min(cnt, k0 + A.stages_per_split);
     return k0 < k1;
   };
-  auto stage_at = [&](int sb, int k) { return A.list ? A.list[(size_t)sb * A.n_stages + k] : k; };
+  auto stage_at = [&](int sb, int k) { return list ? list[(size_t)sb * A.n_stages + k] : k; };
 
   if (warp == 8) {
     if (elect_one()) {
@@ -534,7 +591,7 @@ int nnb_chamfer_tc_bound(const float *src, int n_src, const float *dst, int n_ds
   uint8_t *a_img = static_cast<uint8_t *>(workspace);
   uint8_t *b_img = a_img + (size_t)n_sblocks * 8192;
   float *norm2 = reinterpret_cast<float *>(b_img + (size_t)n_stages * CT_STAGE);
-  NNB_CUDA(cudaMemsetAsync(stats, 0, 3 * sizeof(unsigned int), s));
+  NNB_CUDA(cudaMemsetAsync(stats, 0, 6 * sizeof(unsigned int), s));
   const int ns_pad = n_sblocks * 128, nd_pad = n_stages * 256;
   // stage lists pay off when there are enough stages to skip; small problems run the two plain sweeps
   const bool lists = use_f16 && n_stages >= 16;
@@ -553,7 +610,7 @@ int nnb_chamfer_tc_bound(const float *src, int n_src, const float *dst, int n_ds
                                                                                      b_img, sub_img, norm2, stats, bound, best_init);
     if (lists) {
       NNB_CHECK_LAUNCH();
-      chamfer_tc_boxes_kernel<<<nnb_cdiv(n_stages, 4), 128, 0, s>>>(dst, n_dst, n_stages, box);
+      chamfer_tc_boxes_kernel<<<nnb_cdiv(n_stages, 4), 128, 0, s>>>(dst, n_dst, n_stages, box, stats);
     }
   } else {
     chamfer_tc_prep_kernel<<<nnb_cdiv(ns_pad + nd_pad, 128), 128, 0, s>>>(src, n_src, ns_pad, dst, n_dst, nd_pad, a_img, b_img, norm2, stats,
@@ -573,18 +630,18 @@ int nnb_chamfer_tc_bound(const float *src, int n_src, const float *dst, int n_ds
     const int n_items = n_sblocks * P.n_splits;
     return n_items < nnb_sm_count() ? n_items : nnb_sm_count();
   };
-  CtArgs A{a_img, b_img, norm2, bound, n_src, n_sblocks, n_stages, 1, n_stages, src, dst, stats, best, n_dst, nullptr, nullptr};
+  CtArgs A{a_img, b_img, norm2, bound, n_src, n_sblocks, n_stages, 1, n_stages, src, dst, stats, best, n_dst, nullptr, nullptr, nullptr, 0};
   if (lists) {
     // (1) loose bound from every CT_SUB-th destination
     CtArgs S = A;
-    S.b_img = sub_img; S.n_stages = n_sub_stages;
+    S.b_img = sub_img; S.n_stages = n_sub_stages; S.gate = stats + 3; S.gate_skip = 1;
     const int gs = plan(S, n_sub_stages, 2, 4);
     chamfer_tc_kernel<false, true><<<gs, 320, CS_TOTAL, s>>>(S);
     NNB_CHECK_LAUNCH();
     // (2) stage lists
     chamfer_tc_filter_kernel<<<n_sblocks, 128, 0, s>>>(src, n_src, n_stages, box, bound, norm2, stats, list, list_cnt);
     NNB_CHECK_LAUNCH();
-    A.list = list; A.list_cnt = list_cnt;
+    A.list = list; A.list_cnt = list_cnt; A.gate = stats + 3;
   }
   const int grid = plan(A, n_stages, 4, CT_RING);
   if (use_f16) chamfer_tc_kernel<false, true><<<grid, 320, CS_TOTAL, s>>>(A);
