@@ -237,8 +237,6 @@ class Trainer(object):
         rgb_loss_type = 'l1' if epoch < self.annealing_epochs + scheduling_start else 'l2'
         render_model = (weights['rgb_weight'] != 0.0) or (weights['depth_weight'] != 0.0)
         use_ref_imgs = (weights['pc_weight'] != 0.0) or (weights['rgb_s_weight'] != 0.0) or (weights['t_cycle_weight'] != 0.0)
-        if self.shift_first:
-            raise NotImplementedError("shift_first=True is not used by any shipped config ('next' row)")
 
         n_points = self.n_training_points
         nl = self.nearest_limit
@@ -259,9 +257,17 @@ class Trainer(object):
         c2w = self.pose_param_net(img_idx_i, idx_dev)              # exp-map kernel
         world_mat = _ops.Mat4Inverse.apply(c2w).unsqueeze(0)       # model/training.py:257
 
-        ss_in = None
+        def affine(ss):
+            """The kernels apply depth * a + b.  shift_first (model/training.py:261-264,312-315) means (depth + shift) * scale
+            = depth * scale + shift * scale: same kernels with b = shift * scale (gradients through the two torch ops)."""
+            if ss is None or not self.shift_first:
+                return ss
+            return torch.stack([ss[0], ss[0] * ss[1]])
+
+        ss_raw = ss_in = None
         if self.distortion_net is not None:
-            ss_in = self.distortion_net.scale_shift(img_idx_i, idx_dev)   # [scale, shift] on device, no host sync
+            ss_raw = self.distortion_net.scale_shift(img_idx_i, idx_dev)   # [scale, shift] on device, no host sync
+            ss_in = affine(ss_raw)
         if self.optimizer_focal:
             fxfy = self.focal_net(0)
             pad = torch.zeros(4, device=device)
@@ -283,10 +289,11 @@ class Trainer(object):
             with (torch.cuda.stream(geom) if geom is not None else contextlib.nullcontext()):
                 ref_idx_i = int(ref_idx)
                 c2w_ref = self.pose_param_net(ref_idx_i, ref_idx_dev)
-                ss_ref = self.distortion_net.scale_shift(ref_idx_i, ref_idx_dev) if self.distortion_net is not None else None
+                ss_ref_raw = self.distortion_net.scale_shift(ref_idx_i, ref_idx_dev) if self.distortion_net is not None else None
                 if self.detach_ref_img:
                     c2w_ref = c2w_ref.detach()
-                    ss_ref = ss_ref.detach() if ss_ref is not None else None
+                    ss_ref_raw = ss_ref_raw.detach() if ss_ref_raw is not None else None
+                ss_ref = affine(ss_ref_raw)
                 if img_idx_i < (num_cams - 1):
                     d1_raw, d2_raw, ss1, ss2 = depth_raw, depth_ref_raw, ss_in, ss_ref
                     img1, img2 = img, ref_img
@@ -380,9 +387,9 @@ class Trainer(object):
         if self.optimizer_focal:
             loss_dict['focalx'] = fxfy[0] / camera_mat_gt[0, 0, 0]
             loss_dict['focaly'] = fxfy[1] / camera_mat_gt[0, 1, 1]
-        if ss_in is not None:
-            loss_dict['scale'] = ss_in[0:1]
-            loss_dict['shift'] = ss_in[1:2]
+        if ss_raw is not None:
+            loss_dict['scale'] = ss_raw[0:1]
+            loss_dict['shift'] = ss_raw[1:2]
         return loss_dict
 
     def render_visdata(self, data, resolution, it, out_render_path):

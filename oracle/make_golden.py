@@ -186,11 +186,14 @@ def render_and_step_vectors(ref, cfg):
         "l1_last": dict(idx=n - 1, ref=n - 2, depth_loss_type="l1", epoch=0),
         "l2_rgb_only": dict(idx=0, ref=1, depth_loss_type="l1", epoch=10 ** 6),
     }
+    if os.environ.get("NNB_GOLDEN_EXTRA_CASES"):   # appended later without regenerating the cases above
+        cases = {"shift_first": dict(idx=2, ref=3, depth_loss_type="l1", epoch=0, shift_first=True)}
     out["step"] = {}
     for name, c in cases.items():
         tcfg = dict(cfg["training"])
         tcfg["depth_loss_type"] = c["depth_loss_type"]
         tcfg["n_training_points"] = R
+        tcfg["shift_first"] = c.get("shift_first", False)
         nerf, renderer, net = build_ref_model(ref, cfg, sd)
         pose_net = ref.model.LearnPose(n, True, True, cfg, init_c2w=scene["poses_gt"].clone())
         dist_net = ref.model.Learn_Distortion(n, True, True, cfg)
@@ -318,6 +321,17 @@ def geometry_vectors(ref, cfg):
 
 def main():
     os.makedirs(OUT, exist_ok=True)
+    if "--extra-step-cases" in sys.argv:
+        # adds the later step cases to render_step.pt, leaving every existing entry byte-identical
+        os.environ["NNB_GOLDEN_EXTRA_CASES"] = "1"
+        ref = ref_harness.load_reference()
+        torch.set_num_threads(max(1, os.cpu_count() or 1))
+        extra = render_and_step_vectors(ref, syn.default_cfg())["step"]
+        path = os.path.join(OUT, "render_step.pt")
+        g = torch.load(path)
+        g["step"].update(extra)
+        torch.save(g, path)
+        return
     if "--geometry-only" in sys.argv:
         ref = ref_harness.load_reference()
         torch.set_num_threads(max(1, os.cpu_count() or 1))

@@ -404,7 +404,7 @@ def backproject_cloud(depth_img, camera_mat, res, nl):
 
 def train_loss(batch, P, pose, dist, cfg, ray_idx, noise, epoch=0, scheduling_start=None):
     """Restatement of Trainer.compute_loss, model/training.py:214-416, for the default branches
-    (learned pose + distortion, no learned focal, shift_first False, detach_ref_img True).
+    (learned pose + distortion, no learned focal, detach_ref_img True; shift_first either way).
     `pose` = dict(r, t, init_c2w|None); `dist` = dict(global_scales, global_shifts).
     `ray_idx` / `noise` replace the reference's randperm / rand draws."""
     ct, cr = cfg["training"], cfg["rendering"]
@@ -428,7 +428,8 @@ def train_loss(batch, P, pose, dist, cfg, ray_idx, noise, epoch=0, scheduling_st
     c2w = c2w_of(idx)
     world_mat = torch.inverse(c2w).unsqueeze(0)
     scale_in, shift_in = distortion(dist["global_scales"], dist["global_shifts"], idx, cfg["distortion"]["fix_scaleN"])
-    depth = depth * scale_in + shift_in  # model/training.py:264
+    shift_first = cfg["training"].get("shift_first", False)
+    depth = (depth + shift_in) * scale_in if shift_first else depth * scale_in + shift_in  # model/training.py:261-264
 
     rgb_gt = img.reshape(1, 3, h * w).permute(0, 2, 1)[:, ray_idx]
     _, p_full = pixel_grid(h, w, dtype=img.dtype)
@@ -446,7 +447,7 @@ def train_loss(batch, P, pose, dist, cfg, ray_idx, noise, epoch=0, scheduling_st
         c2w_ref = c2w_of(ridx)
         scale_ref, shift_ref = distortion(dist["global_scales"], dist["global_shifts"], ridx,
                                           cfg["distortion"]["fix_scaleN"])
-        dref = scale_ref * dref + shift_ref
+        dref = scale_ref * (dref + shift_ref) if shift_first else scale_ref * dref + shift_ref  # model/training.py:312-315
         if ct["detach_ref_img"]:
             c2w_ref, scale_ref, shift_ref, dref = c2w_ref.detach(), scale_ref.detach(), shift_ref.detach(), dref.detach()
         ref_Rt = torch.inverse(c2w_ref).unsqueeze(0)

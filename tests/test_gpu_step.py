@@ -34,6 +34,7 @@ def test_compute_loss_and_grads_vs_reference(golden):
     for name, rec in g["step"].items():
         c = rec["case"]
         tr, nerf, pose, dist = _trainer(cfg, scene, g["step_setup"], c["depth_loss_type"], R)
+        tr.shift_first = c.get("shift_first", False)      # model/training.py:261-264,312-315
         tr.fixed_ray_idx = g["render"]["ray_idx"]
         tr.fixed_noise = g["render"]["noise"]
         batch = syn.make_batch(scene, c["idx"], c["ref"])

@@ -143,6 +143,7 @@ def test_train_step_loss_and_grads(golden):
     for name, rec in g["step"].items():
         c = rec["case"]
         cfg["training"]["depth_loss_type"] = c["depth_loss_type"]
+        cfg["training"]["shift_first"] = c.get("shift_first", False)
         P = _params(True)
         pose = {"r": g["step_setup"]["r"].clone().requires_grad_(True), "t": g["step_setup"]["t"].clone().requires_grad_(True),
                 "init_c2w": scene["poses_gt"]}

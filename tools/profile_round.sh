@@ -15,7 +15,8 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 900 --csv --log-fil
 python tools/time_train_mlp.py 4096 2 > $OUT/${TAG}_time_train_mlp.json 2>&1 || { echo "time_train_mlp failed"; exit 1; }
 ncu --set full --clock-control none --import-source on -k regex:'tc_(fwd|bwd|wgrad)_kernel' -s 6 -c 3 -f -o $OUT/${TAG}_mlp \
     python tools/time_train_mlp.py 4096 2 > $OUT/${TAG}_ncu_mlp.log 2>&1 || echo "ncu mlp failed"
-python tools/time_chamfer.py 28830 > $OUT/${TAG}_time_chamfer.json 2>&1 || echo "time_chamfer failed"
-ncu --set full --clock-control none --import-source on -k regex:'chamfer_tc_kernel' -s 2 -c 2 -f -o $OUT/${TAG}_chamfer \
-    python tools/time_chamfer.py 28830 > $OUT/${TAG}_ncu_chamfer.log 2>&1 || echo "ncu chamfer failed"
+python tools/time_chamfer.py 28830 --raster > $OUT/${TAG}_time_chamfer.json 2>&1 || echo "time_chamfer failed"
+# raster-order clouds: three sweeps per call (screen of every 8th destination, screen and exact sweep over the stage lists)
+ncu --set full --clock-control none --import-source on -k regex:'chamfer_tc_kernel' -s 3 -c 3 -f -o $OUT/${TAG}_chamfer \
+    python tools/time_chamfer.py 28830 --raster > $OUT/${TAG}_ncu_chamfer.log 2>&1 || echo "ncu chamfer failed"
 ls -la $OUT
