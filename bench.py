@@ -256,7 +256,7 @@ def run_b200(args):
         "metric": METRIC, "value": rays_per_s, "unit": "rays/s", "n_gpus": world, "steps": args.steps, "warmup": len(warm),
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32" if args.precision == "fp32" else "bf16 operands, f32 accumulate", "data": "synthetic",
-        "config": {"workload": "cfg2: Virtual-KITTI-shaped synthetic scene, %d frames 375x1242, %d rays/step/GPU x 128 samples, "
+        "config": {"workload": "cfg2/cfg3: Virtual-KITTI-shaped synthetic scene, %d frames 375x1242, %d rays/step/GPU x 128 samples, "
                                "losses rgb+depth(l1, learned scale/shift)+Chamfer(28,830 pts)+reprojection, LearnPose, 3x Adam"
                                % (n, RAYS_PER_GPU),
                    "global_rays": rays_global, "resident_scene_bytes": resident.nbytes(), "parallelism": "dp%d" % world, "precision": args.precision,
@@ -458,9 +458,12 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--precision", default=os.environ.get("NNB_PRECISION", "bf16"), choices=["fp32", "bf16"])
     ap.add_argument("--frames", type=int, default=20)
+    ap.add_argument("--rays-per-gpu", type=int, default=RAYS_PER_GPU,
+                    help="rays per step and GPU (default 4096 = cfg2; 8192 at --gpus 8 is cfg3's 65,536-ray global batch)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel of the step eagerly instead of replaying a CUDA graph")
     args = ap.parse_args()
+    globals()["RAYS_PER_GPU"] = args.rays_per_gpu
     if args.impl == "reference":
         run_reference(args)
     else:
