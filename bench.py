@@ -280,6 +280,8 @@ def run_b200(args):
     }
     if world == 1:
         out["extras"] = extras(dev, cfg, scene, tr, args.precision)
+    else:
+        out["extras"] = render_extras_sharded(dev, scene, tr, dp)
     if dp.rank == 0 and not args.no_cpu_baseline and world == 1:
         out["cpu_baseline"] = cpu_baseline(max_seconds=25.0)
     if dp.rank == 0:
@@ -287,6 +289,35 @@ def run_b200(args):
     if world > 1:
         torch.distributed.barrier()
         torch.distributed.destroy_process_group()
+
+
+def render_extras_sharded(dev, scene, tr, dp):
+    """cfg4 at N GPUs: one 375 x 1242 frame, pixel rows sharded across the ranks (Extract_Images.render_frame), the full frame
+    gathered on every rank; device time, max over ranks, median of 5."""
+    import model as mdl
+    from model import _ops
+    h, w = scene["h"], scene["w"]
+    ex = mdl.Extract_Images(tr.model.renderer, {"extract_images": {"resolution": [h, w]}}, device=dev, render_type=tr.rendering_technique, dp=dp)
+    cam, scl = scene["camera_mat"].to(dev).reshape(1, 4, 4), torch.eye(4, device=dev).reshape(1, 4, 4)
+    with torch.no_grad():
+        wm = _ops.Mat4Inverse.apply(tr.pose_param_net(0)).unsqueeze(0)
+    tr.model.eval()
+    ts = []
+    for rep in range(7):
+        torch.cuda.synchronize()
+        torch.distributed.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        ex.render_frame(cam, wm, scl, h, w, gather=True)
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+        if rep >= 2:
+            ts.append(float(t))
+    tr.model.train()
+    ms = sorted(ts)[len(ts) // 2]
+    return {"cfg4_render_ms_per_frame": ms, "cfg4_render_tflops": 151_912_448 * h * w / ms / 1e9, "cfg4_sharding": "pixel rows over %d ranks + all_gather" % dp.world_size}
 
 
 def extras(dev, cfg, scene, tr, precision):
