@@ -84,8 +84,6 @@ class Renderer(nn.Module):
         ndc = cfg['sample_option'] == 'ndc'
         if cfg['sample_option'] not in ('uniform', 'ndc'):
             raise ValueError("unknown sample_option %r" % (cfg['sample_option'],))
-        if cfg['normal_loss'] and not eval_:
-            raise NotImplementedError("normal_loss needs the second-order path ('next' row, SURVEY.md 8f rank 3)")
         batch_size, n_points, _ = pixels.shape
         if batch_size != 1:
             raise ValueError("batch size 1 only (as the reference: model/rendering.py:80 takes element 0)")
@@ -94,6 +92,7 @@ class Renderer(nn.Module):
                                                           cfg['normalise_ray'])
         ray_o = view = None
         dr = None
+        dirs_world = dirs
         if ndc:
             # model/rendering.py:92-93,169-181: rays warped to NDC (near plane 1.0), samples on [0, 1] without jitter;
             # the view-direction encoding keeps the world-space ray.
@@ -127,6 +126,22 @@ class Renderer(nn.Module):
                                                         dirs.detach(), None if noise is None else noise.reshape(n_points, S),
                                                         ray_o=None if ray_o is None else ray_o.detach(),
                                                         view=None if view is None else view.detach())
+        diff_norm = None
+        if cfg['normal_loss'] and not eval_:
+            # model/rendering.py:127-135: normals at the depth-map surface points and at jittered neighbours.  Nothing downstream
+            # reads it (model/losses.py and model/training.py never touch out_dict['normal']), so it is computed forward only;
+            # the draw comes after the stratified jitter, as in the reference.
+            with torch.no_grad():
+                d_i = d_gt.detach()
+                dists = torch.where(torch.isfinite(d_i), d_i, torch.ones_like(d_i))
+                dists = torch.where(d_i == 0, torch.zeros_like(dists), dists)
+                points = origin.detach().view(1, 3) + dirs_world.detach() * dists.unsqueeze(-1)
+                surface = points[mask]
+                n_s = surface.shape[0]
+                neigh = surface + (torch.rand_like(surface) - 0.5) * 0.01
+                g = self.model.gradient(torch.cat([surface, neigh], dim=0), it)[:, 0, :]
+                normals = g / (g.norm(2, dim=1).unsqueeze(-1) + 10 ** (-5))
+                diff_norm = torch.norm(normals[:n_s] - normals[n_s:], dim=-1)
         if eval_ and cfg['normalise_ray']:  # model/rendering.py:144-148
             dist = dist / nrm
             d_gt = d_gt / nrm
@@ -140,7 +155,7 @@ class Renderer(nn.Module):
             depth_gt = 1 - 1 / depth_gt
             d_gt = 1 - 1 / d_gt
         return {
-            'rgb': rgb.reshape(batch_size, -1, 3), 'z_vals': z, 'normal': None,
+            'rgb': rgb.reshape(batch_size, -1, 3), 'z_vals': z, 'normal': diff_norm,
             'depth_pred': depth_pred, 'depth_gt': depth_gt, 'alpha': alpha,
             'depth_pred_dense': dist, 'depth_gt_dense': d_gt, 'mask': mask, 'weights': w,
         }

@@ -82,3 +82,39 @@ def test_sphere_intersection_and_misses():
     got, gmask = geometry.get_sphere_intersection(cam.to(dev()), dirs.to(dev()), 4.0)
     assert torch.equal(gmask.cpu(), wmask) and 0 < int(wmask.sum()) < 200
     assert_close(got, want, 1e-5, 1e-5, "sphere intersections")
+
+
+def test_normal_loss_output_vs_oracle():
+    """rendering.normal_loss (model/rendering.py:127-135): out_dict['normal'] = |n(p) - n(p + jitter)| at the depth-map surface
+    points, normals from the density gradient.  The jitter is the first device draw after the (injected) stratified noise."""
+    import copy
+    import model as mdl
+    from oracle import nope_oracle as O
+    cfg = copy.deepcopy(syn.default_cfg())
+    cfg["rendering"]["normal_loss"] = True
+    scene = syn.make_scene("tiny")
+    sd = _geometry_state()
+    nerf = mdl.OfficialStaticNerf(cfg)
+    nerf.load_state_dict(sd)
+    renderer = mdl.Renderer(nerf, dict(cfg["rendering"], precision="fp32"), device=dev())
+    R = 40
+    idx = syn.ray_choice(scene["h"], scene["w"], R)
+    pixels = O.pixel_grid(scene["h"], scene["w"])[1][:, idx]
+    depth = scene["depths"][1].reshape(1, -1, 1)[:, idx].clone()
+    depth[0, 5, 0] = 0.0                                        # one masked ray
+    world = torch.inverse(scene["poses_gt"][1]).unsqueeze(0)
+    noise = syn.jitter(R)
+    torch.manual_seed(77)
+    out = renderer(pixels.to(dev()), depth.to(dev()), scene["camera_mat"].to(dev()), world.to(dev()), scene["scale_mat"].to(dev()),
+                   "nope_nerf", add_noise=True, eval_=False, noise=noise.to(dev()))
+    assert out["normal"] is not None and out["normal"].shape == (R - 1,)
+    torch.manual_seed(77)
+    jit = torch.rand(R - 1, 3, device=dev()).cpu()              # the same draw as rand_like(surface_points)
+    o, d, _, d_gt, mask = O.ray_setup(pixels, depth, scene["camera_mat"], world, scene["scale_mat"])
+    surf = (o.reshape(1, 3) + d * d_gt.reshape(-1, 1))[mask]
+    pp = torch.cat([surf, surf + (jit - 0.5) * 0.01], 0)
+    g = O.density_gradient(sd, pp)[:, 0, :]
+    n = g / (g.norm(2, dim=1).unsqueeze(-1) + 1e-5)
+    want = torch.norm(n[:R - 1] - n[R - 1:], dim=-1)
+    print("normal-loss output max err %.3e (values up to %.3e)" % (max_err(out["normal"], want), float(want.max())))
+    assert_close(out["normal"], want, 2e-3, 2e-4, "diff_norm")
