@@ -206,9 +206,10 @@ def render_nograd(cfg, params, packed, origin, dirs, noise, want_aux=True, ray_o
     noise = f32(noise).reshape(R, S) if noise is not None else None
     params = [f32(p) for p in params]
     rgb, dist = torch.empty(R, 3, device=dev), torch.empty(R, device=dev)
-    w = torch.empty(R, S, device=dev) if want_aux else None
+    full = want_aux is True                      # want_aux == 'alpha': only the per-sample alpha
+    w = torch.empty(R, S, device=dev) if full else None
     a = torch.empty(R, S, device=dev) if want_aux else None
-    z = torch.empty(R, S, device=dev) if want_aux else None
+    z = torch.empty(R, S, device=dev) if full else None
     nbytes = workspace_bytes(cfg, 0)
     ws = _workspace(dev, nbytes, "render_eval")
     parr = K.param_ptr_array(params)

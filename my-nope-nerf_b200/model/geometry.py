@@ -49,22 +49,45 @@ def secant(model, f_low, f_high, d_low, d_high, n_secant_steps, ray0, ray_dirs, 
     return d_pred
 
 
-def ray_marching(model, cam, ray_dirs, tau=0.5, n_steps=512, n_secant_steps=8, depth_range=(0., 2.4), max_points=3500000, rad=1.0):
+def _proposals_fused(renderer, cam, ray_dirs, d_prop, tau):
+    """Occupancy at the (R, n) proposal depths through the fused tensor-core render kernel: every run of 128 consecutive
+    proposals of a ray is one pseudo-ray with its own origin cam + dir * d[128 j] and direction dir * (d[128 j + 127] - d[128 j]),
+    sampled at linspace(0, 1, 128) without jitter; the kernel's per-sample `alpha` output is the occupancy (dist_alpha off)."""
+    R, n = d_prop.shape
+    seg = n // 128
+    d0 = d_prop[:, 0::128][:, :seg]                                   # (R, seg) first depth of each run
+    d1 = d_prop[:, 127::128][:, :seg]
+    ray_o = (cam.view(1, 1, 3) + ray_dirs.unsqueeze(1) * d0.unsqueeze(-1)).reshape(-1, 3).contiguous()
+    dirs = (ray_dirs.unsqueeze(1) * (d1 - d0).unsqueeze(-1)).reshape(-1, 3).contiguous()
+    model = renderer.model
+    params = [p.detach() for p in model.param_list()]
+    packed = renderer._packed_weights(model.param_list())
+    rc = _ops.make_cfg(R * seg, 128, 0.0, 1.0, model.occ_activation == 'softplus', 0, 0, 0, renderer._prec())
+    _, _, _, alpha, _ = _ops.render_nograd(rc, params, packed, cam, dirs, None, want_aux='alpha', ray_o=ray_o, view=dirs)
+    return alpha.view(R, n) - tau
+
+
+def ray_marching(model, cam, ray_dirs, tau=0.5, n_steps=512, n_secant_steps=8, depth_range=(0., 2.4), max_points=3500000, rad=1.0,
+                 renderer=None):
     """cam (3,), ray_dirs (R,3) -> d (R,): surface distance, inf where no outside->inside crossing, 0 where the first sample is
-    already occupied (model/rendering.py:274-385)."""
+    already occupied (model/rendering.py:274-385).  With `renderer` on the bf16 path and n_steps a multiple of 128 the proposals
+    are evaluated by the fused tensor-core kernel (the secant refinement stays on the fp32 point kernels)."""
     R = ray_dirs.shape[0]
     dev = ray_dirs.device
     inter, _ = get_sphere_intersection(cam, ray_dirs, r=rad)
     d_far = inter[:, 1]
     u = torch.linspace(0, 1, steps=n_steps, device=dev).view(1, n_steps)
     d_prop = depth_range[0] * (1. - u) + d_far.view(R, 1) * u                      # (R, n)
-    # rows of rays per occupancy call so that one call stays below max_points
-    rows = max(1, int(max_points) // n_steps)
-    vals = []
-    for a in range(0, R, rows):
-        p = cam.view(1, 1, 3) + ray_dirs[a:a + rows].unsqueeze(1) * d_prop[a:a + rows].unsqueeze(-1)
-        vals.append(_occupancy(model, p.reshape(-1, 3), tau, max_points).view(-1, n_steps))
-    val = torch.cat(vals, 0)
+    if renderer is not None and renderer.precision == 'bf16' and n_steps % 128 == 0 and not model.dist_alpha:
+        val = _proposals_fused(renderer, cam, ray_dirs, d_prop, tau)
+    else:
+        # rows of rays per occupancy call so that one call stays below max_points
+        rows = max(1, int(max_points) // n_steps)
+        vals = []
+        for a in range(0, R, rows):
+            p = cam.view(1, 1, 3) + ray_dirs[a:a + rows].unsqueeze(1) * d_prop[a:a + rows].unsqueeze(-1)
+            vals.append(_occupancy(model, p.reshape(-1, 3), tau, max_points).view(-1, n_steps))
+        val = torch.cat(vals, 0)
     mask_0_not_occupied = val[:, 0] < 0
     sign_matrix = torch.cat([torch.sign(val[:, :-1] * val[:, 1:]), torch.ones(R, 1, device=dev)], dim=-1)
     cost_matrix = sign_matrix * torch.arange(n_steps, 0, -1, device=dev).float()
@@ -96,7 +119,7 @@ def phong_render(renderer, origin, ray_dirs, it=0):
     was_training = model.training
     model.eval()
     with torch.no_grad():
-        d_i = ray_marching(model, origin, ray_dirs, n_secant_steps=8, n_steps=512, rad=rad)
+        d_i = ray_marching(model, origin, ray_dirs, n_secant_steps=8, n_steps=512, rad=rad, renderer=renderer)
         mask_zero_occupied = d_i == 0
         mask_pred = torch.isfinite(d_i)
         dists = torch.ones_like(d_i)

@@ -51,7 +51,7 @@ class Renderer(nn.Module):
         """Reference signature (model/rendering.py:274): ray0 (1,R,3) repeated camera centre, ray_direction (1,R,3) -> (1,R)."""
         return geometry.ray_marching(model, ray0[0, 0], ray_direction[0], tau=0.5, n_steps=int(n_steps[0]),
                                      n_secant_steps=n_secant_steps, depth_range=depth_range, max_points=max_points,
-                                     rad=rad).unsqueeze(0)
+                                     rad=rad, renderer=self if model is self.model else None).unsqueeze(0)
 
     def to(self, device):
         new = super().to(device)
