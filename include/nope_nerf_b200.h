@@ -67,6 +67,18 @@ int nnb_distortion_fwd(const float *scales, const float *shifts, int cam_id, int
 int nnb_distortion_bwd(const float *scales, int cam_id, int n_cams, int fix_scaleN, const float *d_out2,
                        float *d_scale_row, float *d_shift_row, void *stream);
 
+/* Ray choice (model/training.py:277 `torch.randperm(h*w)[:n_points]`): n_pick DISTINCT indices of [0, n_total), the head of
+ * a keyed pseudo-random permutation (6-round Feistel network with cycle walking), without sorting n_total keys.
+ * keys: 6 int64 on the device (low 32 bits used), drawn by the caller from its generator; out (n_pick,) int64. */
+int nnb_ray_choice(const int64_t *keys, long long n_total, int n_pick, int64_t *out, void *stream);
+
+/* Batch staging for the captured step: n <= NNB_COPY_MAX device-to-device copies (HOST arrays of device pointers and
+ * byte counts, passed to the kernel by value) and up to two int64 scalars (the frame indices of model/training.py:262,323;
+ * scalar_dst[q] NULL = skip) in ONE launch instead of one memcpy node per tensor of the batch dict. */
+#define NNB_COPY_MAX 16
+int nnb_copy_many(const void *const *src, void *const *dst, const unsigned long long *bytes, int n,
+                  int64_t *const *scalar_dst, const int64_t *scalar, void *stream);
+
 /* arange_pixels (model/common.py:13-40): loc (h*w,2) int64 [x,y], scaled (h*w,2) fp32 in [-1,1]. */
 int nnb_pixel_grid(int h, int w, int64_t *loc, float *scaled, void *stream);
 

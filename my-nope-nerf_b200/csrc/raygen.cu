@@ -2,6 +2,7 @@
 // HBM/latency-bound elementwise kernels: one thread per ray/point, coalesced SoA-ish access,
 // block-level shuffle reductions for the handful of matrix/scalar gradients.
 #include "nnb_common.cuh"
+#include <string.h>
 
 // ---------------------------------------------------------------------------------------------
 // arange_pixels: model/common.py:13-40
@@ -330,6 +331,65 @@ static inline int grid_for(int n, int threads) {
   return g < 1 ? 1 : (g > cap ? cap : g);
 }
 
+// ---- ray choice: the first n_pick entries of a keyed pseudo-random permutation of [0, n_total) -------------------------------------
+// Replaces torch.randperm(h*w)[:n_points] (model/training.py:277), which sorts all h*w keys (five radix passes, ~240 us on the
+// critical path before the render) to keep 4,096 of them.  A balanced Feistel network over 2^(2 half) >= n_total values is a
+// bijection for any round function; values that land outside [0, n_total) walk the cycle until they return inside, which keeps
+// the map a bijection of [0, n_total).  Six rounds keyed by `keys` (drawn by the caller from its generator).
+__device__ __forceinline__ uint32_t feistel_round(uint32_t x, uint32_t k) {
+  x ^= k;
+  x *= 0x9E3779B1u; x ^= x >> 15;
+  x *= 0x85EBCA77u; x ^= x >> 13;
+  x *= 0xC2B2AE3Du; x ^= x >> 16;
+  return x;
+}
+
+__global__ void ray_choice_kernel(const int64_t *__restrict__ keys, long long n_total, int n_pick, int half, int64_t *__restrict__ out) {
+  const uint32_t mask = (1u << half) - 1u;
+  uint32_t k[6];
+#pragma unroll
+  for (int r = 0; r < 6; ++r) k[r] = (uint32_t)keys[r];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_pick; i += gridDim.x * blockDim.x) {
+    unsigned long long x = (unsigned long long)i;
+    do {
+      uint32_t l = (uint32_t)(x >> half) & mask, r = (uint32_t)x & mask;
+#pragma unroll
+      for (int q = 0; q < 6; ++q) {
+        const uint32_t t = l ^ (feistel_round(r, k[q]) & mask);
+        l = r; r = t;
+      }
+      x = ((unsigned long long)l << half) | r;
+    } while (x >= (unsigned long long)n_total);
+    out[i] = (int64_t)x;
+  }
+}
+
+// ---- batch staging: up to NNB_COPY_MAX device-to-device copies and two index scalars in one launch ---------------------------------
+struct CopyJobs {
+  const void *src[NNB_COPY_MAX];
+  void *dst[NNB_COPY_MAX];
+  unsigned long long bytes[NNB_COPY_MAX];
+  int n;
+  int64_t *scalar_dst[2];
+  int64_t scalar[2];
+};
+
+__global__ void __launch_bounds__(256) copy_many_kernel(const CopyJobs J) {
+  if (blockIdx.x == 0 && threadIdx.x < 2 && J.scalar_dst[threadIdx.x]) *J.scalar_dst[threadIdx.x] = J.scalar[threadIdx.x];
+  const unsigned long long t0 = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x, nt = (unsigned long long)gridDim.x * blockDim.x;
+  for (int j = 0; j < J.n; ++j) {
+    const unsigned long long nb = J.bytes[j];
+    const bool vec = (((uintptr_t)J.src[j] | (uintptr_t)J.dst[j]) & 15) == 0;
+    const unsigned long long nv = vec ? nb / 16 : 0;
+    const uint4 *s4 = static_cast<const uint4 *>(J.src[j]);
+    uint4 *d4 = static_cast<uint4 *>(J.dst[j]);
+    for (unsigned long long e = t0; e < nv; e += nt) d4[e] = __ldcs(s4 + e);
+    const unsigned char *s1 = static_cast<const unsigned char *>(J.src[j]);
+    unsigned char *d1 = static_cast<unsigned char *>(J.dst[j]);
+    for (unsigned long long e = nv * 16 + t0; e < nb; e += nt) d1[e] = s1[e];
+  }
+}
+
 extern "C" {
 
 int nnb_pixel_grid(int h, int w, int64_t *loc, float *scaled, void *stream) {
@@ -355,6 +415,41 @@ int nnb_gather_rays_bwd(const int64_t *ray_idx, int n_rays, const float *depth_i
   NNB_CUDA(cudaMemsetAsync(d_scale_shift, 0, 2 * sizeof(float), nnb_stream(stream)));
   if (n_rays == 0) return 0;
   gather_rays_bwd_kernel<<<grid_for(n_rays, 256), 256, 0, nnb_stream(stream)>>>(ray_idx, n_rays, depth_img, d_depth, d_scale_shift);
+  NNB_CHECK_LAUNCH();
+  return 0;
+}
+
+int nnb_ray_choice(const int64_t *keys, long long n_total, int n_pick, int64_t *out, void *stream) {
+  if (!keys || !out || n_total < 1 || n_pick < 0 || n_pick > n_total || n_total > (1ll << 40)) return NNB_ERR_BAD_ARG;
+  if (n_pick == 0) return 0;
+  int half = 1;
+  while ((1ull << (2 * half)) < (unsigned long long)n_total) ++half;
+  ray_choice_kernel<<<grid_for(n_pick, 128), 128, 0, nnb_stream(stream)>>>(keys, n_total, n_pick, half, out);
+  NNB_CHECK_LAUNCH();
+  return 0;
+}
+
+int nnb_copy_many(const void *const *src, void *const *dst, const unsigned long long *bytes, int n, int64_t *const *scalar_dst,
+                  const int64_t *scalar, void *stream) {
+  if (n < 0 || n > NNB_COPY_MAX || (n > 0 && (!src || !dst || !bytes))) return NNB_ERR_BAD_ARG;
+  CopyJobs J;
+  memset(&J, 0, sizeof(J));
+  unsigned long long total = 0;
+  for (int j = 0; j < n; ++j) {
+    if (bytes[j] && (!src[j] || !dst[j])) return NNB_ERR_BAD_ARG;
+    J.src[j] = src[j]; J.dst[j] = dst[j]; J.bytes[j] = bytes[j];
+    total += bytes[j];
+  }
+  J.n = n;
+  for (int q = 0; q < 2; ++q) {
+    J.scalar_dst[q] = scalar_dst ? scalar_dst[q] : nullptr;
+    J.scalar[q] = scalar ? scalar[q] : 0;
+  }
+  if (total == 0 && !J.scalar_dst[0] && !J.scalar_dst[1]) return 0;
+  const unsigned long long want = (total / 16 + 255) / 256;
+  const int sms = nnb_sm_count();
+  const int grid = (int)(want < 1 ? 1 : (want > (unsigned long long)(8 * sms) ? (unsigned long long)(8 * sms) : want));
+  copy_many_kernel<<<grid, 256, 0, nnb_stream(stream)>>>(J);
   NNB_CHECK_LAUNCH();
   return 0;
 }

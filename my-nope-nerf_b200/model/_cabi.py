@@ -37,6 +37,7 @@ _p, _i, _f, _sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
 _exp = C.POINTER(RayExtras)
 _cfgp = C.POINTER(RenderCfg)
 _pp = C.POINTER(C.c_void_p)
+COPY_MAX = 16   # NNB_COPY_MAX
 
 # name -> argtypes (return type is int unless listed in _RESTYPE)
 SIGNATURES = {
@@ -51,6 +52,8 @@ SIGNATURES = {
     "nnb_distortion_fwd": [_p, _p, _i, _i, _i, _p, _p],
     "nnb_distortion_bwd": [_p, _i, _i, _i, _p, _p, _p, _p],
     "nnb_pixel_grid": [_i, _i, _p, _p, _p],
+    "nnb_ray_choice": [_p, C.c_longlong, _i, _p, _p],
+    "nnb_copy_many": [_p, _p, _p, _i, _p, _p, _p],
     "nnb_gather_rays_fwd": [_p, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p],
     "nnb_gather_rays_bwd": [_p, _i, _p, _p, _p, _p],
     "nnb_raygen_fwd": [_p, _p, _p, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p],

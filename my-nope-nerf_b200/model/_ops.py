@@ -94,6 +94,31 @@ def pixel_grid(h, w, device):
     return loc, scaled
 
 
+def ray_choice(n_total, n_pick, device):
+    """n_pick distinct pixel indices of [0, n_total), uniformly scattered: the draw of model/training.py:277
+    (`torch.randperm(h*w)[:n_points]`) without sorting h*w keys.  The six round keys come from torch's generator on `device`
+    (graph-safe), so `torch.manual_seed` fixes the choice."""
+    keys = torch.randint(0, 2 ** 31 - 1, (6,), device=device, dtype=torch.int64)
+    out = torch.empty(int(n_pick), device=device, dtype=torch.int64)
+    call("nnb_ray_choice", ptr(keys), int(n_total), int(n_pick), ptr(out), stream())
+    return out
+
+
+def copy_many(pairs, scalars=()):
+    """One launch for a list of (dst, src) device tensors (same nbytes each pair, contiguous) and up to two
+    (dst int64 device tensor, python int) scalars: the batch staging of Trainer.train_step_graphed."""
+    for i in range(0, max(len(pairs), 1), K.COPY_MAX):
+        part = pairs[i:i + K.COPY_MAX]
+        n = len(part)
+        src = (C.c_void_p * max(n, 1))(*[s.data_ptr() for _, s in part])
+        dst = (C.c_void_p * max(n, 1))(*[d.data_ptr() for d, _ in part])
+        nb = (C.c_ulonglong * max(n, 1))(*[d.numel() * d.element_size() for d, _ in part])
+        sc = scalars if i == 0 else ()
+        sd = (C.c_void_p * 2)(*([t.data_ptr() for t, _ in sc] + [None] * (2 - len(sc))))
+        sv = (C.c_int64 * 2)(*([int(v) for _, v in sc] + [0] * (2 - len(sc))))
+        call("nnb_copy_many", src, dst, nb, n, sd, sv, stream())
+
+
 class GatherRays(torch.autograd.Function):
     """pixels / rgb_gt / depth*scale+shift at ray_idx (model/training.py:264,285-288; model/network.py:21-24).
     scale_shift: tensor [scale, shift] on device or None."""

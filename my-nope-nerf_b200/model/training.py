@@ -2,7 +2,7 @@
 process_data_dict, anneal; same loss_dict keys plus `scale`, `shift`).
 
 compute_loss keeps the reference's control flow (weight annealing, reference-frame pairing, zero-weight skipping,
-RNG draw order: randperm for the rays, then rand for the stratified jitter) and replaces its tensor math with the
+RNG draw order: the ray choice, then rand for the stratified jitter) and replaces its tensor math with the
 C-ABI kernels:  pose exp-map, 4x4 inverse, distortion, fused ray gather, ray generation, fused render,
 point-cloud back-projection, reprojection sampling and the loss kernels.  Multi-GPU: every rank draws the same
 global ray batch and takes its contiguous shard; gradients are averaged with ONE flat NCCL allreduce (parallel.py).
@@ -111,11 +111,18 @@ class Trainer(object):
             slot = self._capture_step(data, tensors, it, epoch, scheduling_start)
             self._graphs[key] = slot
         static = slot['static']
+        # batch staging: every device-resident tensor of the batch and the two frame indices in ONE launch (nnb_copy_many)
+        pairs = []
         for k in tensors:
-            static[k].copy_(data[k], non_blocking=True)
-        static['img.idx_dev'].copy_(data['img.idx'].reshape(1), non_blocking=True)
+            src, dst = data[k], static[k]
+            if src.is_cuda and src.is_contiguous() and src.dtype == dst.dtype and src.device == dst.device:
+                pairs.append((dst, src))
+            else:
+                dst.copy_(src, non_blocking=True)
+        scalars = [(static['img.idx_dev'], idx)]
         if ref >= 0:
-            static['img.ref_idxs_dev'].copy_(data['img.ref_idxs'].reshape(1), non_blocking=True)
+            scalars.append((static['img.ref_idxs_dev'], ref))
+        _ops.copy_many(pairs, scalars)
         static['img.idx'], static['img.ref_idxs'] = data.get('img.idx'), data.get('img.ref_idxs')
         slot['graph'].replay()
         self.graphed_launches = getattr(self, 'graphed_launches', 0) + slot['n_launches']
@@ -156,11 +163,11 @@ class Trainer(object):
         for m in self._all_nets():
             m.train()
         static = {k: data[k].to(dev, copy=True) for k in tensors}
-        static['img.idx_dev'] = data['img.idx'].reshape(1).to(dev)
+        static['img.idx_dev'] = data['img.idx'].reshape(1).to(dev, dtype=torch.int64)
         static['img.idx'] = data.get('img.idx')
         static['img.ref_idxs'] = data.get('img.ref_idxs')
         if data.get('img.ref_idxs') is not None:
-            static['img.ref_idxs_dev'] = data['img.ref_idxs'].reshape(1).to(dev)
+            static['img.ref_idxs_dev'] = data['img.ref_idxs'].reshape(1).to(dev, dtype=torch.int64)
         params = [p for m in self._all_nets() for p in m.parameters() if p.requires_grad]
 
         geom = torch.cuda.Stream() if self.fork_geometry else None
@@ -280,7 +287,7 @@ class Trainer(object):
         # poses and distortion parameters only, not on the rendered rays.  It is issued BEFORE the ray choice and the render so that, when a second
         # stream is set (train_step_graphed), its many small launches become a parallel branch of the captured graph and run
         # beside the persistent render kernels, in the forward and (autograd replays each node on its forward stream) the
-        # backward pass.  Neither branch draws random numbers, so the RNG order (randperm, then rand) is unchanged.
+        # backward pass.  Neither branch draws random numbers, so the RNG order (ray choice, then rand) is unchanged.
         geom = self._geom_stream if use_ref_imgs else None
         if use_ref_imgs:
             main_stream = torch.cuda.current_stream() if geom is not None else None
@@ -344,12 +351,12 @@ class Trainer(object):
         if self.fixed_ray_idx is not None:
             ray_idx = self.fixed_ray_idx.to(device)
         else:
-            ray_idx = torch.randperm(h * w, device=device)[:n_points]
+            ray_idx = _ops.ray_choice(h * w, min(n_points, h * w), device)
             if data.get('img.dpt') is None:
                 depth_mask_flat = torch.flatten(depth_mask)
                 while not depth_mask_flat[ray_idx].any():
                     print('No valid depths found, resampling...')
-                    ray_idx = torch.randperm(h * w, device=device)[:n_points]
+                    ray_idx = _ops.ray_choice(h * w, min(n_points, h * w), device)
         n_global = ray_idx.numel()
         lo, hi = self.dp.shard(n_global)
         ray_idx_local = ray_idx[lo:hi].contiguous()

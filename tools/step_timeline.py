@@ -43,3 +43,25 @@ print("--- GPU time per step by kernel")
 for e in rows:
     if e.self_device_time_total > 0:
         print("%-90s gpu %8.1f us  n=%d" % (e.key[:90], e.self_device_time_total / 3, e.count // 3))
+if '--trace' in sys.argv:
+    # chronological device activity of the LAST profiled step: start offset, duration, stream, name; plus idle gaps on the union
+    path = os.path.join(ROOT, "gpurun_out", "step_trace.json")
+    os.makedirs(os.path.dirname(path), exist_ok=True)
+    prof.export_chrome_trace(path)
+    tr_ev = [e for e in json.load(open(path))["traceEvents"] if e.get("cat") in ("kernel", "gpu_memcpy", "gpu_memset")]
+    tr_ev.sort(key=lambda e: e["ts"])
+    n3 = len(tr_ev) // 3
+    last = tr_ev[2 * n3:]
+    t0 = last[0]["ts"]
+    print("--- last step, chronological (us from its first device activity): start dur stream name")
+    busy_end = t0
+    idle = 0.0
+    for e in last:
+        if e["ts"] > busy_end:
+            idle += e["ts"] - busy_end
+        gap = e["ts"] - busy_end
+        busy_end = max(busy_end, e["ts"] + e["dur"])
+        print("%9.1f %8.1f s%-3s %s%s" % (e["ts"] - t0, e["dur"], e["args"].get("stream", "?"), e["name"][:80],
+                                         ("   <- idle %.1f before" % gap) if gap > 1.5 else ""))
+    print("span %.1f us, device idle (no stream busy) %.1f us" % (busy_end - t0, idle))
+    os.remove(path)

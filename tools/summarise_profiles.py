@@ -71,7 +71,7 @@ if __name__ == "__main__":
         rep = os.path.join(OUT, "%s_chamfer.ncu-rep" % tag)
         if os.path.exists(rep):
             f.write("\n")
-            full_summary(rep, "Chamfer sweeps: tools/time_chamfer.py 28830 [--raster from r1e on] (P = 28,830 per cloud), -k regex:chamfer_tc_kernel (r1d: random-order clouds, the gated-out first screen returns at once: 4.6 us)", f)
+            full_summary(rep, "Chamfer sweeps: tools/time_chamfer.py 28830 --raster (P = 28,830 per cloud, raster-order clouds: sub-sampled screen, screen and exact sweep over the stage lists), -k regex:chamfer_tc_kernel -s 3 -c 3", f)
         for name in ("time_train_mlp.json", "time_chamfer.json"):
             p = os.path.join(OUT, "%s_%s" % (tag, name))
             if os.path.exists(p):
