@@ -60,6 +60,12 @@ int nnb_pose_bwd(const float *r, const float *t, const float *init_c2w, int cam_
 int nnb_mat4_inv_fwd(const float *m, float *inv, void *stream);
 int nnb_mat4_inv_bwd(const float *inv, const float *d_inv, float *d_m, void *stream);
 
+/* Relative pose between the frame and its reference: c = a @ b on row-major 4x4 matrices (model/training.py:329
+ * `ref_Rt @ torch.inverse(world_mat)`, :344 `world_mat @ torch.inverse(ref_Rt)`).  Backward: d_a = d_c b^T, d_b = a^T d_c
+ * (either may be NULL). */
+int nnb_mat4_mul_fwd(const float *a, const float *b, float *c, void *stream);
+int nnb_mat4_mul_bwd(const float *a, const float *b, const float *d_c, float *d_a, float *d_b, void *stream);
+
 /* Learn_Distortion.forward: model/distortions.py:19-27.  out = {scale, shift}.
  * scale below 0.01 -> constant 0.01 (gradient cut); last camera pinned to 1 when fix_scaleN. */
 int nnb_distortion_fwd(const float *scales, const float *shifts, int cam_id, int n_cams, int fix_scaleN,
@@ -170,12 +176,17 @@ int nnb_render_bwd(const nnb_render_cfg *cfg, const float *const *params_host, c
  * model/rendering.py:169-181 + get_ndc_rays_fxfy model/common.py:632-675): the sample points are
  * ray_origins[r] + dirs[r] * z while the view-direction encoding still sees -view_dirs[r].
  * NULL members fall back to the shared `origin` / to `dirs`.  The d_* members are backward outputs
- * ((R,3), overwritten) and are required exactly when their input is given. */
+ * ((R,3), overwritten) and are required exactly when their input is given.
+ * wgrad_stream (bf16 path, backward only; NULL = `stream`): the weight-gradient kernel is launched on this stream, ordered
+ * after the data-gradient kernel by an event.  It keeps one small CTA per SM (64 registers x 192 threads), so what follows the
+ * render backward on `stream` -- the ray-generation and pose backward, which need d_origin / d_dirs only -- runs beside it.
+ * The caller joins wgrad_stream before it reads d_params or reuses the workspace. */
 typedef struct {
   const float *ray_origins; /* (R,3) or NULL */
   const float *view_dirs;   /* (R,3) or NULL */
   float *d_ray_origins;     /* (R,3) or NULL */
   float *d_view_dirs;       /* (R,3) or NULL */
+  void *wgrad_stream;       /* cudaStream_t or NULL */
 } nnb_ray_extras;
 
 /* nnb_render_fwd / nnb_render_bwd with the extras above (ex == NULL: identical to the plain calls). */

@@ -1605,9 +1605,16 @@ int nnb_tc_render_bwd(const nnb_render_cfg *cfg, const float *const *params, con
   W.trace = g_trace;
   for (int i = 0; i < NNB_NUM_PARAMS; ++i) W.d_params[i] = d_params[i];
   W.n_tiles = R; W.n_jobs = (int)wg_plan().jobs.size();
-  tc_wgrad_kernel<<<wg_plan().n_ctas, 192, SW_TOTAL, s>>>(W);
+  cudaStream_t sw = (ex && ex->wgrad_stream) ? nnb_stream(ex->wgrad_stream) : s;
+  if (sw != s) {   // fork: the weight gradient follows the data-gradient kernel on its own stream; the caller joins
+    static cudaEvent_t fork_ev = nullptr;
+    if (!fork_ev) NNB_CUDA(cudaEventCreateWithFlags(&fork_ev, cudaEventDisableTiming));
+    NNB_CUDA(cudaEventRecord(fork_ev, s));
+    NNB_CUDA(cudaStreamWaitEvent(sw, fork_ev, 0));
+  }
+  tc_wgrad_kernel<<<wg_plan().n_ctas, 192, SW_TOTAL, sw>>>(W);
   NNB_CHECK_LAUNCH();
-  if (g_bwd_timing) NNB_CUDA(cudaEventRecord(g_bwd_ev[2], s));
+  if (g_bwd_timing) NNB_CUDA(cudaEventRecord(g_bwd_ev[2], sw));
   return 0;
 }
 

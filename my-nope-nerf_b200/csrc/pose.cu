@@ -41,6 +41,34 @@ __global__ void mat4_inv_bwd_kernel(const float *__restrict__ inv, const float *
   for (int i = 0; i < 16; ++i) dm[i] = (float)c[i];
 }
 
+// C = A B on 4x4 row-major matrices (the relative pose ref_Rt @ inverse(world_mat), model/training.py:329,344), one thread per
+// element, no shared memory: unlike the library GEMM it replaces it can share an SM with the persistent render kernels.
+__global__ void mat4_mul_fwd_kernel(const float *__restrict__ a, const float *__restrict__ b, float *__restrict__ c) {
+  const int i = threadIdx.x >> 2, j = threadIdx.x & 3;
+  if (threadIdx.x >= 16 || blockIdx.x != 0) return;
+  float acc = 0.f;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) acc = fmaf(a[4 * i + k], b[4 * k + j], acc);
+  c[threadIdx.x] = acc;
+}
+
+// dA = dC B^T (threads 0-15), dB = A^T dC (threads 16-31)
+__global__ void mat4_mul_bwd_kernel(const float *__restrict__ a, const float *__restrict__ b, const float *__restrict__ dc,
+                                    float *__restrict__ da, float *__restrict__ db) {
+  if (blockIdx.x != 0 || threadIdx.x >= 32) return;
+  const int e = threadIdx.x & 15, i = e >> 2, j = e & 3;
+  float acc = 0.f;
+  if (threadIdx.x < 16) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) acc = fmaf(dc[4 * i + k], b[4 * j + k], acc);
+    if (da) da[e] = acc;
+  } else {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) acc = fmaf(a[4 * k + i], dc[4 * k + j], acc);
+    if (db) db[e] = acc;
+  }
+}
+
 // model/distortions.py:19-27
 __global__ void distortion_fwd_kernel(const float *__restrict__ scales, const float *__restrict__ shifts, int cam,
                                       int n, int fix, float *__restrict__ out) {
@@ -87,6 +115,20 @@ int nnb_mat4_inv_fwd(const float *m, float *inv, void *stream) {
 int nnb_mat4_inv_bwd(const float *inv, const float *d_inv, float *d_m, void *stream) {
   if (!inv || !d_inv || !d_m) return NNB_ERR_BAD_ARG;
   mat4_inv_bwd_kernel<<<1, 32, 0, nnb_stream(stream)>>>(inv, d_inv, d_m);
+  NNB_CHECK_LAUNCH();
+  return 0;
+}
+
+int nnb_mat4_mul_fwd(const float *a, const float *b, float *c, void *stream) {
+  if (!a || !b || !c) return NNB_ERR_BAD_ARG;
+  mat4_mul_fwd_kernel<<<1, 32, 0, nnb_stream(stream)>>>(a, b, c);
+  NNB_CHECK_LAUNCH();
+  return 0;
+}
+
+int nnb_mat4_mul_bwd(const float *a, const float *b, const float *d_c, float *d_a, float *d_b, void *stream) {
+  if (!a || !b || !d_c || (!d_a && !d_b)) return NNB_ERR_BAD_ARG;
+  mat4_mul_bwd_kernel<<<1, 32, 0, nnb_stream(stream)>>>(a, b, d_c, d_a, d_b);
   NNB_CHECK_LAUNCH();
   return 0;
 }

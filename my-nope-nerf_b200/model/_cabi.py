@@ -30,7 +30,8 @@ class RenderCfg(C.Structure):
 
 class RayExtras(C.Structure):
     """nnb_ray_extras: per-ray origins / view directions of the NDC sampling branch and their backward outputs."""
-    _fields_ = [("ray_origins", C.c_void_p), ("view_dirs", C.c_void_p), ("d_ray_origins", C.c_void_p), ("d_view_dirs", C.c_void_p)]
+    _fields_ = [("ray_origins", C.c_void_p), ("view_dirs", C.c_void_p), ("d_ray_origins", C.c_void_p), ("d_view_dirs", C.c_void_p),
+                ("wgrad_stream", C.c_void_p)]
 
 
 _p, _i, _f, _sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
@@ -49,6 +50,8 @@ SIGNATURES = {
     "nnb_pose_bwd": [_p, _p, _p, _i, _p, _p, _p, _p],
     "nnb_mat4_inv_fwd": [_p, _p, _p],
     "nnb_mat4_inv_bwd": [_p, _p, _p, _p],
+    "nnb_mat4_mul_fwd": [_p, _p, _p, _p],
+    "nnb_mat4_mul_bwd": [_p, _p, _p, _p, _p, _p],
     "nnb_distortion_fwd": [_p, _p, _i, _i, _i, _p, _p],
     "nnb_distortion_bwd": [_p, _i, _i, _i, _p, _p, _p, _p],
     "nnb_pixel_grid": [_i, _i, _p, _p, _p],

@@ -94,6 +94,28 @@ def pixel_grid(h, w, device):
     return loc, scaled
 
 
+class Mat4Mul(torch.autograd.Function):
+    """a @ b on 4x4 matrices (the relative pose of model/training.py:329,344) without a library GEMM."""
+
+    @staticmethod
+    def forward(ctx, a, b):
+        a, b = f32(a).reshape(4, 4), f32(b).reshape(4, 4)
+        out = torch.empty_like(a)
+        call("nnb_mat4_mul_fwd", ptr(a), ptr(b), ptr(out), stream())
+        ctx.save_for_backward(a, b)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        a, b = ctx.saved_tensors
+        da = torch.empty_like(a) if ctx.needs_input_grad[0] else None
+        db = torch.empty_like(b) if ctx.needs_input_grad[1] else None
+        if da is None and db is None:
+            return None, None
+        call("nnb_mat4_mul_bwd", ptr(a), ptr(b), ptr(f32(g).reshape(4, 4)), ptr(da), ptr(db), stream())
+        return da, db
+
+
 def ray_choice(n_total, n_pick, device):
     """n_pick distinct pixel indices of [0, n_total), uniformly scattered: the draw of model/training.py:277
     (`torch.randperm(h*w)[:n_points]`) without sorting h*w keys.  The six round keys come from torch's generator on `device`
@@ -214,10 +236,19 @@ def _workspace(device, nbytes, tag):
     return buf
 
 
-def _extras(ray_o, view, d_ray_o=None, d_view=None):
+# Stream for the weight-gradient kernel of the render backward (nnb_ray_extras.wgrad_stream).  None: everything on the current
+# stream.  Whoever sets it (Trainer.train_step_graphed) joins it before reading parameter gradients.
+wgrad_stream = None
+wgrad_forked = False   # set when a backward handed wgrad_stream to the library since the flag was last cleared
+
+
+def _extras(ray_o, view, d_ray_o=None, d_view=None, backward=False):
     def v(t):
         return ptr(t).value if t is not None else None
-    return K.RayExtras(v(ray_o), v(view), v(d_ray_o), v(d_view))
+    global wgrad_forked
+    ws = wgrad_stream.cuda_stream if (backward and wgrad_stream is not None) else None
+    wgrad_forked = wgrad_forked or ws is not None
+    return K.RayExtras(v(ray_o), v(view), v(d_ray_o), v(d_view), ws)
 
 
 def render_nograd(cfg, params, packed, origin, dirs, noise, want_aux=True, ray_o=None, view=None):
@@ -286,8 +317,9 @@ class RenderRays(torch.autograd.Function):
 
         def opt(g):
             return ptr(f32(g)) if g is not None else None
-        call("nnb_render_bwd", C.byref(cfg), parr, ptr(ctx.packed), ptr(origin), ptr(dirs), ptr(w), ptr(a), ptr(z), opt(g_rgb),
-             opt(g_dist), opt(g_a), opt(g_w), garr, ptr(d_origin), ptr(d_dirs), ptr(ctx.ws), ctx.nbytes, stream())
+        ex = _extras(None, None, backward=True)
+        call("nnb_render_bwd_ex", C.byref(cfg), parr, ptr(ctx.packed), ptr(origin), ptr(dirs), C.byref(ex), ptr(w), ptr(a), ptr(z),
+             opt(g_rgb), opt(g_dist), opt(g_a), opt(g_w), garr, ptr(d_origin), ptr(d_dirs), ptr(ctx.ws), ctx.nbytes, stream())
         ctx.ws = None
         return (None, None, d_origin, d_dirs, None) + tuple(grads)
 
@@ -329,7 +361,7 @@ class RenderRaysEx(torch.autograd.Function):
         d_origin, d_dirs = torch.empty(3, device=dev), torch.empty_like(dirs)
         d_ray_o, d_view = torch.empty_like(ray_o), torch.empty_like(view)
         parr, garr = K.param_ptr_array(params), K.param_ptr_array(grads)
-        ex = _extras(ray_o, view, d_ray_o, d_view)
+        ex = _extras(ray_o, view, d_ray_o, d_view, backward=True)
 
         def opt(g):
             return ptr(f32(g)) if g is not None else None

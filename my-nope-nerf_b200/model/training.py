@@ -27,6 +27,7 @@ class Trainer(object):
         self.model = model
         self.optimizer = optimizer
         self.device = device
+        self.fork_wgrad = True      # train_step_graphed: weight-gradient kernel on its own stream (joined before the optimiser)
         self.fork_geometry = True   # train_step_graphed: reference-frame branch as a parallel branch of the graph
         self._geom_stream = None    # set while train_step_graphed warms up and captures: forks the reference-frame branch
         self.optimizer_pose = optimizer_pose
@@ -171,18 +172,25 @@ class Trainer(object):
         params = [p for m in self._all_nets() for p in m.parameters() if p.requires_grad]
 
         geom = torch.cuda.Stream() if self.fork_geometry else None
+        # the weight-gradient kernel of the render backward runs on its own stream: it leaves room on every SM (64 registers x
+        # 192 threads), so the ray-generation / pose backward chain that follows the data-gradient kernel runs beside it
+        wgrad = torch.cuda.Stream() if (self.fork_wgrad and self.model.renderer.precision == 'bf16') else None
 
         def body():
             for p in params:
                 p.grad = None
             self._geom_stream = geom
+            _ops.wgrad_stream, _ops.wgrad_forked = wgrad, False
             try:
                 ld = self.compute_loss(static, it=it, epoch=epoch, scheduling_start=scheduling_start)
                 ld['loss'].backward()
                 if geom is not None:
                     torch.cuda.current_stream().wait_stream(geom)   # nothing of the branch is left unjoined when capture ends
+                if wgrad is not None and _ops.wgrad_forked:
+                    torch.cuda.current_stream().wait_stream(wgrad)  # parameter gradients complete before the optimiser reads them
             finally:
                 self._geom_stream = None
+                _ops.wgrad_stream = None
             return ld
 
         warn = getattr(torch.autograd.graph, 'set_warn_on_accumulate_grad_stream_mismatch', None)
@@ -305,11 +313,11 @@ class Trainer(object):
                     d1_raw, d2_raw, ss1, ss2 = depth_raw, depth_ref_raw, ss_in, ss_ref
                     img1, img2 = img, ref_img
                     # ref_Rt @ inverse(world_mat) with inverse(world_mat) == c2w (model/training.py:329)
-                    Rt_rel_12 = _ops.Mat4Inverse.apply(c2w_ref) @ c2w
+                    Rt_rel_12 = _ops.Mat4Mul.apply(_ops.Mat4Inverse.apply(c2w_ref), c2w)
                 else:
                     d1_raw, d2_raw, ss1, ss2 = depth_ref_raw, depth_raw, ss_ref, ss_in
                     img1, img2 = ref_img, img
-                    Rt_rel_12 = world_mat[0] @ c2w_ref                 # world_mat @ inverse(ref_Rt) (model/training.py:344)
+                    Rt_rel_12 = _ops.Mat4Mul.apply(world_mat[0], c2w_ref)                 # world_mat @ inverse(ref_Rt) (model/training.py:344)
                 R_rel_12 = Rt_rel_12[:3, :3]
                 t_rel_12 = Rt_rel_12[:3, 3]
                 scale1 = ss1[0] if ss1 is not None else None

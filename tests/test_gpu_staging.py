@@ -66,3 +66,26 @@ def test_copy_many_bytes_and_scalars():
     assert int(a) == 17 and int(b) == 1 << 40
     _ops.copy_many([], [(a, 5)])
     assert int(a) == 5 and int(b) == 1 << 40
+
+
+def test_mat4_mul_forward_and_backward_vs_torch():
+    """nnb_mat4_mul_fwd / _bwd (relative pose, model/training.py:329,344) against torch's matmul and its autograd: fp32, 1e-6."""
+    from model import _ops
+    g = torch.Generator().manual_seed(9)
+    a = torch.randn(4, 4, generator=g).to(dev()).requires_grad_()
+    b = torch.randn(4, 4, generator=g).to(dev()).requires_grad_()
+    w = torch.randn(4, 4, generator=g).to(dev())
+    c = _ops.Mat4Mul.apply(a, b)
+    (c * w).sum().backward()
+    ga, gb = a.grad.clone(), b.grad.clone()
+    a.grad = b.grad = None
+    ref = a.double() @ b.double()
+    (ref * w.double()).sum().backward()
+    assert (c.double() - ref).abs().max() <= 1e-6 * float(ref.abs().max())
+    assert (ga.double() - a.grad.double()).abs().max() <= 1e-6 * float(a.grad.abs().max())
+    assert (gb.double() - b.grad.double()).abs().max() <= 1e-6 * float(b.grad.abs().max())
+    # one-sided gradient (the reference frame's pose detached)
+    a2 = a.detach().clone().requires_grad_()
+    c2 = _ops.Mat4Mul.apply(a2, b.detach())
+    (c2 * w).sum().backward()
+    assert (a2.grad - ga).abs().max() == 0
