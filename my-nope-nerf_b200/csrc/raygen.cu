@@ -488,7 +488,7 @@ int nnb_raygen_bwd(const float *pixels, const float *depth, const float *camera_
 int nnb_backproject_fwd(const float *depth_img, int h, int w, int h4, int w4, const float *scale_shift,
                         const float *camera_mat, float nearest_limit, float *pc, uint8_t *clamped, void *stream) {
   if (!depth_img || !camera_mat || !pc || h4 < 2 || w4 < 2) return NNB_ERR_BAD_ARG;
-  backproject_fwd_kernel<<<grid_for(h4 * w4, 256), 256, 0, nnb_stream(stream)>>>(depth_img, h, w, h4, w4, scale_shift, camera_mat,
+  backproject_fwd_kernel<<<grid_for(h4 * w4, 128), 128, 0, nnb_stream(stream)>>>(depth_img, h, w, h4, w4, scale_shift, camera_mat,
                                                                                 nearest_limit, pc, clamped);
   NNB_CHECK_LAUNCH();
   return 0;

@@ -109,7 +109,10 @@ class Loss(nn.Module):
             loss_dist_1st, loss_dist_2nd = self.get_weight_dist_loss(t_list)
         else:
             loss_dist_1st, loss_dist_2nd = zero, zero
-        # 'pc_loss_pre' / 'rgb_s_loss_pre': the same two calls, already made by the trainer on its reference-frame stream
+        # 'pc_loss_pre' / 'rgb_s_loss_pre': the same two calls, already made by the trainer on its reference-frame stream;
+        # 'join_pre' makes the current stream wait for that stream -- only here, so that the terms above do not wait for it
+        if kwargs.get('join_pre') is not None:
+            kwargs['join_pre']()
         pc_loss, rgb_s_loss = kwargs.get('pc_loss_pre'), kwargs.get('rgb_s_loss_pre')
         if pc_loss is None:
             pc_loss = self.get_pc_loss(X, Y) if weights['pc_weight'] != 0.0 else zero

@@ -395,7 +395,7 @@ class Trainer(object):
             rendered_rgb = rendered_depth = gt_depth = None
 
         if geom is not None:
-            main_stream.wait_stream(geom)
+            kwargs['join_pre'] = lambda: main_stream.wait_stream(geom)   # Loss.forward joins the branch where it first needs it
         if render_model and self.detach_gt_depth:
             gt_depth = gt_depth.detach()
         loss_dict = self.loss(rendered_rgb, rgb_gt, rendered_depth, gt_depth, **kwargs)
