@@ -228,7 +228,8 @@ def run_b200(args):
     _cabi.profile_flush()
     prof = {k: v[0] / prof_steps for k, v in _cabi.profile.items()}
     _cabi.profile = None
-    mlp_ms = prof.get("nnb_render_fwd", 0.0) + prof.get("nnb_render_bwd", 0.0)
+    fwd_ms_all = prof.get("nnb_render_fwd", 0.0) + prof.get("nnb_render_fwd_ex", 0.0)
+    mlp_ms = fwd_ms_all + prof.get("nnb_render_bwd", 0.0) + prof.get("nnb_render_bwd_ex", 0.0)
     pk, pk_kind = peaks()
     peak_tf = pk.get("bf16_tflops_sustained", pk.get("bf16_tflops"))
     achieved_tf = FLOP_PER_RAY_TRAIN * RAYS_PER_GPU / (mlp_ms * 1e-3) / 1e12 if mlp_ms > 0 else 0.0
@@ -239,7 +240,7 @@ def run_b200(args):
     if args.precision == "bf16" and split[0] > 0:
         hbm = pk.get("hbm_gbs", 6650.0)
         f_third = FLOP_PER_RAY_TRAIN / 3.0 * RAYS_PER_GPU
-        fwd_ms = prof.get("nnb_render_fwd", 0.0)
+        fwd_ms = fwd_ms_all
         wg_bytes = WGRAD_BYTES_PER_RAY * RAYS_PER_GPU
         kernels = [
             {"kernel": "tc_fwd_kernel<save>", "ms": fwd_ms, "bound": "tensor", "achieved": f_third / fwd_ms / 1e9, "peak": peak_tf,

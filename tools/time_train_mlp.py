@@ -37,5 +37,5 @@ for _ in range(iters):
 _cabi.profile_flush()
 prof = {k: v[0] / iters for k, v in _cabi.profile.items()}
 _cabi.profile = None
-tot = prof.get("nnb_render_fwd", 0) + prof.get("nnb_render_bwd", 0)
+tot = prof.get("nnb_render_fwd", 0) + prof.get("nnb_render_bwd", 0) + prof.get("nnb_render_bwd_ex", 0)
 print(json.dumps({"rays": R, "ms": prof, "mlp_ms": tot, "tflops": 455_737_344 * R / tot / 1e9}))
