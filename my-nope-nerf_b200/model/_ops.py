@@ -300,6 +300,7 @@ class RenderRays(torch.autograd.Function):
         ctx.cfg, ctx.packed, ctx.ws, ctx.nbytes = cfg, packed, ws, nbytes
         ctx.save_for_backward(origin, dirs, w, a, z, *params)
         ctx.mark_non_differentiable(z)
+        ctx.set_materialize_grads(False)   # unused outputs (weights, alpha) arrive as None in backward, not as zero fills
         return rgb, dist, w, a, z
 
     @staticmethod
@@ -346,6 +347,7 @@ class RenderRaysEx(torch.autograd.Function):
         ctx.cfg, ctx.packed, ctx.ws, ctx.nbytes = cfg, packed, ws, nbytes
         ctx.save_for_backward(ray_o, dirs, view, w, a, z, *params)
         ctx.mark_non_differentiable(z)
+        ctx.set_materialize_grads(False)   # unused outputs (weights, alpha) arrive as None in backward, not as zero fills
         return rgb, dist, w, a, z
 
     @staticmethod
