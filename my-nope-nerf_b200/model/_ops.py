@@ -251,6 +251,17 @@ def _extras(ray_o, view, d_ray_o=None, d_view=None, backward=False):
     return K.RayExtras(v(ray_o), v(view), v(d_ray_o), v(d_view), ws)
 
 
+def _release_ws(ctx, flat):
+    """Drop the saved-activation workspace of a render node after its backward was enqueued.  With the weight-gradient kernel
+    forked onto `wgrad_stream` that kernel still reads the workspace (and writes `flat`) after the launching stream has moved
+    on: tell the caching allocator, so that the blocks are not handed to a later allocation of the launching stream before
+    the fork is joined (inside a capture, blocks with a recorded stream use stay reserved until the capture ends)."""
+    if wgrad_stream is not None:
+        ctx.ws.record_stream(wgrad_stream)
+        flat.record_stream(wgrad_stream)
+    ctx.ws = None
+
+
 def render_nograd(cfg, params, packed, origin, dirs, noise, want_aux=True, ray_o=None, view=None):
     """Forward only (eval / render loops).  Returns rgb, dist, weights, alpha, z (aux None if not wanted).
     ray_o / view: per-ray origins and view directions of the NDC branch (nnb_ray_extras)."""
@@ -321,7 +332,7 @@ class RenderRays(torch.autograd.Function):
         ex = _extras(None, None, backward=True)
         call("nnb_render_bwd_ex", C.byref(cfg), parr, ptr(ctx.packed), ptr(origin), ptr(dirs), C.byref(ex), ptr(w), ptr(a), ptr(z),
              opt(g_rgb), opt(g_dist), opt(g_a), opt(g_w), garr, ptr(d_origin), ptr(d_dirs), ptr(ctx.ws), ctx.nbytes, stream())
-        ctx.ws = None
+        _release_ws(ctx, flat)
         return (None, None, d_origin, d_dirs, None) + tuple(grads)
 
 
@@ -369,7 +380,7 @@ class RenderRaysEx(torch.autograd.Function):
             return ptr(f32(g)) if g is not None else None
         call("nnb_render_bwd_ex", C.byref(cfg), parr, ptr(ctx.packed), ptr(ray_o), ptr(dirs), C.byref(ex), ptr(w), ptr(a), ptr(z),
              opt(g_rgb), opt(g_dist), opt(g_a), opt(g_w), garr, ptr(d_origin), ptr(d_dirs), ptr(ctx.ws), ctx.nbytes, stream())
-        ctx.ws = None
+        _release_ws(ctx, flat)
         return (None, None, d_ray_o, d_dirs, d_view, None) + tuple(grads)
 
 
@@ -686,10 +697,14 @@ def mlp_points_density_grad(params, pts, want_raw=False):
     return (grad, raw) if want_raw else grad
 
 
-def pack_weights(params):
-    """bf16 tile images of the 24 tensors for the tcgen05 path (refreshed whenever the fp32 masters change)."""
-    nbytes = int(K.lib().nnb_pack_weights_bytes())
-    packed = torch.empty(nbytes, dtype=torch.uint8, device=params[0].device)
+def alloc_packed(device):
+    return torch.empty(int(K.lib().nnb_pack_weights_bytes()), dtype=torch.uint8, device=device)
+
+
+def pack_weights(params, out=None):
+    """bf16 tile images of the 24 tensors for the tcgen05 path (refreshed whenever the fp32 masters change); `out`: an
+    `alloc_packed` buffer to re-pack in place."""
+    packed = out if out is not None else alloc_packed(params[0].device)
     parr = K.param_ptr_array([f32(p.detach()) for p in params])
     call("nnb_pack_weights", parr, ptr(packed), stream())
     return packed

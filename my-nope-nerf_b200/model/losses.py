@@ -4,7 +4,8 @@ forward() keeps the reference's signature, zero-weight skipping and its 10 retur
 kernel launch (rgb, depth l1 / invariant, Chamfer, reprojection photometric); the terms whose weights are [0,0] in
 every shipped config (pose smoothness, depth consistency, t-cycle, SSIM) stay plain PyTorch.
 Differences kept on purpose: tensors follow the inputs' device (no hard-coded .cuda()), and a NaN loss raises
-instead of dropping into a debugger (model/losses.py:213-214).
+FloatingPointError (Loss.raise_if_nan, called by the Trainer after every step, one step late so that the read never
+stalls the launch queue) instead of dropping into a debugger (model/losses.py:213-214).
 """
 import torch
 from torch import nn
@@ -26,7 +27,32 @@ class Loss(nn.Module):
         self.check_nan = True
         # data-parallel context (set by Trainer): the Chamfer SOURCE points are sharded across ranks
         self.dp = None
+        self._nan_pending, self._nan_step = None, 0
         self._weight_vectors = {}   # (weights of the active terms, device) -> device vector, built once per schedule phase
+
+    def raise_if_nan(self, loss_dict):
+        """model/losses.py:213-214 (`if torch.isnan(loss): breakpoint()`) without a host synchronisation on the step just
+        issued: the loss is copied to pinned host memory asynchronously and examined when the NEXT step has been queued."""
+        loss = loss_dict['loss']
+        if not loss.is_cuda:
+            if bool(torch.isnan(loss)):
+                raise FloatingPointError("NaN loss")
+            return
+        prev = self._nan_pending
+        host = prev[1] if prev is not None else torch.zeros(2, dtype=torch.float32).pin_memory()
+        slot = 0
+        if prev is not None:
+            ev, _, slot, step = prev
+            ev.synchronize()
+            if bool(torch.isnan(host[slot])):
+                self._nan_pending = None
+                raise FloatingPointError("NaN loss at step %d (model/losses.py:213)" % step)
+            slot ^= 1
+        host[slot:slot + 1].copy_(loss.detach().reshape(1), non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        self._nan_pending = (ev, host, slot, self._nan_step)
+        self._nan_step += 1
 
     # -- individual terms (reference method names) ----------------------------------------------
     def get_rgb_full_loss(self, rgb_values, rgb_gt, rgb_loss_type='l2'):
@@ -100,11 +126,36 @@ class Loss(nn.Module):
                 rgb_loss_type='l2', depth_mask=None, **kwargs):
         dev = rgb_gt.device
         zero = torch.zeros((), device=dev)
+        # Data parallelism: the rendered tensors are this rank's shard [lo, hi) of the global batch and the
+        # gradient allreduce AVERAGES over the G ranks, so every per-ray term is returned as G x (its share of the GLOBAL
+        # normaliser): the rank average of the values is the 1-GPU loss and the averaged gradient is the 1-GPU gradient,
+        # also for unequal shards and ragged masks.
+        dpi = kwargs.get('dp_info')
+        G = self.dp.world_size if (dpi is not None and self.dp is not None) else 1
         rgb3 = None
         if weights['rgb_weight'] != 0.0 or weights['depth_weight'] != 0.0:
-            rgb3 = _ops.RgbLoss.apply(rgb_pred, rgb_gt)
+            rgb3 = _ops.RgbLoss.apply(rgb_pred, rgb_gt)            # sums over the shard / shard size
+            if dpi is not None:
+                rgb3 = rgb3 * (float(G) * float(dpi['hi'] - dpi['lo']) / float(dpi['n_global']))
         rgb_full_loss = (rgb3[0] if rgb_loss_type == 'l1' else rgb3[1]) if weights['rgb_weight'] != 0.0 else zero
-        depth_loss = self.get_depth_loss(depth_pred, depth_gt, depth_mask) if weights['depth_weight'] != 0.0 else zero
+        if weights['depth_weight'] == 0.0:
+            depth_loss = zero
+        elif dpi is None:
+            depth_loss = self.get_depth_loss(depth_pred, depth_gt, depth_mask)
+        elif self.depth_loss_type == 'l1':
+            # model/losses.py:60-63 divides by the number of valid rays of the WHOLE batch (known on every rank: mask_global)
+            c_loc = depth_mask.sum().float() if depth_mask is not None else torch.tensor(float(depth_pred.numel()), device=dev)
+            c_glob = dpi['mask_global'].sum().float().clamp_min(1.0)
+            depth_loss = self.get_depth_loss(depth_pred, depth_gt, depth_mask) * (c_loc * float(G) / c_glob)
+        else:
+            # model/losses.py:35-58 takes the median and the mean absolute deviation of the WHOLE batch: all-gather the rendered
+            # depths (R x 4 B), evaluate the term redundantly on every rank, keep the gradient of this rank's rays only
+            from . import parallel
+            lo, hi = dpi['lo'], dpi['hi']
+            pred_all = parallel.AllGatherRows.apply(depth_pred, self.dp, dpi['n_global'])
+            g_all = dpi['depth_gt_global']
+            gt_all = torch.cat([g_all[:lo].detach(), depth_gt, g_all[hi:].detach()])
+            depth_loss = self.get_depth_loss(pred_all, gt_all, dpi['mask_global']) * float(G)
         if weights['weight_dist_2nd_loss'] != 0.0 or weights['weight_dist_1st_loss'] != 0.0:
             loss_dist_1st, loss_dist_2nd = self.get_weight_dist_loss(t_list)
         else:

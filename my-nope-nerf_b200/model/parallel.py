@@ -10,6 +10,8 @@ import torch.distributed as dist
 class DataParallelContext(object):
     def __init__(self, rank=0, world_size=1, group=None):
         self.rank, self.world_size, self.group = rank, world_size, group
+        self.timing = None
+        self.bytes_per_allreduce = 0
 
     @classmethod
     def from_env(cls):
@@ -21,18 +23,31 @@ class DataParallelContext(object):
         """Contiguous [lo, hi) slice of n units for this rank (first n % world ranks take one extra)."""
         return shard_range(n, self.rank, self.world_size)
 
-    def allreduce_grads(self, params):
-        """Average the gradients of `params` across ranks with one collective over a flat fp32 buffer.
-        Parameters whose grad is None on this rank contribute zeros (every rank must pass the same list)."""
+    def allreduce_grads(self, params, extra=()):
+        """Average the gradients of `params` across ranks with ONE collective over a flat fp32 buffer.  Parameters whose grad
+        is None on this rank contribute zeros (every rank must pass the same list).  `extra`: scalar tensors (the loss terms of
+        the step) averaged in place by the same collective.  `self.timing` = [] collects CUDA-event pairs around the call."""
         if self.world_size == 1:
             return
         params = [p for p in params if p.requires_grad]
         if not params:
             return
-        flat = flatten_grads(params)
-        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)
-        flat.div_(self.world_size)
-        unflatten_grads(flat, params)
+        ev = None
+        if self.timing is not None and torch.cuda.is_available():
+            ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+            ev[0].record()
+        extra = [e for e in extra if torch.is_tensor(e)]
+        flat = flatten_grads(params, extra)
+        if dist.get_backend(self.group) == 'nccl':
+            dist.all_reduce(flat, op=dist.ReduceOp.AVG, group=self.group)     # the average is taken inside the collective
+        else:
+            dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)
+            flat.div_(self.world_size)
+        unflatten_grads(flat, params, extra)
+        if ev is not None:
+            ev[1].record()
+            self.timing.append(ev)
+            self.bytes_per_allreduce = flat.numel() * 4
 
     def gather_rows(self, local, n_total):
         """All ranks' row shards (in rank order) concatenated on every rank: render bands -> full frame."""
@@ -53,12 +68,14 @@ def shard_range(n, rank, world_size):
     return lo, lo + base + (1 if rank < rem else 0)
 
 
-def flatten_grads(params):
-    """One fp32 buffer holding every gradient (zeros where a parameter has no gradient on this rank): one `cat` launch."""
-    return torch.cat([(p.grad if p.grad is not None else torch.zeros_like(p)).reshape(-1).float() for p in params])
+def flatten_grads(params, extra=()):
+    """One fp32 buffer holding every gradient (zeros where a parameter has no gradient on this rank) followed by the `extra`
+    scalars: one `cat` launch."""
+    return torch.cat([(p.grad if p.grad is not None else torch.zeros_like(p)).reshape(-1).float() for p in params]
+                     + [e.detach().reshape(-1).float() for e in extra])
 
 
-def unflatten_grads(flat, params):
+def unflatten_grads(flat, params, extra=()):
     views, o = [], 0
     for p in params:
         n = p.numel()
@@ -67,7 +84,30 @@ def unflatten_grads(flat, params):
     missing = [i for i, p in enumerate(params) if p.grad is None]
     for i in missing:
         params[i].grad = torch.empty_like(params[i])
-    torch._foreach_copy_([p.grad for p in params], views)
+    dst = [p.grad for p in params]
+    for e in extra:
+        n = e.numel()
+        views.append(flat[o:o + n].view_as(e))
+        dst.append(e.detach())
+        o += n
+    with torch.no_grad():
+        torch._foreach_copy_(dst, views)
+
+
+class AllGatherRows(torch.autograd.Function):
+    """Every rank's shard of a 1-D tensor concatenated in rank order (shards as DataParallelContext.shard cuts them).  The
+    caller evaluates the same function of the gathered tensor on every rank and scales it by the world size, so the backward
+    is the slice of the incoming gradient that belongs to this rank's shard: no collective in the backward pass."""
+
+    @staticmethod
+    def forward(ctx, local, dp, n_total):
+        ctx.range = dp.shard(n_total)
+        return dp.gather_rows(local.detach().contiguous(), n_total)
+
+    @staticmethod
+    def backward(ctx, g):
+        lo, hi = ctx.range
+        return g[lo:hi].contiguous(), None, None
 
 
 def init_from_env(backend=None):

@@ -28,13 +28,14 @@ class Renderer(nn.Module):
         self.precision = kwargs.get('precision', cfg.get('precision', 'fp32'))
         self._packed = None
         self._packed_version = None
+        self._pack_event = None
 
     # -- reference API -------------------------------------------------------------------------
     def forward(self, pixels, depth, camera_mat, world_mat, scale_mat, rendering_technique, add_noise=True,
-                eval_=False, it=1000000, noise=None, lazy_mask=False):
+                eval_=False, it=1000000, noise=None, lazy_mask=False, shard=None):
         if rendering_technique == 'nope_nerf':
             return self.nope_nerf(pixels, depth, camera_mat, world_mat, scale_mat, it=it, add_noise=add_noise,
-                                  eval_=eval_, noise=noise, lazy_mask=lazy_mask)
+                                  eval_=eval_, noise=noise, lazy_mask=lazy_mask, shard=shard)
         if rendering_technique == 'phong_renderer':
             return self.phong_renderer(pixels, camera_mat, world_mat, scale_mat, it=it)
         raise ValueError("unknown rendering technique %r" % (rendering_technique,))
@@ -70,16 +71,57 @@ class Renderer(nn.Module):
                              c['use_ray_dir'], self._prec())
 
     def _packed_weights(self, params):
+        """bf16 stage images of the 24 fp32 masters, in ONE persistent buffer that is re-packed in place: its address is
+        baked into captured graphs, so it must never be reallocated.  Eagerly the pack runs when a master changed (version
+        counters); while a CUDA graph is being captured it ALWAYS runs, so that it becomes a node of the graph and every replay
+        reads the masters the optimiser has just updated (a version check at capture time would freeze the capture-time images
+        into every replay)."""
         if self._prec() != _cabi.PREC_BF16:
             return None
+        dev = params[0].device
+        if self._packed is None or self._packed.device != dev:
+            self._packed = _ops.alloc_packed(dev)
+            self._packed_version = None
+        if self._pack_event is not None:          # begin_pack() already issued this step's pack on a side stream
+            torch.cuda.current_stream().wait_event(self._pack_event)
+            self._pack_event = None
+            return self._packed
+        capturing = torch.cuda.is_current_stream_capturing()
         version = tuple(p._version for p in params) + tuple(p.data_ptr() for p in params)
-        if self._packed is None or self._packed_version != version:
-            self._packed = _ops.pack_weights(params)
-            self._packed_version = version
+        if capturing or self._packed_version != version:
+            _ops.pack_weights(params, out=self._packed)
+            self._packed_version = None if capturing else version
         return self._packed
 
+    def join_pack(self):
+        """Join a pack that no render consumed (a step whose rgb / depth weights are both zero)."""
+        if self._pack_event is not None:
+            torch.cuda.current_stream().wait_event(self._pack_event)
+            self._pack_event = None
+
+    def begin_pack(self, stream):
+        """Issue this step's weight pack on `stream` (forked from the current stream), off the critical path of the pose /
+        ray-generation chain; the next `_packed_weights` call makes the render stream wait for it."""
+        if self._prec() != _cabi.PREC_BF16:
+            return
+        params = self.model.param_list()
+        if self._packed is None or self._packed.device != params[0].device:
+            self._packed = _ops.alloc_packed(params[0].device)
+        cur = torch.cuda.current_stream()
+        stream.wait_stream(cur)
+        with torch.cuda.stream(stream):
+            _ops.pack_weights(params, out=self._packed)
+            ev = torch.cuda.Event()
+            ev.record(stream)
+        self._packed_version = None
+        self._pack_event = ev
+
     def nope_nerf(self, pixels, depth, camera_mat, world_mat, scale_mat, add_noise=False, it=100000, eval_=False,
-                  noise=None, lazy_mask=False):
+                  noise=None, lazy_mask=False, shard=None):
+        """shard = (lo, hi): data parallelism.  `pixels` / `depth` / `noise` hold the GLOBAL ray batch; ray
+        generation (33 B/ray) runs on all of it on every rank, so that the validity mask and the depth targets of the whole
+        batch are known everywhere without a collective, and only rays [lo, hi) go through the fused render.  The returned
+        per-ray tensors are the shard's; `mask_global` / `depth_gt_global` cover the whole batch."""
         cfg = self.cfg
         ndc = cfg['sample_option'] == 'ndc'
         if cfg['sample_option'] not in ('uniform', 'ndc'):
@@ -90,6 +132,13 @@ class Renderer(nn.Module):
         S = cfg['num_points'] - cfg['outside_steps']
         origin, dirs, nrm, d_gt, mask = _ops.RayGen.apply(pixels, depth, camera_mat, world_mat, scale_mat,
                                                           cfg['normalise_ray'])
+        d_gt_global, mask_global = d_gt, mask
+        if shard is not None:
+            lo, hi = shard
+            dirs, nrm, d_gt, mask = dirs[lo:hi], nrm[lo:hi], d_gt[lo:hi], mask[lo:hi]
+            if noise is not None:
+                noise = noise.reshape(n_points, S)[lo:hi]
+            n_points = hi - lo
         ray_o = view = None
         dr = None
         dirs_world = dirs
@@ -158,4 +207,5 @@ class Renderer(nn.Module):
             'rgb': rgb.reshape(batch_size, -1, 3), 'z_vals': z, 'normal': diff_norm,
             'depth_pred': depth_pred, 'depth_gt': depth_gt, 'alpha': alpha,
             'depth_pred_dense': dist, 'depth_gt_dense': d_gt, 'mask': mask, 'weights': w,
+            'depth_gt_global': d_gt_global, 'mask_global': mask_global,
         }

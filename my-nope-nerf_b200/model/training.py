@@ -9,6 +9,7 @@ global ray batch and takes its contiguous shard; gradients are averaged with ONE
 """
 import contextlib
 import logging
+import os
 
 import torch
 
@@ -59,9 +60,37 @@ class Trainer(object):
         # test hooks: inject the ray choice / jitter instead of drawing them (parity tests)
         self.fixed_ray_idx = None
         self.fixed_noise = None
+        # 'auto' (default; env NNB_GRAPH=0/1 overrides): `train_step`, the call train.py:213 makes, replays the step as a CUDA
+        # graph whenever the batch allows it (see _graph_ok); False: always launch kernel by kernel; True: always graph
+        env = os.environ.get('NNB_GRAPH', 'auto')
+        self.use_graph = {'0': False, '1': True}.get(env, 'auto')
+        # 'feistel' (nnb_ray_choice, no sort) or 'reference' (torch.randperm(h*w)[:n], the draw of model/training.py:277 with
+        # the same consumption of the device generator); cfg key `ray_choice`, env NNB_RAY_CHOICE
+        self.ray_choice = cfg.get('ray_choice', os.environ.get('NNB_RAY_CHOICE', 'feistel'))
+        if self.ray_choice not in ('feistel', 'reference'):
+            raise ValueError("ray_choice must be 'feistel' or 'reference' (got %r)" % (self.ray_choice,))
 
     # -- reference API -------------------------------------------------------------------------
     def train_step(self, data, it=None, epoch=None, scheduling_start=None, render_path=None):
+        """model/training.py:70-100.  Same signature and return value; on a CUDA device the step is replayed as a CUDA graph
+        (train_step_graphed) when the batch qualifies, else launched kernel by kernel (train_step_eager).  Both run the same
+        kernels; tests/test_gpu_step.py checks that they produce the same losses and parameters."""
+        if self._graph_ok(data):
+            return self.train_step_graphed(data, it=it, epoch=epoch, scheduling_start=scheduling_start)
+        return self.train_step_eager(data, it=it, epoch=epoch, scheduling_start=scheduling_start, render_path=render_path)
+
+    def _graph_ok(self, data):
+        if self.use_graph is False:
+            return False
+        if self.use_graph is True:
+            return True
+        dev = torch.device(self.device) if self.device is not None else None
+        return (dev is not None and dev.type == 'cuda' and self.pose_param_net is not None
+                and self.fixed_ray_idx is None and self.fixed_noise is None
+                and data.get('img.dpt') is not None       # sparse depth: the resample loop of model/training.py:279-284 reads the mask on the host
+                and _cabi.profile is None)                # per-entry-point timing (bench.py) needs eager launches
+
+    def train_step_eager(self, data, it=None, epoch=None, scheduling_start=None, render_path=None):
         self.model.train()
         self.optimizer.zero_grad()
         if self.pose_param_net:
@@ -78,7 +107,7 @@ class Trainer(object):
         loss_dict['loss'].backward()
         if self.dp.world_size > 1:
             nets = [self.model, self.pose_param_net, self.distortion_net, self.focal_net]
-            self.dp.allreduce_grads([p for n in nets if n is not None for p in n.parameters()])
+            self.dp.allreduce_grads([p for n in nets if n is not None for p in n.parameters()], extra=self._loss_scalars(loss_dict))
         self.optimizer.step()
         if self.optimizer_pose:
             self.optimizer_pose.step()
@@ -86,6 +115,8 @@ class Trainer(object):
             self.optimizer_focal.step()
         if self.optimizer_distortion:
             self.optimizer_distortion.step()
+        if self.loss.check_nan:
+            self.loss.raise_if_nan(loss_dict)
         return loss_dict
 
     # -- the same step as a CUDA graph -----------------------------------------
@@ -127,9 +158,13 @@ class Trainer(object):
         static['img.idx'], static['img.ref_idxs'] = data.get('img.idx'), data.get('img.ref_idxs')
         slot['graph'].replay()
         self.graphed_launches = getattr(self, 'graphed_launches', 0) + slot['n_launches']
+        for p in slot['no_grad']:
+            p.grad = None       # a parameter this graph variant gives no gradient must not carry one from another variant
         for p, g in slot['grads']:
             p.grad = g
-        self._optimizer_tail()
+        self._optimizer_tail(slot['loss_dict'])
+        if self.loss.check_nan:
+            self.loss.raise_if_nan(slot['loss_dict'])
         return slot['loss_dict']
 
     # keys of the batch schema the training step reads (process_data_dict / process_data_reference); the DataLoader also yields
@@ -152,9 +187,24 @@ class Trainer(object):
     def _all_nets(self):
         return [m for m in (self.model, self.pose_param_net, self.distortion_net, self.focal_net) if m is not None]
 
-    def _optimizer_tail(self):
+    LOSS_KEYS = ('loss', 'loss_rgb', 'loss_depth', 'l2_mean', 'loss_dist_1st', 'loss_dist_2nd', 'loss_pc', 'loss_rgb_s',
+                 'loss_depth_consistency', 'loss_t_cycle')
+
+    def _loss_scalars(self, loss_dict):
+        """The loss terms the gradient allreduce averages along with the gradients: a rank's per-ray terms are G x its share
+        of the global normaliser (Loss.forward), so their rank average is the 1-GPU value.  Distinct storages only."""
+        seen, out = set(), []
+        for k in self.LOSS_KEYS:
+            v = loss_dict.get(k)
+            if torch.is_tensor(v) and v.numel() == 1 and v.data_ptr() not in seen:
+                seen.add(v.data_ptr())
+                out.append(v)
+        return out
+
+    def _optimizer_tail(self, loss_dict=None):
         if self.dp.world_size > 1:
-            self.dp.allreduce_grads([p for m in self._all_nets() for p in m.parameters()])
+            self.dp.allreduce_grads([p for m in self._all_nets() for p in m.parameters()],
+                                    extra=self._loss_scalars(loss_dict) if loss_dict is not None else ())
         for opt in (self.optimizer, self.optimizer_pose, self.optimizer_focal, self.optimizer_distortion):
             if opt:
                 opt.step()
@@ -176,14 +226,22 @@ class Trainer(object):
         # 192 threads), so the ray-generation / pose backward chain that follows the data-gradient kernel runs beside it
         wgrad = torch.cuda.Stream() if (self.fork_wgrad and self.model.renderer.precision == 'bf16') else None
 
+        renderer = self.model.renderer
+        pack = torch.cuda.Stream() if renderer.precision == 'bf16' else None
+
         def body():
             for p in params:
                 p.grad = None
             self._geom_stream = geom
             _ops.wgrad_stream, _ops.wgrad_forked = wgrad, False
             try:
+                if pack is not None:
+                    # the bf16 weight images are re-packed from the fp32 masters INSIDE the graph (every replay follows an
+                    # optimiser step), on a side stream beside the pose / ray-generation chain
+                    renderer.begin_pack(pack)
                 ld = self.compute_loss(static, it=it, epoch=epoch, scheduling_start=scheduling_start)
                 ld['loss'].backward()
+                renderer.join_pack()                                # no-op when the render consumed the pack
                 if geom is not None:
                     torch.cuda.current_stream().wait_stream(geom)   # nothing of the branch is left unjoined when capture ends
                 if wgrad is not None and _ops.wgrad_forked:
@@ -211,7 +269,8 @@ class Trainer(object):
         with torch.cuda.graph(graph):
             loss_dict = body()
         return {'graph': graph, 'static': static, 'loss_dict': loss_dict, 'n_launches': _cabi.kernel_launches() - l0,
-                'grads': [(p, p.grad) for p in params if p.grad is not None]}
+                'grads': [(p, p.grad) for p in params if p.grad is not None],
+                'no_grad': [p for p in params if p.grad is None]}
 
     def process_data_dict(self, data):
         device = self.device
@@ -355,44 +414,65 @@ class Trainer(object):
                     if weights['rgb_s_weight'] != 0.0:
                         kwargs['rgb_s_loss_pre'] = self.loss.get_rgb_s_loss(kwargs['rgb_pc1'], kwargs['rgb_pc1_proj'], kwargs['valid_points'])
 
-        # ray choice: same draw as the reference (model/training.py:277); ranks draw the SAME global batch
+        # Ray choice (model/training.py:277); ranks draw the SAME global batch.  'reference': the reference's own call,
+        # torch.randperm(h*w, device)[:n] on the device generator, followed by its torch.rand(1, R, S) (model/rendering.py:190):
+        # a seeded run visits the reference's rays and jitter (tests/test_gpu_step.py::test_seeded_draws_match_reference_calls).
+        # 'feistel' (default): head of a keyed pseudo-random permutation, no sort of h*w keys (240 us at 375 x 1242); it
+        # consumes the generator differently (six randint keys), so seeds are NOT reference-compatible in that mode.
+        def draw():
+            if self.ray_choice == 'reference':
+                return torch.randperm(h * w, device=device)[:n_points]
+            return _ops.ray_choice(h * w, min(n_points, h * w), device)
         if self.fixed_ray_idx is not None:
             ray_idx = self.fixed_ray_idx.to(device)
         else:
-            ray_idx = _ops.ray_choice(h * w, min(n_points, h * w), device)
+            ray_idx = draw()
             if data.get('img.dpt') is None:
                 depth_mask_flat = torch.flatten(depth_mask)
                 while not depth_mask_flat[ray_idx].any():
                     print('No valid depths found, resampling...')
-                    ray_idx = _ops.ray_choice(h * w, min(n_points, h * w), device)
+                    ray_idx = draw()
         n_global = ray_idx.numel()
         lo, hi = self.dp.shard(n_global)
-        ray_idx_local = ray_idx[lo:hi].contiguous()
+        sharded = self.dp.world_size > 1
+        shard = (lo, hi) if sharded else None
 
-        # fused gather: pixels, rgb_gt and depth*scale+shift for the selected rays only
-        pixels, rgb_gt, depth_sel = _ops.GatherRays.apply(ray_idx_local, img[0], depth_raw[0, 0], ss_in, h, w)
-        rgb_gt = rgb_gt.unsqueeze(0)
+        if (h_depth, w_depth) != (h, w):
+            # model/network.py:21-24 resamples the depth map to the image size (F.interpolate, mode 'area') before the gather
+            depth_raw = torch.nn.functional.interpolate(depth_raw, (h, w), mode='area')
+        # fused gather: pixels, rgb_gt and depth*scale+shift for the selected rays only.  Data parallel: stage 1 (33 B/ray)
+        # covers the GLOBAL batch on every rank -- the validity mask of the whole batch is then known without a collective --
+        # and only this rank's rays [lo, hi) are rendered (Renderer.nope_nerf `shard`).
+        pixels, rgb_gt, depth_sel = _ops.GatherRays.apply(ray_idx.contiguous(), img[0], depth_raw[0, 0], ss_in, h, w)
+        rgb_gt = (rgb_gt[lo:hi] if sharded else rgb_gt).unsqueeze(0)
 
         out_dict = None
         if render_model:
             renderer = self.model.renderer
             S = renderer.cfg['num_points'] - renderer.cfg['outside_steps']
             if self.fixed_noise is not None:
-                noise = self.fixed_noise.to(device).reshape(n_global, S)[lo:hi]
+                noise = self.fixed_noise.to(device).reshape(n_global, S)
             elif not eval_mode:
                 # the reference draws (1, R, S) inside the renderer (model/rendering.py:190)
-                noise = torch.rand(1, n_global, S, device=device).reshape(n_global, S)[lo:hi]
+                noise = torch.rand(1, n_global, S, device=device).reshape(n_global, S)
             else:
                 noise = None
+            self._last_draw = (ray_idx, noise)    # references only (parity tests read them)
             out_dict = renderer(pixels.unsqueeze(0), depth_sel.reshape(1, -1, 1), camera_mat, world_mat, scale_mat,
                                 self.rendering_technique, add_noise=noise is not None, eval_=eval_mode, it=it, noise=noise,
-                                lazy_mask=True)
+                                lazy_mask=True, shard=shard)
             rendered_rgb = out_dict['rgb']
             rendered_depth = out_dict['depth_pred_dense']
             gt_depth = out_dict['depth_gt_dense']
             kwargs['depth_mask'] = out_dict['mask']
+            if sharded:
+                gt_all = out_dict['depth_gt_global']
+                kwargs['dp_info'] = {'lo': lo, 'hi': hi, 'n_global': n_global, 'mask_global': out_dict['mask_global'],
+                                     'depth_gt_global': gt_all.detach() if self.detach_gt_depth else gt_all}
         else:
             rendered_rgb = rendered_depth = gt_depth = None
+            if sharded:
+                kwargs['dp_info'] = {'lo': lo, 'hi': hi, 'n_global': n_global}
 
         if geom is not None:
             kwargs['join_pre'] = lambda: main_stream.wait_stream(geom)   # Loss.forward joins the branch where it first needs it

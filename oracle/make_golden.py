@@ -319,8 +319,125 @@ def geometry_vectors(ref, cfg):
     return out
 
 
+def cfg2_scene_setup():
+    """Inputs of the BASELINE.json cfg2 golden case: shared by this generator and tests/test_gpu_cfg2.py."""
+    scene = syn.make_scene("cfg2")
+    n = scene["n"]
+    r0, t0 = syn.init_pose_params(n)
+    scales = 1.0 + 0.01 * torch.arange(n, dtype=torch.float32).view(n, 1)
+    shifts = 0.005 * torch.arange(n, dtype=torch.float32).view(n, 1)
+    R = syn.SHAPES["cfg2"][3]
+    return scene, r0, t0, scales, shifts, syn.ray_choice(scene["h"], scene["w"], R), syn.jitter(R, 128)
+
+
+def _opt_clone(t):
+    return t.clone() if t is not None else None
+
+
+def cfg2_vectors(ref, cfg):
+    """BASELINE.json cfg2 at full size through the UNMODIFIED reference Trainer.compute_loss + backward: 20-frame 375 x 1242
+    scene, 4,096 injected rays x 128 samples, full loss set (rgb L1, depth l1 with learned scale/shift, Chamfer on 28,830-point
+    clouds, reprojection), LearnPose.  ~25 GB and several minutes on the host."""
+    import time
+    scene, r0, t0, scales, shifts, ray_idx, noise = cfg2_scene_setup()
+    n, h, w, R = scene["n"], scene["h"], scene["w"], ray_idx.numel()
+    sd = syn.init_mlp_state(42)
+    out = {"torch_version": torch.__version__, "cases": {}}
+    for name, c in {"mid": dict(idx=5, ref=6), "last": dict(idx=n - 1, ref=n - 2)}.items():
+        tcfg = dict(cfg["training"], n_training_points=R)
+        nerf, renderer, net = build_ref_model(ref, cfg, sd)
+        pose_net = ref.model.LearnPose(n, True, True, cfg, init_c2w=scene["poses_gt"].clone())
+        dist_net = ref.model.Learn_Distortion(n, True, True, cfg)
+        with torch.no_grad():
+            pose_net.r.copy_(r0)
+            pose_net.t.copy_(t0)
+            dist_net.global_scales.copy_(scales)
+            dist_net.global_shifts.copy_(shifts)
+        trainer = ref.model.Trainer(net, None, tcfg, device=torch.device("cpu"), pose_param_net=pose_net, distortion_net=dist_net)
+        # record what the unmodified loss functions see and return (the wrappers call the originals)
+        seen = {}
+        o_idx, o_pc = trainer.loss.comp_closest_pts_idx_with_split, trainer.loss.get_pc_loss
+
+        def idx_rec(a, b, _o=o_idx):
+            r = _o(a, b)
+            seen.setdefault("nn_idx", []).append(r.to(torch.int32).clone())
+            return r
+
+        def pc_rec(X, Y, _o=o_pc):
+            seen["X"], seen["Y"] = X.detach().clone(), Y.detach().clone()
+            return _o(X, Y)
+
+        trainer.loss.comp_closest_pts_idx_with_split, trainer.loss.get_pc_loss = idx_rec, pc_rec
+        o_model_fwd = net.forward
+
+        def net_rec(*a, _o=o_model_fwd, **k):
+            r = _o(*a, **k)
+            seen["rgb"], seen["depth_pred"], seen["depth_gt"] = r["rgb"].detach().clone(), r["depth_pred"].detach().clone(), r["depth_gt"].detach().clone()
+            return r
+
+        net.forward = net_rec
+        batch = syn.make_batch(scene, c["idx"], c["ref"])
+        t0_ = time.time()
+        with injected_draws(noise=noise, perm=torch.cat([ray_idx, torch.zeros(h * w - R, dtype=torch.long)])):
+            ld = trainer.compute_loss(batch, it=1, epoch=0, scheduling_start=tcfg["scheduling_start"], out_render_path="/tmp")
+        ld["loss"].backward()
+        small = ("fc_density.weight", "fc_density.bias", "fc_rgb.weight", "fc_rgb.bias", "rgb_layers.0.bias", "layers0.0.weight",
+                 "layers1.6.bias")
+        out["cases"][name] = {
+            "case": c, "loss_dict": {k: v.detach().clone().reshape(-1) for k, v in ld.items()},
+            "grad_r": pose_net.r.grad.clone(), "grad_t": pose_net.t.grad.clone(),
+            "grad_scales": _opt_clone(dist_net.global_scales.grad), "grad_shifts": _opt_clone(dist_net.global_shifts.grad),
+            "mlp_grad_stats": {k: flat_stats(v.grad) for k, v in nerf.named_parameters()},
+            "mlp_grads": {k: v.grad.clone() for k, v in nerf.named_parameters() if k in small},
+            "X": seen["X"][0].clone(), "Y": seen["Y"][0].clone(), "nn_idx_xy": seen["nn_idx"][0], "nn_idx_yx": seen["nn_idx"][1],
+            "rgb": seen["rgb"], "depth_pred": seen["depth_pred"], "depth_gt": seen["depth_gt"],
+        }
+        print("cfg2", name, "%.0f s" % (time.time() - t0_), {k: float(v.reshape(-1)[0]) for k, v in ld.items()}, flush=True)
+    out["setup"] = {"ray_idx_checksum": int(ray_idx.sum()), "noise_checksum": float(noise.double().sum()), "scales": scales, "shifts": shifts}
+    return out
+
+
+def cfg5_clouds():
+    """BASELINE.json cfg5: (i) two 100,000-point clouds back-projected from a 250 x 400 depth crop in raster
+    order, the second moved by a small rigid offset; (ii) two clouds drawn from U(-1,1)^3 (seeds 7 / 8)."""
+    g = torch.Generator().manual_seed(7)
+    hh, ww = 250, 400
+    v, u = torch.meshgrid(torch.linspace(-0.75, 0.75, hh), torch.linspace(-1, 1, ww), indexing="ij")
+    zz = 2.0 + 0.3 * torch.sin(3 * u) * torch.cos(2 * v)
+    a = torch.stack([u * zz, v * zz, -zz], -1).reshape(-1, 3).contiguous()
+    b = (a + torch.tensor([0.013, -0.007, 0.02]) + 1e-3 * torch.randn(a.shape, generator=g)).contiguous()
+    ra = torch.rand(100000, 3, generator=torch.Generator().manual_seed(7)) * 2 - 1
+    rb = torch.rand(100000, 3, generator=torch.Generator().manual_seed(8)) * 2 - 1
+    return {"raster": (a, b), "random": (ra, rb)}
+
+
+CFG5_SLICES = (0, 33333, 66666, 98976)   # starts of the four 1,024-source slices
+
+
+def cfg5_vectors(ref, cfg):
+    """Nearest-neighbour indices of the reference's comp_closest_pts_idx_with_split (model/losses.py:129-144) at 100,000 x
+    100,000, evaluated on 1,024-source slices (the function's own kind of split; 1.2 GB per slice)."""
+    L = ref.losses.Loss(cfg["training"])
+    out = {"torch_version": torch.__version__, "slices": CFG5_SLICES, "slice_len": 1024}
+    for name, (a, b) in cfg5_clouds().items():
+        rec = {}
+        for s0 in CFG5_SLICES:
+            rec[s0] = L.comp_closest_pts_idx_with_split(a[s0:s0 + 1024].t().contiguous(), b.t().contiguous()).to(torch.int32)
+        out[name] = rec
+        print("cfg5", name, [int(v.sum()) for v in rec.values()], flush=True)
+    return out
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
+    if "--cfg2" in sys.argv or "--cfg5" in sys.argv:
+        ref = ref_harness.load_reference()
+        torch.set_num_threads(max(1, os.cpu_count() or 1))
+        if "--cfg5" in sys.argv:
+            torch.save(cfg5_vectors(ref, syn.default_cfg()), os.path.join(OUT, "cfg5_chamfer.pt"))
+        if "--cfg2" in sys.argv:
+            torch.save(cfg2_vectors(ref, syn.default_cfg()), os.path.join(OUT, "cfg2_step.pt"))
+        return
     if "--extra-step-cases" in sys.argv:
         # adds the later step cases to render_step.pt, leaving every existing entry byte-identical
         os.environ["NNB_GOLDEN_EXTRA_CASES"] = "1"
