@@ -1,6 +1,8 @@
 """CheckpointIO -- same on-disk format as the reference's model/checkpoints.py: torch.save of
 {module_name: state_dict, **scalars}; strict load_state_dict, so files are interchangeable with the reference."""
+import datetime
 import os
+import shutil
 
 import torch
 
@@ -30,8 +32,9 @@ class CheckpointIO(object):
             backup_dir = os.path.join(self.checkpoint_dir, 'backup_model_best')
             if not os.path.exists(backup_dir):
                 os.makedirs(backup_dir)
-            ts = len(os.listdir(backup_dir))
-            os.replace(filename, os.path.join(backup_dir, '%s_%d.pt' % (os.path.basename(filename)[:-3], ts)))
+            # a COPY under a timestamp name (model/checkpoints.py:43-53): model_best.pt itself stays in place
+            ts = datetime.datetime.now().timestamp()
+            shutil.copy(filename, os.path.join(backup_dir, '%s.pt' % ts))
 
     def load(self, filename, device=None, load_model_only=False):
         if not os.path.isabs(filename):
@@ -42,9 +45,13 @@ class CheckpointIO(object):
         return self.parse_state_dict(state_dict, load_model_only)
 
     def parse_state_dict(self, state_dict, load_model_only=False):
+        if load_model_only:
+            # model/checkpoints.py:82-84: only the 'model' entry survives, so no scalars (epoch_it, it, ...) are returned and
+            # the caller restarts its schedule
+            state_dict = {'model': state_dict['model']}
         for k, v in self.module_dict.items():
             if k in state_dict:
-                if load_model_only and k != 'model':
-                    continue
                 v.load_state_dict(state_dict[k])
+            else:
+                print('Warning: Could not find %s in checkpoint!' % k)
         return {k: v for k, v in state_dict.items() if k not in self.module_dict}

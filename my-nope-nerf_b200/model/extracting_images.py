@@ -1,6 +1,9 @@
 """Extract_Images -- the full-frame novel-view render loop of the reference's model/extracting_images.py:54-76.
-Pixel rows can be sharded across ranks (parallel.DataParallelContext); file output (PNG/NPY/MP4) stays with the
-caller -- it is host I/O outside the hot path."""
+Pixel rows can be sharded across ranks (parallel.DataParallelContext); `generate_images` returns and writes what the
+reference's does (img / depth / disp / geo), the MP4 assembly stays in vis/render.py."""
+import os
+
+import numpy as np
 import torch
 
 from . import _ops, parallel
@@ -48,8 +51,10 @@ class Extract_Images(object):
         return rgb.view(h, w, 3), depth.view(h, w)
 
     def generate_images(self, data, render_dir, c2ws, fxfy, it, output_geo):
-        """Reference signature (model/extracting_images.py:40).  Returns {'img': uint8 (h,w,3), 'depth': fp32 (h,w)} as
-        numpy arrays; writing them to `render_dir` is the caller's job."""
+        """Reference signature and outputs (model/extracting_images.py:40-131): renders frame `img.idx`, writes
+        depth_out/<idx>.npy and the img / depth / disparity (/ geo) PNGs under `render_dir`, and returns
+        {'img': uint8 (h,w,3), 'depth': uint8 (h,w) min-max normalised, 'geo': uint8 (h,w,3) or None, 'disp': uint8 (h,w,3)
+        inferno-mapped 1/depth} -- the four arrays vis/render.py:106-109 stacks into videos."""
         self.renderer.eval()
         (camera_mat, scale_mat, img_idx) = self.process_data_dict(data)
         img_idx = int(img_idx)
@@ -59,4 +64,51 @@ class Extract_Images(object):
                                       device=self.device)
         h, w = self.resolution
         rgb, depth = self.render_frame(camera_mat, world_mat, scale_mat, h, w, it=it)
-        return {'img': (rgb * 255).to(torch.uint8).cpu().numpy(), 'depth': depth.cpu().numpy()}
+        img_out = (rgb * 255).to(torch.uint8).cpu().numpy()
+        depth_raw = depth.cpu().numpy()
+
+        geo_out = None
+        if output_geo:
+            # model/extracting_images.py:79-98: the phong-shaded sphere-traced surface, 1,024 pixels per call
+            _, pixels = _ops.pixel_grid(h, w, self.device)
+            with torch.no_grad():
+                parts = [self.renderer(pixels[a:a + 1024].unsqueeze(0), None, camera_mat, world_mat, scale_mat, 'phong_renderer',
+                                       eval_=True, it=it, add_noise=False)['rgb'] for a in range(0, h * w, 1024)]
+            geo_out = (torch.cat(parts, dim=1).reshape(h, w, 3) * 255).to(torch.uint8).cpu().numpy()
+
+        disp = 1 / depth_raw
+        depth_out = np.clip(255.0 / depth_raw.max() * (depth_raw - depth_raw.min()), 0, 255).astype(np.uint8)
+        disp_u8 = np.clip(255.0 / disp.max() * (disp - disp.min()), 0, 255).astype(np.uint8)
+        disp_out = _inferno(disp_u8)
+        if render_dir is not None and self.dp.rank == 0:
+            name = str(img_idx).zfill(4) + '.png'
+            dirs = {k: os.path.join(render_dir, k) for k in ('img_out', 'depth_out', 'disp_out', 'geo_out')}
+            for k, d in dirs.items():
+                if k != 'geo_out' or output_geo:
+                    os.makedirs(d, exist_ok=True)
+            np.save(os.path.join(dirs['depth_out'], '{}.npy'.format(img_idx)), depth_raw)
+            _imwrite(os.path.join(dirs['img_out'], name), img_out)
+            _imwrite(os.path.join(dirs['depth_out'], name), depth_out)
+            _imwrite(os.path.join(dirs['disp_out'], name), disp_out)
+            if output_geo:
+                _imwrite(os.path.join(dirs['geo_out'], name), geo_out)
+        return {'img': img_out, 'depth': depth_out, 'geo': geo_out, 'disp': disp_out}
+
+
+def _inferno(gray_u8):
+    """cv2.applyColorMap(x, COLORMAP_INFERNO)[:, :, ::-1] (model/extracting_images.py:120): uint8 (h,w) -> RGB uint8 (h,w,3)."""
+    import cv2
+    return np.ascontiguousarray(cv2.applyColorMap(gray_u8, cv2.COLORMAP_INFERNO)[:, :, ::-1])
+
+
+def _imwrite(path, arr):
+    """PNG output: imageio when it is installed (what the reference calls), else OpenCV (RGB -> BGR)."""
+    try:
+        import imageio
+        if hasattr(imageio, 'imwrite'):
+            imageio.imwrite(path, arr)
+            return
+    except ImportError:
+        pass
+    import cv2
+    cv2.imwrite(path, arr[:, :, ::-1] if arr.ndim == 3 else arr)

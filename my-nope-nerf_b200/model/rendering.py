@@ -6,6 +6,8 @@ Two launches replace the ~60 the reference issues: ray generation, then the fuse
 sampling + encoding + MLP + compositing render.  Extra keys (`depth_pred_dense`, `depth_gt_dense`, `mask`) let the
 loss stack consume the dense tensors + mask without the reference's boolean-index host sync.
 """
+import os
+
 import torch
 import torch.nn as nn
 
@@ -24,8 +26,15 @@ class Renderer(nn.Module):
         self.white_background = cfg['white_background']
         self.cfg = cfg
         self.model = model.to(device)
-        # 'fp32' (CUDA cores, tight tolerance) or 'bf16' (tcgen05 tensor cores); not a reference option
-        self.precision = kwargs.get('precision', cfg.get('precision', 'fp32'))
+        # 'bf16' (tcgen05 tensor cores, fp32 accumulate) or 'fp32' (CUDA cores, tight tolerance).  Not a reference option, so it
+        # needs no YAML key: keyword > cfg['precision'] > env NNB_PRECISION > 'auto' = bf16 whenever the tensor-core tile fits
+        # (one ray = 128 samples), else fp32.  Both are CUDA paths of this library; there is no CPU path behind either.
+        prec = kwargs.get('precision', cfg.get('precision', os.environ.get('NNB_PRECISION', 'auto')))
+        if prec == 'auto':
+            prec = 'bf16' if (cfg['num_points'] - cfg['outside_steps']) == 128 else 'fp32'
+        if prec not in ('bf16', 'fp32'):
+            raise ValueError("precision must be 'bf16', 'fp32' or 'auto' (got %r)" % (prec,))
+        self.precision = prec
         self._packed = None
         self._packed_version = None
         self._pack_event = None
