@@ -29,6 +29,7 @@ extern "C" {
 #define NNB_ERR_WORKSPACE (-2)
 #define NNB_ERR_UNSUPPORTED (-3)
 #define NNB_ERR_NO_DEVICE (-4)
+#define NNB_ERR_TOO_LARGE (-5) /* problem exceeds the fixed capacity of an allocation-free entry point */
 
 #define NNB_NUM_PARAMS 24 /* 12 Linear layers x {weight, bias}, reference state_dict order */
 
@@ -309,6 +310,14 @@ size_t nnb_chamfer_workspace_bytes(int n_src, int n_dst);
 int nnb_debug_chamfer_pass1(int cuda_cores);
 int nnb_chamfer_nn(const float *src, int n_src, const float *dst, int n_dst, int64_t *idx, float *dist, void *workspace,
                    size_t workspace_bytes, void *stream);
+/* nnb_chamfer_nn without a caller-supplied workspace.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  Same
+ * inputs, outputs and results as nnb_chamfer_nn; the scratch is a file-scope `static __device__` array of the library
+ * (4.7 MB, held by every GPU that loads the library until exit), so n_src and n_dst are limited to
+ * NNB_CHAMFER_STATIC_MAX_POINTS each -- beyond that it returns NNB_ERR_TOO_LARGE.  It calls no cudaMalloc / cudaFree.  All
+ * calls share the one array: calls that overlap on the GPU (two streams, two threads) race; serialise them. */
+#define NNB_CHAMFER_STATIC_MAX_POINTS 32768
+int nnb_chamfer_nn_static(const float *src, int n_src, const float *dst, int n_dst, int64_t *idx, float *dist, void *stream);
 /* Loss.comp_point_point_error: model/losses.py:145-150.  loss = mean_i ||X_i - Y[idx_i]||. */
 int nnb_chamfer_err_fwd(const float *X, int n, const float *Y, const int64_t *idx, float *loss, void *stream);
 /* d_X (n,3) overwritten; d_Y (m,3) accumulated (+=) by scatter-add. */

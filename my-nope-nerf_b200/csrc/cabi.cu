@@ -30,6 +30,7 @@ const char *nnb_error_string(int code) {
     case NNB_ERR_WORKSPACE: return "nope_nerf_b200: workspace too small";
     case NNB_ERR_UNSUPPORTED: return "nope_nerf_b200: unsupported configuration";
     case NNB_ERR_NO_DEVICE: return "nope_nerf_b200: no sm_100 device";
+    case NNB_ERR_TOO_LARGE: return "nope_nerf_b200: problem size exceeds the fixed capacity of this allocation-free entry point";
     default: return "nope_nerf_b200: unknown error";
   }
 }

@@ -388,3 +388,42 @@ int nnb_align_clouds_bwd(const float *pc1, int n1, const float *pc2, int n2, con
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------
+// nnb_chamfer_nn_static: the same nearest-neighbour search for callers that cannot allocate (CUDA graph capture, serving
+// loops, harnesses that forbid cudaMalloc).  The workspace nnb_chamfer_nn takes from its caller lives here, in a file-scope
+// device array that every GPU loading this library holds until exit.  No counterpart in the
+// reference.
+//   * limit: n_src, n_dst <= NNB_CHAMFER_STATIC_MAX_POINTS (32,768 each: the training clouds are 28,830 points);
+//     larger problems return NNB_ERR_TOO_LARGE and must use nnb_chamfer_nn with a caller-owned workspace.
+//   * in host code the array's NAME is a host-side stand-in, not a device address: the device address is fetched once per
+//     device with cudaGetSymbolAddress (that device current) and that pointer is what the kernels receive.
+//   * every call shares the array; it keeps the previous call's contents.  nnb_chamfer_nn initialises every word of the
+//     workspace it reads (bounds, statistics, operand images) before reading it, so nothing has to be cleared between calls --
+//     but two calls that overlap on the GPU (different streams, or two host threads) RACE on it.  Serialise them.
+//   * calls no cudaMalloc / cudaFree / allocating library routine.
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+constexpr int CH_STATIC_MAX_POINTS = NNB_CHAMFER_STATIC_MAX_POINTS;
+constexpr size_t CH_STATIC_BYTES = 4724480 + 256;   // nnb_chamfer_workspace_bytes(32768, 32768) = 4,724,480 (checked at run time below)
+constexpr int CH_STATIC_MAX_DEVICES = 64;
+}  // namespace
+static __device__ __align__(256) unsigned char g_chamfer_static_scratch[CH_STATIC_BYTES];
+static void *g_chamfer_static_ptr[CH_STATIC_MAX_DEVICES] = {nullptr};
+
+extern "C" int nnb_chamfer_nn_static(const float *src, int n_src, const float *dst, int n_dst, int64_t *idx, float *dist,
+                                     void *stream) {
+  if (!src || !dst || !idx || n_src <= 0 || n_dst <= 0) return NNB_ERR_BAD_ARG;
+  if (n_src > CH_STATIC_MAX_POINTS || n_dst > CH_STATIC_MAX_POINTS) return NNB_ERR_TOO_LARGE;
+  if (nnb_chamfer_workspace_bytes(n_src, n_dst) > CH_STATIC_BYTES) return NNB_ERR_TOO_LARGE;
+  int dev = 0;
+  NNB_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= CH_STATIC_MAX_DEVICES) return NNB_ERR_UNSUPPORTED;
+  if (!g_chamfer_static_ptr[dev]) {
+    void *p = nullptr;
+    NNB_CUDA(cudaGetSymbolAddress(&p, g_chamfer_static_scratch));   // this device's copy of the array (device `dev` is current)
+    if (!p) return NNB_ERR_UNSUPPORTED;
+    g_chamfer_static_ptr[dev] = p;
+  }
+  return nnb_chamfer_nn(src, n_src, dst, n_dst, idx, dist, g_chamfer_static_ptr[dev], CH_STATIC_BYTES, stream);
+}

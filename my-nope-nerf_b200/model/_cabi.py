@@ -95,6 +95,7 @@ SIGNATURES = {
     "nnb_chamfer_workspace_bytes": [_i, _i],
     "nnb_debug_chamfer_pass1": [_i],
     "nnb_chamfer_nn": [_p, _i, _p, _i, _p, _p, _p, C.c_size_t, _p],
+    "nnb_chamfer_nn_static": [_p, _i, _p, _i, _p, _p, _p],
     "nnb_chamfer_err_fwd": [_p, _i, _p, _p, _p, _p],
     "nnb_chamfer_err_bwd": [_p, _i, _p, _p, _p, _p, _p, _p],
     "nnb_align_clouds_fwd": [_p, _i, _p, _i, _p, _p, _p, _p, _p],
