@@ -4,10 +4,15 @@
   python bench.py --gpus N --steps K --warmup W            # this repo's sm_100a path
   python bench.py --impl reference --gpus N --steps K ...  # the reference algorithm (oracle port) on the host cores
 
-One step = Trainer.train_step on one synthetic Virtual-KITTI-shaped frame pair: 4,096 rays x 128 samples per GPU,
-full loss set (rgb L1, depth with learned scale/shift, Chamfer point-cloud, reprojection), LearnPose + distortion,
-three Adam updates.  N > 1: every rank draws the same global batch of 4096*N rays, renders its shard, and the
+One step = Trainer.train_step on one synthetic Virtual-KITTI-shaped frame pair: 4,096 rays x 128 samples per GPU (BASELINE.json
+cfg2 on every GPU), full loss set (rgb L1, depth with learned scale/shift, Chamfer point-cloud, reprojection), LearnPose +
+distortion, three Adam updates.  N > 1: every rank draws the same global batch of 4096*N rays, renders its shard, and the
 MLP/pose/distortion gradients are averaged with one NCCL allreduce (weak scaling).  Prints ONE JSON line on rank 0.
+
+`extras` carries, device-timed in the same run: cfg3 (the 65,536-ray global batch sharded over the N ranks: the strong-scaling
+curve), the gradient allreduce alone (microseconds, bus GB/s), data-parallel parity (N > 1: all-reduced gradient vs the one-rank
+gradient of the same global batch), the drop-in path an unchanged train.py gets (host batches, three torch.optim.Adam, .item()
+reads), cfg4 (one rendered frame), cfg5 (Chamfer at 100k), and at N = 1 the stock-PyTorch-eager step on the same GPU.
 """
 import argparse
 import json
@@ -187,18 +192,23 @@ def run_b200(args):
     # The step runs as a CUDA graph (Trainer.train_step_graphed) unless --no-graph.  Warm-up (>= 3 steps), extended by one
     # step on each of the two frames that select a different graph (last frame / neighbour of the last frame), so that no
     # graph capture falls into the timed region.
-    step_fn = tr.train_step if args.no_graph else tr.train_step_graphed
+    step_fn = tr.train_step_eager if args.no_graph else tr.train_step_graphed
     warm = list(range(max(args.warmup, 3))) + ([] if args.no_graph else [n - 2, n - 1])
     for it in warm:
         step_fn(dev_batches[it % n], it=it, epoch=0, scheduling_start=sched)
     sampler = ClockSampler(local)
     sampler.start()
+    # The timed region of K steps is repeated `--repeats` times back to back (default 5) and the MEDIAN repeat is reported:
+    # one 50 ms region is a single sample of a machine whose clocks move under the power cap.
+    reps = max(1, args.repeats)
     l0 = _cabi.kernel_launches() + getattr(tr, "graphed_launches", 0)
-    ms = timed(dev_batches, args.steps, read_back=False)
-    launches = _cabi.kernel_launches() + getattr(tr, "graphed_launches", 0) - l0   # eager launches + kernel nodes replayed
+    ms_all = [timed(dev_batches, args.steps, read_back=False) for _ in range(reps)]
+    launches = (_cabi.kernel_launches() + getattr(tr, "graphed_launches", 0) - l0) // reps   # eager launches + kernel nodes replayed, per repeat
+    ms = sorted(ms_all)[len(ms_all) // 2]
     # end to end: pinned host batch -> device every step (model.BatchUploader), loss read back every step; own untimed warm-up
     timed(host_batches, max(args.warmup, 3, n), read_back=True)   # >= one pass over the frames: every graph variant captured
-    ms_e2e = timed(host_batches, args.steps, read_back=True)
+    ms_e2e_all = [timed(host_batches, args.steps, read_back=True) for _ in range(reps)]
+    ms_e2e = sorted(ms_e2e_all)[len(ms_e2e_all) // 2]
     if os.environ.get("NNB_E2E_PROBE"):   # debugging aid: where does the end-to-end leg lose time?
         import time as _t
         for label, fn in (("resident, no readback", lambda: timed(dev_batches, args.steps, read_back=False)),
@@ -218,7 +228,7 @@ def run_b200(args):
     if args.precision == "bf16":
         _cabi.lib().nnb_debug_bwd_timing(1, None)
     for it in range(prof_steps):
-        tr.train_step(dev_batches[it % n], it=it, epoch=0, scheduling_start=sched)
+        tr.train_step_eager(dev_batches[it % n], it=it, epoch=0, scheduling_start=sched)
         if args.precision == "bf16":
             _cabi.lib().nnb_debug_bwd_timing(1, bwd_ms)      # CUDA events around the two backward kernels of this step
             split[0] += bwd_ms[0] / prof_steps
@@ -254,10 +264,12 @@ def run_b200(args):
     rays_per_s = rays_global * args.steps / (ms * 1e-3)
     rays_per_s_e2e = rays_global * args.steps / (ms_e2e * 1e-3)
     out = {
-        "metric": METRIC, "value": rays_per_s, "unit": "rays/s", "n_gpus": world, "steps": args.steps, "warmup": len(warm),
+        "metric": METRIC, "value": rays_per_s, "unit": "rays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "warmup_effective": len(warm), "warmup_note": "requested warm-up (>= 3) plus one step on each of the two frames that select another graph variant",
+        "repeats": reps, "ms_per_step_repeats": [round(m / args.steps, 4) for m in ms_all], "value_is": "median of the repeats",
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32" if args.precision == "fp32" else "bf16 operands, f32 accumulate", "data": "synthetic",
-        "config": {"workload": "cfg2/cfg3: Virtual-KITTI-shaped synthetic scene, %d frames 375x1242, %d rays/step/GPU x 128 samples, "
+        "config": {"workload": "cfg2 per GPU: Virtual-KITTI-shaped synthetic scene, %d frames 375x1242, %d rays/step/GPU x 128 samples, "
                                "losses rgb+depth(l1, learned scale/shift)+Chamfer(28,830 pts)+reprojection, LearnPose, 3x Adam"
                                % (n, RAYS_PER_GPU),
                    "global_rays": rays_global, "resident_scene_bytes": resident.nbytes(), "parallelism": "dp%d" % world, "precision": args.precision,
@@ -266,7 +278,8 @@ def run_b200(args):
                                 % (13.0e3 * RAYS_PER_GPU * 128 / 1e9 if args.precision == "fp32" else 1.31e6 * RAYS_PER_GPU / 1e9)},
         "clocks": sampler.result(),
         "e2e": {"value": rays_per_s_e2e, "unit": "rays/s", "h2d_bytes_per_step": batch_bytes({k: v for k, v in host_batches[0].items() if k in tr.STEP_KEYS and k not in ("img.idx", "img.ref_idxs")}),
-                "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps},
+                "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps,
+                "ms_per_step_repeats": [round(m / args.steps, 4) for m in ms_e2e_all]},
         "gpu_launches": launches,
         "roofline": {"bound": "tensor", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
                      "frac": achieved_tf / peak_tf if peak_tf else None,
@@ -493,6 +506,8 @@ def main():
     ap.add_argument("--rays-per-gpu", type=int, default=RAYS_PER_GPU,
                     help="rays per step and GPU (default 4096 = cfg2; 8192 at --gpus 8 is cfg3's 65,536-ray global batch)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--repeats", type=int, default=5, help="the timed region of --steps steps is repeated this many times; the median is reported")
+    ap.add_argument("--no-extras", action="store_true", help="skip the extras (cfg3 / cfg4 / cfg5 / comparators): headline only")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel of the step eagerly instead of replaying a CUDA graph")
     args = ap.parse_args()
     globals()["RAYS_PER_GPU"] = args.rays_per_gpu

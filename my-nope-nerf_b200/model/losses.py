@@ -155,7 +155,10 @@ class Loss(nn.Module):
             pred_all = parallel.AllGatherRows.apply(depth_pred, self.dp, dpi['n_global'])
             g_all = dpi['depth_gt_global']
             gt_all = torch.cat([g_all[:lo].detach(), depth_gt, g_all[hi:].detach()])
-            depth_loss = self.get_depth_loss(pred_all, gt_all, dpi['mask_global']) * float(G)
+            full = self.get_depth_loss(pred_all, gt_all, dpi['mask_global'])
+            # every rank evaluates the SAME global term; a rank keeps only its own rays' slice of the gradient (AllGatherRows),
+            # so the averaged gradient needs G x that slice, while the VALUE must stay L (the rank mean of L is L):
+            depth_loss = float(G) * full - float(G - 1) * full.detach()
         if weights['weight_dist_2nd_loss'] != 0.0 or weights['weight_dist_1st_loss'] != 0.0:
             loss_dist_1st, loss_dist_2nd = self.get_weight_dist_loss(t_list)
         else:

@@ -106,14 +106,19 @@ def test_cfg2_step_fp32_vs_reference(cfg2_golden, case):
     ld = tr.compute_loss(batch, it=1, epoch=0, scheduling_start=cfg["training"]["scheduling_start"])
     ld["loss"].backward()
     torch.cuda.synchronize()
-    _compare("cfg2/%s fp32" % case, rec, ld, nerf, pose, dist, loss_tol=1e-4, grad_tol=2e-3, mlp_tol=2e-3, stat_tol=2e-3)
+    # north_star: fp32 paths <= 1e-5 relative.  Measured on B200 (profiles/r2_parity_errors.txt): losses <= 8.3e-7, pose /
+    # distortion gradients <= 1.6e-5 scale-relative, MLP gradients <= 2.3e-4 relative L2 except layers0.0.weight at 2.4e-3 (the
+    # layer behind the 2^9 positional-encoding gain: an fp32 rounding of a sample position moves sin(512 x) by 512 ulp on BOTH
+    # sides, which add up in a different order) -- asserted at 1e-5 / 1e-4 / 5e-3.
+    _compare("cfg2/%s fp32" % case, rec, ld, nerf, pose, dist, loss_tol=1e-5, grad_tol=1e-4, mlp_tol=5e-3, stat_tol=1e-3)
 
 
 @pytest.mark.parametrize("case", ["mid", "last"])
 def test_cfg2_graphed_bf16_step_vs_reference(cfg2_golden, case):
-    """The path bench.py times: bf16 tensor-core render inside the CUDA-graph step, FlatAdam.  Bounds: losses
-    1e-3 relative, pose / distortion gradients 5e-2 scale-relative, MLP gradients 0.25 relative L2 against the fp32 reference
-    (ReLU masks flip for pre-activations within bf16 rounding of zero)."""
+    """The path bench.py times: bf16 tensor-core render inside the CUDA-graph step, FlatAdam.  Measured on B200 against the
+    fp32 reference (profiles/r2_parity_errors.txt): losses <= 6.3e-6 relative, pose / distortion gradients <= 2.4e-5
+    scale-relative, MLP gradients <= 2.9e-2 relative L2 (ReLU masks flip for pre-activations within bf16 rounding of zero; over
+    4,096 rays the flips average out far below the 0.13 of the 64-ray fixture) -- asserted at 1e-4 / 1e-3 / 6e-2."""
     g, scene, r0, t0, scales, shifts, ray_idx, noise = cfg2_golden
     rec = g["cases"][case]
     cfg = syn.default_cfg()
@@ -127,7 +132,7 @@ def test_cfg2_graphed_bf16_step_vs_reference(cfg2_golden, case):
     ld = tr.train_step_graphed(batch, it=1, epoch=0, scheduling_start=sched)
     ld = tr.train_step_graphed(batch, it=2, epoch=0, scheduling_start=sched)    # a REPLAY of the captured graph
     torch.cuda.synchronize()
-    _compare("cfg2/%s bf16 graphed" % case, rec, ld, nerf, pose, dist, loss_tol=1e-3, grad_tol=5e-2, mlp_tol=0.25, stat_tol=0.1)
+    _compare("cfg2/%s bf16 graphed" % case, rec, ld, nerf, pose, dist, loss_tol=1e-4, grad_tol=1e-3, mlp_tol=6e-2, stat_tol=3e-2)
 
 
 @pytest.mark.parametrize("case", ["mid", "last"])
@@ -152,7 +157,8 @@ def test_cfg2_chamfer_indices_and_render_vs_reference(cfg2_golden, case):
         print("cfg2/%s Chamfer %s: %d of %d indices differ from the reference's" % (case, name, int(diff.sum()), got.numel()))
         assert int(diff.sum()) == 0
     cfg = syn.default_cfg()
-    for precision, tol in (("fp32", 1e-4), ("bf16", 1e-2)):
+    # measured on B200: fp32 rgb 1.8e-7 abs / depth 3.2e-7 rel; bf16 rgb 1.2e-4 abs / depth 3.4e-5 rel (north_star: <= 1e-2 abs rgb)
+    for precision, tol in (("fp32", 1e-5), ("bf16", 1e-3)):
         tr, nerf, pose, dist = _trainer(cfg, scene, r0, t0, scales, shifts, precision)
         tr.fixed_ray_idx, tr.fixed_noise = ray_idx, noise
         seen = {}
@@ -204,5 +210,5 @@ def test_cfg5_chamfer_100k_indices_bit_exact(golden, order, chamfer_pass1):
     d_chk = torch.linalg.norm(a - b[idx], dim=1)
     torch.testing.assert_close(dist.cpu(), d_chk, rtol=1e-6, atol=1e-7)
     probe = torch.randint(0, 100000, (512,), generator=torch.Generator().manual_seed(1))
-    d_probe = torch.cdist(a.to(dev()), b[probe].to(dev())).min(dim=1).values.cpu()
+    d_probe = torch.cdist(a.to(dev()), b[probe].to(dev()), compute_mode="donot_use_mm_for_euclid_dist").min(dim=1).values.cpu()
     assert bool((d_chk <= d_probe * (1 + 1e-6) + 1e-7).all())

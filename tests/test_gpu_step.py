@@ -43,20 +43,25 @@ def test_compute_loss_and_grads_vs_reference(golden):
         for k in LOSS_KEYS + ("scale", "shift"):
             assert torch.is_tensor(ld[k]), k
             print(name, k, "got %.7f want %.7f" % (float(ld[k].reshape(-1)[0]), float(rec["loss_dict"][k].reshape(-1)[0])))
-            assert_close(ld[k].reshape(-1).float(), rec["loss_dict"][k].float(), 2e-4, 2e-5, "%s/%s" % (name, k))
+            # north_star: fp32 paths <= 1e-5 relative (measured on B200: <= 1e-6, profiles/r2_parity_errors.txt)
+            assert_close(ld[k].reshape(-1).float(), rec["loss_dict"][k].float(), 1e-5, 1e-6, "%s/%s" % (name, k))
         ld["loss"].backward()
-        assert_close(pose.r.grad, rec["grad_r"], 5e-3, 5e-3 * float(rec["grad_r"].abs().max()), name + "/grad_r")
-        assert_close(pose.t.grad, rec["grad_t"], 5e-3, 5e-3 * float(rec["grad_t"].abs().max()), name + "/grad_t")
+
+        def srel(got, want):
+            return float((got.cpu() - want).abs().max() / want.abs().max().clamp_min(1e-12))
+        pairs = [("grad_r", pose.r.grad, rec["grad_r"]), ("grad_t", pose.t.grad, rec["grad_t"])]
         if rec["grad_scales"] is not None:
-            assert_close(dist.global_scales.grad, rec["grad_scales"], 5e-3, 5e-3 * float(rec["grad_scales"].abs().max()), name + "/grad_scales")
-            assert_close(dist.global_shifts.grad, rec["grad_shifts"], 5e-3, 5e-3 * float(rec["grad_shifts"].abs().max()), name + "/grad_shifts")
+            pairs += [("grad_scales", dist.global_scales.grad, rec["grad_scales"]), ("grad_shifts", dist.global_shifts.grad, rec["grad_shifts"])]
+        for gname, got, want in pairs:
+            e = srel(got, want)
+            print(name, gname, "scale-relative err %.3e" % e)
+            assert e <= 2e-4, (name, gname, e)       # end to end through ray generation and the 2^9 encoding gain
         if "mlp_grads" in rec:
             worst = 0.0
             for k, p in nerf.named_parameters():
-                ref = rec["mlp_grads"][k]
-                e = float((p.grad.cpu() - ref).abs().max() / ref.abs().max().clamp_min(1e-12))
+                e = srel(p.grad, rec["mlp_grads"][k])
                 worst = max(worst, e)
-                assert e < 5e-3, "%s grad %s scale-relative err %.3e" % (name, k, e)
+                assert e < 2e-4, "%s grad %s scale-relative err %.3e" % (name, k, e)
             print(name, "worst MLP grad scale-relative err %.3e" % worst)
 
 
@@ -350,5 +355,8 @@ def test_wgrad_on_its_own_stream_gives_the_same_step(golden):
             assert scale > 0, (step, k)
             rel = max_err(b[k], a[k]) / scale
             worst[min(step, 1)] = max(worst[min(step, 1)], rel)
-            assert rel <= (1e-4 if step == 0 else 5e-2), (step, k, rel)
+            # first step: the same computation, only the order of the weight-gradient atomics differs.  Later steps compare two
+            # bf16 TRAJECTORIES (the graph re-packs the updated weights every replay): they separate through ReLU-mask flips,
+            # so only their order of magnitude is checked
+            assert rel <= (1e-4 if step == 0 else 0.2), (step, k, rel)
     print("forked wgrad: worst scale-relative gradient difference, first step %.2e, later steps %.2e" % tuple(worst))
