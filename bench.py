@@ -110,6 +110,23 @@ def build_trainer(dev, n_frames, rays_global, precision, dp):
     return cfg, scene, tr
 
 
+def ncu_traffic(precision):
+    """DRAM bytes per 4,096-ray step of the MLP kernels as ncu measured them (profiles/ncu_traffic.json), only if that capture
+    was taken on the kernel source that is in the tree now."""
+    import hashlib
+    path = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if precision != "bf16" or not os.path.exists(path):
+        return None
+    try:
+        rec = json.load(open(path))
+        src = hashlib.sha256(open(os.path.join(PKG, "csrc", "mlp_tc.cu"), "rb").read()).hexdigest()[:16]
+        if rec.get("mlp_tc_sha16") != src:
+            return None
+        return rec
+    except Exception:
+        return None
+
+
 def batch_bytes(b):
     return sum(v.numel() * v.element_size() for v in b.values() if torch.is_tensor(v))
 
@@ -261,6 +278,7 @@ def run_b200(args):
              "unit": "GB/s", "frac": wg_bytes / split[1] / 1e6 / hbm,
              "tensor_frac": f_third / split[1] / 1e9 / peak_tf},
         ]
+    traffic = ncu_traffic(args.precision)
     rays_per_s = rays_global * args.steps / (ms * 1e-3)
     rays_per_s_e2e = rays_global * args.steps / (ms_e2e * 1e-3)
     out = {
@@ -283,19 +301,54 @@ def run_b200(args):
         "gpu_launches": launches,
         "roofline": {"bound": "tensor", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
                      "frac": achieved_tf / peak_tf if peak_tf else None,
-                     # dram__bytes_read + dram__bytes_write of the three kernels behind these two entry points, ncu --set full,
-                     # 4,096 rays (profiles/r1b_ncu_full_tc_kernels.txt): fwd 2.772 + dgrad 2.678 + wgrad 5.377 GB
-                     "traffic": 10.83e9 if args.precision == "bf16" else None, "traffic_unit": "B per step (ncu)",
+                     # dram__bytes_read + dram__bytes_write of the kernels behind these two entry points, per step, from the ncu
+                     # --set full capture recorded in profiles/ncu_traffic.json (tools/ncu_traffic.py writes it from the .ncu-rep
+                     # of THIS kernel version; null when the recorded source hash is not the current csrc/mlp_tc.cu)
+                     "traffic": traffic["bytes_per_step"] if traffic else None, "traffic_unit": "B per step (ncu dram__bytes_read.sum + dram__bytes_write.sum)",
+                     "traffic_source": traffic["source"] if traffic else "no ncu capture recorded for this kernel version",
+                     "traffic_kernels": traffic["kernels"] if traffic else None,
                      "kernel": "nnb_render_fwd + nnb_render_bwd (sampling+encoding+MLP+compositing, fwd and bwd)",
                      "kernel_ms_per_step": mlp_ms, "peak_source": "%s bf16 sustained" % pk_kind,
                      "algorithmic_flop_per_step": FLOP_PER_RAY_TRAIN * RAYS_PER_GPU,
                      "kernels": kernels},
         "stages_ms_per_step": {k: round(v, 4) for k, v in sorted(prof.items(), key=lambda kv: -kv[1])},
     }
-    if world == 1:
-        out["extras"] = extras(dev, cfg, scene, tr, args.precision)
-    else:
-        out["extras"] = render_extras_sharded(dev, scene, tr, dp)
+    import bench_extras as X
+    ex = {}
+    if not args.no_extras:
+        clk = out["clocks"].get("sm_mhz")
+        hbm = pk.get("hbm_gbs", 6650.0)
+        if world == 1:
+            ex.update(extras(dev, cfg, scene, tr, args.precision))
+            # per-stage rooflines (rank 0, N = 1 only: single-GPU kernels)
+            try:
+                st = X.stage_rooflines(dev, hbm)
+                ch = X.chamfer_rooflines(dev, clk)
+                out["roofline"]["kernels"] = (out["roofline"]["kernels"] or []) + ch + st
+            except Exception as e:      # an extra must never cost the headline line
+                ex["stage_rooflines_error"] = repr(e)[:300]
+        else:
+            ex.update(render_extras_sharded(dev, scene, tr, dp))
+        X.release(tr)           # the headline trainer's graphs own ~5 GB of workspace each: free them before the 65,536-ray step
+        for name, fn in (("cfg3", lambda: X.cfg3(dev, scene, cfg, host_batches, resident, args.precision, dp)),
+                         ("allreduce", lambda: X.allreduce_alone(dev, dp, n)),
+                         ("dp_parity", lambda: X.dp_parity(dev, scene, cfg, dp)),
+                         ("dropin", lambda: X.dropin_path(dev, scene, cfg, host_batches, "auto", dp)),
+                         ("torch_eager_gpu", (lambda: X.torch_eager_gpu(dev, scene, cfg)) if world == 1 else (lambda: None))):
+            try:
+                r = fn()
+                if r is not None:
+                    ex[name] = r
+            except Exception as e:
+                ex[name + "_error"] = repr(e)[:300]
+                torch.cuda.empty_cache()
+            if world > 1:
+                torch.distributed.barrier()
+        if "dropin" in ex:
+            ex["dropin_ms_per_step"] = ex["dropin"]["ms_per_step"]
+        if "allreduce" in ex:
+            ex["allreduce_us"] = ex["allreduce"]["us"]
+    out["extras"] = ex
     if dp.rank == 0 and not args.no_cpu_baseline and world == 1:
         out["cpu_baseline"] = cpu_baseline(max_seconds=25.0)
     if dp.rank == 0:
@@ -432,46 +485,63 @@ def cpu_step_sample(rays_sample=128, nn_slice=1024, threads=None):
     O.nearest_idx(X[:, :nn_slice], Y, slice_len=256)
     t["chamfer_slice_s"] = time.perf_counter() - t0_
     ray_part = max(t["render_and_reproj_s"] - t["reproj_s"], 0.0)
-    step_s = ray_part * (RAYS_PER_GPU / rays_sample) + t["reproj_s"] + t["chamfer_slice_s"] * (Pn / nn_slice) * 2
+    ray_full = ray_part * (RAYS_PER_GPU / rays_sample)
+    nn_full = t["chamfer_slice_s"] * (Pn / nn_slice) * 2
+    step_s = ray_full + t["reproj_s"] + nn_full
+    # how much of the claimed step time was MEASURED (the rest is the linear extrapolation of a slice)
+    t["measured_s"] = t["render_and_reproj_s"] + t["chamfer_slice_s"]
+    t["extrapolated_fraction"] = 1.0 - (ray_part + t["reproj_s"] + t["chamfer_slice_s"]) / step_s
+    t["render_extrapolated"] = rays_sample < RAYS_PER_GPU
     return step_s, t, Pn
 
 
+def _cpu_sample_text(cores, rays_sample, nn_slice, t, Pn, step_s):
+    return ("oracle port (PyTorch CPU, %d threads) of one cfg2 step: render + rgb/depth losses fwd+bwd on %d of %d rays (%.2f s%s), "
+            "reprojection and point clouds at full size (%.2f s), Chamfer nearest neighbour on %d of %d sources per direction (%.2f s, "
+            "extrapolated linearly to both full directions: the reference's own loop is a split over sources, model/losses.py:136-143); "
+            "full step ~ %.1f s of which %.0f %% is extrapolated"
+            % (cores, rays_sample, RAYS_PER_GPU, t["render_and_reproj_s"] - t["reproj_s"],
+               ", extrapolated linearly in rays" if t["render_extrapolated"] else ", MEASURED in full", t["reproj_s"], nn_slice, Pn,
+               t["chamfer_slice_s"], step_s, 100.0 * t["extrapolated_fraction"]))
+
+
 def cpu_baseline(max_seconds=25.0):
+    """Bounded (10-30 s) sample inside the GPU arm's run: 1,024 rays, 1,024 Chamfer sources."""
     cores = os.cpu_count() or 1
-    step_s, t, Pn = cpu_step_sample(rays_sample=128, nn_slice=1024, threads=cores)
+    step_s, t, Pn = cpu_step_sample(rays_sample=1024, nn_slice=1024, threads=cores)
     return {"value": RAYS_PER_GPU / step_s, "unit": "rays/s", "cores": cores, "kind": "port",
-            "sample": "oracle port (PyTorch CPU, %d threads) of one cfg2 step, extrapolated: render+rgb/depth fwd+bwd on 128 of 4,096 rays "
-                      "(%.2f s), reprojection at full size (%.2f s), Chamfer NN on 1,024 of %d sources per direction (%.2f s); "
-                      "full step ~ %.1f s" % (cores, t["render_and_reproj_s"], t["reproj_s"], Pn, t["chamfer_slice_s"], step_s),
-            "step_seconds_extrapolated": step_s}
+            "sample": _cpu_sample_text(cores, 1024, 1024, t, Pn, step_s), "step_seconds_extrapolated": step_s,
+            "extrapolated_fraction": t["extrapolated_fraction"], "measured_seconds": t["measured_s"]}
 
 
 def run_reference(args):
+    """The reference arm: the reference's algorithm (oracle port; the reference itself is a Python script tree that cannot
+    travel to the GPU box) on all host cores.  Every step renders the FULL 4,096-ray batch; only the Chamfer term -- ~150 s of
+    the step on 16 cores -- is measured on a 2,048-source slice per direction and extrapolated."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     cores = os.cpu_count() or 1
     warm = min(args.warmup, 1)
-    steps = min(args.steps, 3)
+    steps = max(1, min(args.steps, 2))
     for _ in range(warm):
-        cpu_step_sample(rays_sample=32, nn_slice=256, threads=cores)
+        cpu_step_sample(rays_sample=64, nn_slice=256, threads=cores)
     t0 = time.perf_counter()
     vals = []
     for _ in range(steps):
-        step_s, t, Pn = cpu_step_sample(rays_sample=128, nn_slice=1024, threads=cores)
-        vals.append(step_s)
+        step_s, t, Pn = cpu_step_sample(rays_sample=RAYS_PER_GPU, nn_slice=2048, threads=cores)
+        vals.append((step_s, t))
     wall = time.perf_counter() - t0
-    step_s = sorted(vals)[len(vals) // 2]
+    step_s, t = sorted(vals, key=lambda v: v[0])[len(vals) // 2]
     v = RAYS_PER_GPU / step_s
-    sample = ("each step = bounded sample of the cfg2 step on the host: render+rgb/depth fwd+bwd on 128 of 4,096 rays, reprojection at full "
-              "size, Chamfer NN on 1,024 of %d sources per direction; per-step time extrapolated linearly (%.1f s); wall %.1f s for %d samples"
-              % (Pn, step_s, wall, steps))
+    sample = _cpu_sample_text(cores, RAYS_PER_GPU, 2048, t, Pn, step_s) + "; wall %.1f s for %d steps" % (wall, steps)
     out = {"impl": "reference", "metric": METRIC, "value": v, "unit": "rays/s", "n_gpus": args.gpus, "steps": steps, "warmup": warm,
            "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
            "config": {"workload": "cfg2: Virtual-KITTI-shaped synthetic scene, 375x1242, 4096 rays/step x 128 samples, full loss set "
                                   "(reference algorithm, PyTorch CPU; the reference publishes no GPU-free path faster than this)",
                       "parallelism": "host cores"},
-           "cpu_baseline": {"value": v, "unit": "rays/s", "cores": cores, "kind": "port", "sample": sample},
+           "cpu_baseline": {"value": v, "unit": "rays/s", "cores": cores, "kind": "port", "sample": sample,
+                            "extrapolated_fraction": t["extrapolated_fraction"], "measured_seconds_per_step": t["measured_s"]},
            "e2e": {"value": v, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit(out)
 
