@@ -30,6 +30,34 @@ def med_ms(fn, reps=7, warm=2):
     return sorted(ts)[len(ts) // 2]
 
 
+def graph_ms(fn, inner=10, reps=7):
+    """Median DEVICE time of one fn() in ms: `inner` calls captured in a CUDA graph and replayed, so that no host launch
+    overhead sits between the events (a 10 us kernel launched from Python is otherwise timed at 30-60 us)."""
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        for _ in range(2):
+            fn()
+    torch.cuda.current_stream().wait_stream(s)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(inner):
+            fn()
+    g.replay()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(reps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1) / inner)
+    del g
+    return sorted(ts)[len(ts) // 2]
+
+
 def _fresh_trainer(dev, scene, cfg, rays_global, precision, dp, flat=True, **tkw):
     import model as mdl
     n = scene["n"]
@@ -148,9 +176,11 @@ def cfg3(dev, scene, cfg, host_batches, resident, precision, dp, steps=10, repea
     n = scene["n"]
     frames = list(range(n - 2))
     sched = cfg["training"]["scheduling_start"]
-    # same key set as the end-to-end leg's uploaded batches: both legs replay ONE captured graph
+    # same keys AND shapes as the end-to-end leg's uploaded batches, so that both legs replay ONE captured graph (a second variant
+    # would own a second 86 GB workspace at N = 1)
     keys = [k for k in host_batches[0] if k in tr.STEP_KEYS]
-    dev_batches = [{k: v for k, v in resident.batch(i, i + 1).items() if k in keys} for i in frames]
+    dev_batches = [{k: (host_batches[i][k].to(dev) if torch.is_tensor(host_batches[i][k]) and k not in ("img.idx", "img.ref_idxs") else host_batches[i][k])
+                    for k in keys} for i in frames]
 
     def sync_all():
         torch.cuda.synchronize()
@@ -198,6 +228,7 @@ def cfg3(dev, scene, cfg, host_batches, resident, precision, dp, steps=10, repea
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
     ms = sorted(ms_all)[len(ms_all) // 2]
     ms_e2e = float(t) / steps
+    assert len(tr._graphs) == 1, "cfg3 legs must share one graph variant"
     out = {"global_rays": G, "rays_per_gpu": G // world, "n_gpus": world, "ms_per_step": ms, "ms_per_step_repeats": [round(m, 3) for m in ms_all],
            "rays_per_s": G / (ms * 1e-3), "e2e": {"ms_per_step": ms_e2e, "rays_per_s": G / (ms_e2e * 1e-3)},
            "tflops_per_gpu": FLOP_PER_RAY_TRAIN * (G / world) / (ms * 1e-3) / 1e12, "scaling": "strong", "steps": steps,
@@ -290,9 +321,12 @@ def dp_parity(dev, scene, cfg, dp, rays_global=2048):
 # ---------------------------------------------------------------------------------------------------------------------
 # per-stage rooflines of the HBM-bound stages: algorithmic bytes per unit x units / CUDA-event time
 # ---------------------------------------------------------------------------------------------------------------------
-def stage_rooflines(dev, hbm_gbs, units=262144):
-    """Each stage on `units` (>= 65,536) rays / points so that the figure is bandwidth, not launch latency.  Bytes per unit are
-    SURVEY.md 8d's algorithmic figures (inputs read once + outputs written once)."""
+def stage_rooflines(dev, hbm_gbs, units=1048576):
+    """Each stage on `units` (>= 65,536; default 1 M) rays / points, timed as CUDA-graph replays (graph_ms: device time, no
+    host launch gaps), so that the figure is bandwidth and not launch latency.  Bytes per unit are SURVEY.md 8d's algorithmic
+    figures (inputs read once + outputs written once).  Between replays the inputs + outputs of a stage (tens to hundreds of
+    MB) exceed or rival the 126 MB L2 only for the compositing stages; the smaller ones are L2-resident on replay, which the
+    `note` of each entry says -- their figure is an upper bound of what HBM would give."""
     from model import _ops
     g = torch.Generator().manual_seed(5)
     R = units
@@ -307,11 +341,14 @@ def stage_rooflines(dev, hbm_gbs, units=262144):
     S = torch.eye(4, device=dev).unsqueeze(0)
     pixels, rgb_gt, depth_sel = _ops.GatherRays.apply(ray_idx, img, depth_img, ss, h, w)
     out = []
+    med_ms = graph_ms      # noqa: F811  (every stage below is timed as a graph replay)
 
     def add(name, ms, bytes_per_unit, n_units, unit, note=""):
         gbs = bytes_per_unit * n_units / (ms * 1e-3) / 1e9
+        mb = bytes_per_unit * n_units / 1e6
         out.append({"kernel": name, "bound": "hbm", "ms": ms, "us": ms * 1e3, "units": n_units, "unit": "GB/s", "per": unit,
-                    "bytes_per_unit": bytes_per_unit, "achieved": gbs, "peak": hbm_gbs, "frac": gbs / hbm_gbs, "note": note})
+                    "bytes_per_unit": bytes_per_unit, "achieved": gbs, "peak": hbm_gbs, "frac": gbs / hbm_gbs,
+                    "note": note + ("; %.0f MB per launch%s" % (mb, " (fits the 126 MB L2 on replay)" if mb < 100 else ""))})
 
     with torch.no_grad():
         add("nnb_gather_rays_fwd (ray gather: pixels, rgb_gt, depth*scale+shift)", med_ms(lambda: _ops.GatherRays.apply(ray_idx, img, depth_img, ss, h, w)),
@@ -323,10 +360,12 @@ def stage_rooflines(dev, hbm_gbs, units=262144):
         dp_, dg_ = (torch.rand(R, generator=g) + 0.5).to(dev), (torch.rand(R, generator=g) + 0.5).to(dev)
         mask = torch.ones(R, dtype=torch.bool, device=dev)
         add("nnb_depth_l1_fwd", med_ms(lambda: _ops.DepthL1.apply(dp_, dg_, mask)), 9, R, "ray", "SURVEY 8d: 8 B/ray + 1 mask")
-        add("nnb_depth_invariant_fwd (2 radix selects + 2 passes, ONE block)", med_ms(lambda: _ops.DepthInvariant.apply(dp_, dg_, mask)), 16, R, "ray",
-            "single-block kernel by design (R <= a few 100k): latency-bound, reported for completeness")
+        Ri = 65536
+        dpi, dgi, mi = dp_[:Ri].contiguous(), dg_[:Ri].contiguous(), mask[:Ri].contiguous()
+        add("nnb_depth_invariant_fwd (2 radix selects + 2 passes, ONE block)", med_ms(lambda: _ops.DepthInvariant.apply(dpi, dgi, mi)), 16, Ri, "ray",
+            "single-block kernel by design (a training batch is 4,096 rays): latency-bound, reported for completeness")
     # standalone compositing, forward and backward (3,088 / 4,624 B per ray)
-    Rc = 65536
+    Rc = 262144            # 0.8 GB forward, 1.2 GB backward per launch: far beyond L2
     alpha = (torch.rand(Rc, 128, generator=g) * 0.2).to(dev).requires_grad_(True)
     rgb_s = torch.rand(Rc, 128, 3, generator=g).to(dev).requires_grad_(True)
     z = torch.sort(torch.rand(Rc, 128, generator=g) * 10)[0].to(dev)
@@ -335,8 +374,12 @@ def stage_rooflines(dev, hbm_gbs, units=262144):
     rgb, dist, wts = _ops.Composite.apply(alpha, rgb_s, z, False, False)
     g_rgb, g_dist = torch.rand_like(rgb), torch.rand_like(dist)
 
-    def bwd():
-        torch.autograd.grad([rgb, dist], [alpha, rgb_s], [g_rgb, g_dist], retain_graph=True)
+    da, dc = torch.empty_like(alpha), torch.empty_like(rgb_s)
+    from model._cabi import call, ptr, stream
+    a_, c_ = alpha.detach(), rgb_s.detach()
+
+    def bwd():     # the C-ABI call of Composite.backward without the autograd engine (it allocates per call)
+        call("nnb_composite_bwd", ptr(a_), ptr(c_), ptr(z), ptr(wts.detach()), Rc, 128, 0, 0, ptr(g_rgb), ptr(g_dist), None, ptr(da), ptr(dc), stream())
     add("nnb_composite_bwd", med_ms(bwd), 4624, Rc, "ray", "SURVEY 8d: 4,624 B/ray")
     # reference-frame branch: back-projection and reprojection at >= 65,536 points (h4 x w4 = 320 x 416 = 133,120)
     h4, w4 = 320, 416
@@ -410,6 +453,10 @@ def chamfer_rooflines(dev, sm_mhz, n_sm=148):
                     "cuda_core_epilogue_bound_tpairs": core_bound / 1e12, "frac_of_cuda_core_bound": pps / core_bound,
                     "algorithmic_gflop": 8 * pairs / 1e9,
                     "tensor_issued_tflops": 2 * 2 * 16 * pairs / (ms * 1e-3) / 1e12, "fp16_mma_peak_tflops_measured": fp16_peak,
-                    "tensor_frac": 2 * 2 * 16 * pairs / (ms * 1e-3) / 1e12 / fp16_peak,
-                    "note": "issued tensor work = 2 sweeps x one 128x256x16 fp16 MMA per 128 x 256 pairs (64 FLOP/pair) when no stage is skipped"})
+                    "tensor_frac": (2 * 2 * 16 * pairs / (ms * 1e-3) / 1e12 / fp16_peak) if kind == "random" else None,
+                    "note": "issued tensor work = 2 sweeps x one 128x256x16 fp16 MMA per 128 x 256 pairs (64 FLOP/pair) when no stage is "
+                            "skipped (random order); raster order: the stage lists skip most pairs, so algorithmic pairs/s exceeds the "
+                            "sweep bounds and the issued-work figure does not apply"})
+        if kind == "raster":
+            out[-1]["tensor_issued_tflops"] = None
     return out
