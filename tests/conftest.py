@@ -33,3 +33,16 @@ def golden():
     def load(name):
         return torch.load(os.path.join(GOLDEN, name + ".pt"), weights_only=False)
     return load
+
+
+@pytest.fixture(scope="session", autouse=True)
+def _sanitizer_cuda_core_chamfer():
+    """tools/sanitizer_round.sh racecheck: NNB_SANITIZER_CUDA_CORES=1 runs every Chamfer search on the CUDA-core sweeps (racecheck
+    does not model the mbarrier / async-proxy synchronisation of the tcgen05 kernels)."""
+    if os.environ.get("NNB_SANITIZER_CUDA_CORES") == "1":
+        from model import _cabi
+        old = _cabi.lib().nnb_debug_chamfer_pass1(1)
+        yield
+        _cabi.lib().nnb_debug_chamfer_pass1(old)
+    else:
+        yield

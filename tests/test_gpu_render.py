@@ -219,3 +219,44 @@ def test_renderer_variants_vs_reference(golden, name, precision):
     assert max_err(ev["rgb"], v["eval"]["rgb"]) <= etol
     assert max_err(ev["depth_pred"], v["eval"]["depth_pred"]) <= etol * far
     assert_close(ev["depth_gt"], v["eval"]["depth_gt"], 1e-5, 1e-6, "eval depth_gt")
+
+
+@pytest.mark.parametrize("dist_alpha,white", [(False, False), (True, False), (False, True)])
+def test_composite_vector_path_is_bit_identical_to_the_generic_kernels(dist_alpha, white):
+    """S = 128 with 16-byte aligned tensors takes the float4 kernels (composite_fwd128 / bwd128); the same values through views
+    that start 4 bytes into their storage take the generic kernels.  Same arithmetic in the same order: outputs and gradients
+    must agree bit for bit."""
+    from model import _cabi
+    from model._cabi import call, ptr, stream
+    g = torch.Generator().manual_seed(17)
+    R, S = 777, 128
+    def pair(*shape, scale=1.0):
+        t = (torch.rand(*shape, generator=g) * scale).to(dev())
+        pad = torch.empty(t.numel() + 1, device=dev())
+        mis = pad[1:].view(*shape)          # 4 bytes into the allocation: not 16-byte aligned
+        mis.copy_(t)
+        assert t.data_ptr() % 16 == 0 and mis.data_ptr() % 16 == 4
+        return t, mis
+    alpha, alpha_m = pair(R, S, scale=0.3)
+    rgb_s, rgb_s_m = pair(R, S, 3)
+    z0 = torch.sort(torch.rand(R, S, generator=g) * 10)[0].to(dev())
+    z, z_m = z0.clone(), torch.empty(R * S + 1, device=dev())[1:].view(R, S)
+    z_m.copy_(z0)
+    g_rgb, g_dist = torch.randn(R, 3, generator=g).to(dev()), torch.randn(R, generator=g).to(dev())
+    g_w, g_w_m = pair(R, S)
+    outs = []
+    for a_, c_, z_, gw_, aligned in ((alpha, rgb_s, z, g_w, True), (alpha_m, rgb_s_m, z_m, g_w_m, False)):
+        rgb, dist = torch.empty(R, 3, device=dev()), torch.empty(R, device=dev())
+        if aligned:
+            w, ao, da, dc = (torch.empty(R, S, device=dev()), torch.empty(R, S, device=dev()), torch.empty(R, S, device=dev()),
+                             torch.empty(R, S, 3, device=dev()))
+        else:
+            w, ao, da = [torch.empty(R * S + 1, device=dev())[1:].view(R, S) for _ in range(3)]
+            dc = torch.empty(R * S * 3 + 1, device=dev())[1:].view(R, S, 3)
+        call("nnb_composite_fwd", ptr(a_), ptr(c_), ptr(z_), R, S, int(dist_alpha), int(white), ptr(rgb), ptr(dist), ptr(w), ptr(ao), stream())
+        call("nnb_composite_bwd", ptr(a_), ptr(c_), ptr(z_), ptr(w), R, S, int(dist_alpha), int(white), ptr(g_rgb), ptr(g_dist), ptr(gw_),
+             ptr(da), ptr(dc), stream())
+        torch.cuda.synchronize()
+        outs.append([t.clone() for t in (rgb, dist, w, ao, da, dc)])
+    for name, a, b in zip(("rgb", "dist", "weights", "alpha", "d_alpha", "d_rgb_s"), outs[0], outs[1]):
+        assert torch.equal(a, b), name
