@@ -8,7 +8,7 @@ PSNR of full-frame renders of all 8 frames.  Reported: per-arm mean +- std, the 
 error and 95 % interval (t distribution), and -- the noise floor -- the same statistic for fp32 against a REPEAT of fp32 with the
 same seed (the fp32 path's split-K weight gradient adds with atomics, so even identical seeds separate).
 
-usage: python tools/psnr_study.py [steps=1000] [seeds=5] [every=100]  -> markdown on stdout"""
+usage: python tools/psnr_study.py [steps=1000] [seeds=5] [every=100] [first_seed=42]  -> markdown on stdout"""
 import math
 import os
 import sys
@@ -24,6 +24,7 @@ from model import _ops  # noqa: E402
 steps = int(sys.argv[1]) if len(sys.argv) > 1 else 1000
 n_seeds = int(sys.argv[2]) if len(sys.argv) > 2 else 5
 every = int(sys.argv[3]) if len(sys.argv) > 3 else 100
+seed0 = int(sys.argv[4]) if len(sys.argv) > 4 else 42
 R = 1024
 dev = torch.device("cuda:0")
 T95 = {2: 12.706, 3: 4.303, 4: 3.182, 5: 2.776, 6: 2.571, 7: 2.447, 8: 2.365, 9: 2.306, 10: 2.262}
@@ -81,7 +82,7 @@ def stats(v):
 
 
 if __name__ == "__main__":
-    seeds = list(range(42, 42 + n_seeds))
+    seeds = list(range(seed0, seed0 + n_seeds))
     rows = []
     for s in seeds:
         a, a2, b = run("fp32", s), run("fp32", s), run("bf16", s)
