@@ -263,54 +263,63 @@ def test_batch_uploader_pipeline_matches_direct_upload(golden):
 
 
 def test_training_psnr_bf16_tracks_fp32():
-    """Training-level parity of the two precision paths (north_star asks for a PSNR-drift bound when bf16 tensor cores are used).
-    Training is chaotic: two runs of the fp32 path itself (atomics in its split-K weight gradients) differ by up to ~1 dB at
-    matched steps over the first 1k steps (profiles/r1d_psnr_drift.txt), so a 0.05 dB bound is below the noise floor of the
-    reference arithmetic.  Step 200 sits on the steepest part of the curve (17 -> 23 -> 26 dB at steps 100 / 200 / 300), where
-    1 dB is a handful of steps: repeated runs of this test gave fp32 20.3-21.4 dB and bf16 23.2-23.9 dB.  What is asserted: both
-    paths learn (PSNR of the training frames rises by > 4.5 dB in 200 steps) and the bf16 path ends within 4 dB of the fp32 path;
-    the 1,000-step record in profiles/ is the drift evidence."""
+    """Training-level parity of the two precision paths (north_star: "<= 0.05 dB PSNR drift over 1k steps if bf16 tensor cores are
+    used").  The evidence is the paired multi-seed study of tools/psnr_study.py (profiles/r2_psnr_drift.md: cfg1 scene, 1,000
+    steps, 20 seeds): bf16 - fp32 = +0.045 dB +- 0.099 (standard error), while fp32 against a REPEAT of fp32 with the same seed
+    differs by -0.066 dB +- 0.095 with single pairs up to 1.1 dB apart (the fp32 path's split-K weight gradient adds with atomics
+    and training is chaotic) -- the bf16 drift is not separable from the reference arithmetic's own run-to-run noise.  This test is the small version of that study: three seeds, 300 steps on the tiny
+    scene, both arms with identical initialisation and per-step draws.  Asserted: both paths learn (> 6 dB gained), and the
+    MEAN final PSNR of the bf16 arm is within 1.5 dB of the fp32 arm's (single pairs scatter by ~1 dB on this steep part of the
+    curve)."""
     import model as mdl
     from model import _ops
-    res = {}
-    for precision in ("fp32", "bf16"):
-        cfg = syn.default_cfg()
-        scene = syn.make_scene("tiny")
-        n, h, w = scene["n"], scene["h"], scene["w"]
-        nerf = mdl.OfficialStaticNerf(cfg)
-        nerf.load_state_dict(syn.init_mlp_state(42))
-        net = mdl.get_model(mdl.Renderer(nerf, dict(cfg["rendering"], precision=precision), device=dev()), cfg, device=dev()).to(dev())
-        pose = mdl.LearnPose(n, True, True, cfg, init_c2w=scene["poses_gt"].clone()).to(dev())
-        dist = mdl.Learn_Distortion(n, True, True, cfg).to(dev())
-        tcfg = dict(cfg["training"], n_training_points=512)
-        tr = mdl.Trainer(net, mdl.FlatAdam(net.parameters(), lr=tcfg["learning_rate"]), tcfg, device=dev(),
-                         optimizer_pose=mdl.FlatAdam(pose.parameters(), lr=tcfg["pose_lr"]), pose_param_net=pose,
-                         optimizer_distortion=mdl.FlatAdam(dist.parameters(), lr=tcfg["distortion_lr"]), distortion_net=dist)
-        rs = mdl.ResidentScene([syn.make_batch(scene, i) for i in range(n)], dev())
-        ex = mdl.Extract_Images(net.renderer, {"extract_images": {"resolution": [h, w]}}, device=dev(), render_type=tr.rendering_technique)
-        cam, scl = scene["camera_mat"].to(dev()).reshape(1, 4, 4), torch.eye(4, device=dev()).reshape(1, 4, 4)
+    res = {"fp32": [], "bf16": []}
+    for seed in (42, 43, 44):
+        for precision in ("fp32", "bf16"):
+            cfg = syn.default_cfg()
+            scene = syn.make_scene("tiny")
+            n, h, w = scene["n"], scene["h"], scene["w"]
+            nerf = mdl.OfficialStaticNerf(cfg)
+            nerf.load_state_dict(syn.init_mlp_state(seed))
+            net = mdl.get_model(mdl.Renderer(nerf, dict(cfg["rendering"], precision=precision), device=dev()), cfg, device=dev()).to(dev())
+            pose = mdl.LearnPose(n, True, True, cfg, init_c2w=scene["poses_gt"].clone()).to(dev())
+            dist = mdl.Learn_Distortion(n, True, True, cfg).to(dev())
+            tcfg = dict(cfg["training"], n_training_points=512)
+            tr = mdl.Trainer(net, mdl.FlatAdam(net.parameters(), lr=tcfg["learning_rate"]), tcfg, device=dev(),
+                             optimizer_pose=mdl.FlatAdam(pose.parameters(), lr=tcfg["pose_lr"]), pose_param_net=pose,
+                             optimizer_distortion=mdl.FlatAdam(dist.parameters(), lr=tcfg["distortion_lr"]), distortion_net=dist)
+            tr.use_graph = False        # eager: the per-step torch.manual_seed fixes the draws identically on both arms
+            rs = mdl.ResidentScene([syn.make_batch(scene, i) for i in range(n)], dev())
+            ex = mdl.Extract_Images(net.renderer, {"extract_images": {"resolution": [h, w]}}, device=dev(), render_type=tr.rendering_technique)
+            cam, scl = scene["camera_mat"].to(dev()).reshape(1, 4, 4), torch.eye(4, device=dev()).reshape(1, 4, 4)
 
-        def psnr():
-            vals = []
-            net.eval()
-            with torch.no_grad():
-                for f in (0, n // 2, n - 1):
-                    wm = _ops.Mat4Inverse.apply(pose(f)).unsqueeze(0)
-                    rgb, _ = ex.render_frame(cam, wm, scl, h, w)
-                    vals.append(-10.0 * float(torch.log10(((rgb.permute(2, 0, 1) - scene["imgs"][f].to(dev())) ** 2).mean())))
-            net.train()
-            return sum(vals) / len(vals)
+            def psnr():
+                vals = []
+                net.eval()
+                with torch.no_grad():
+                    for f in range(n):
+                        wm = _ops.Mat4Inverse.apply(pose(f)).unsqueeze(0)
+                        rgb, _ = ex.render_frame(cam, wm, scl, h, w)
+                        vals.append(-10.0 * float(torch.log10(((rgb.permute(2, 0, 1) - scene["imgs"][f].to(dev())) ** 2).mean())))
+                net.train()
+                return sum(vals) / len(vals)
 
-        p0 = psnr()
-        for it in range(200):
-            torch.manual_seed(1000 + it)
-            f = it % n
-            tr.train_step(rs.batch(f, f + 1 if f < n - 1 else f - 1), it=it, epoch=0, scheduling_start=cfg["training"]["scheduling_start"])
-        res[precision] = (p0, psnr())
-    print("PSNR start -> after 200 steps:", {k: "%.2f -> %.2f dB" % v for k, v in res.items()})
-    for k, (a, b) in res.items():
-        assert b - a > 4.5, (k, a, b)
-    assert abs(res["bf16"][1] - res["fp32"][1]) < 4.0, res
+            p0 = psnr()
+            tail = []
+            for it in range(300):
+                torch.manual_seed(seed * 1000003 + it)
+                f = it % n
+                tr.train_step(rs.batch(f, f + 1 if f < n - 1 else f - 1), it=it, epoch=0, scheduling_start=cfg["training"]["scheduling_start"])
+                if it in (259, 279, 299):
+                    tail.append(psnr())
+            res[precision].append((p0, sum(tail) / len(tail)))
+    print("PSNR start -> mean of steps 260/280/300, per seed:", {k: ["%.2f -> %.2f" % v for v in vs] for k, vs in res.items()})
+    for k, vs in res.items():
+        for a, b in vs:
+            assert b - a > 6.0, (k, a, b)
+    mean = {k: sum(b for _, b in vs) / len(vs) for k, vs in res.items()}
+    print("mean final PSNR: fp32 %.3f dB, bf16 %.3f dB, difference %+.3f dB" % (mean["fp32"], mean["bf16"], mean["bf16"] - mean["fp32"]))
+    assert abs(mean["bf16"] - mean["fp32"]) < 1.5, res
 
 
 def test_wgrad_on_its_own_stream_gives_the_same_step(golden):
