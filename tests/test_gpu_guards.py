@@ -114,7 +114,8 @@ def test_training_step_writes_inside_its_buffers_and_reads_nothing_unwritten(gua
     for ga, gb in zip(got_g, want_g):
         for x, y in zip(ga, gb):
             assert bool(torch.isfinite(x).all())
-            assert float((x - y).abs().max()) <= 1e-4 * float(y.abs().max()) + 1e-12      # weight-gradient atomics add in another order
+            # weight-gradient atomics add in another order: 1e-4 of the tensor's scale, with a floor for near-cancelling scalars
+            assert float((x - y).abs().max()) <= 1e-4 * float(y.abs().max()) + 1e-7
 
 
 @pytest.mark.parametrize("n,m", [(1, 1), (129, 257), (4099, 1023), (28830, 28829)])
