@@ -143,6 +143,76 @@ def test_shard_ranges_partition():
             assert max(sizes) - min(sizes) <= 1
 
 
+def _dp_loss_forward_check(dp, world, rank, _ops, losses):
+    """Loss.forward under data parallelism on gloo, the loss kernels replaced by torch stand-ins of the same
+    signature: per-rank terms are G x (share of the GLOBAL normaliser), the invariant depth loss all-gathers the rendered depths
+    (parallel.AllGatherRows), and the loss scalars ride in the gradient allreduce.  Unequal shards (61 rays) and a ragged mask: the
+    rank mean of values and gradients must be the one-rank result."""
+    import torch.distributed as dist
+    from model import parallel
+
+    class _Rgb(torch.autograd.Function):      # _ops.RgbLoss: [l1_sum / R, l2_sum / R, mse]
+        @staticmethod
+        def forward(ctx, pred, gt):
+            ctx.save_for_backward(pred, gt)
+            d = (pred - gt).reshape(-1, 3)
+            return torch.stack([d.abs().sum() / d.shape[0], (d * d).sum() / d.shape[0], (d * d).mean()])
+
+        @staticmethod
+        def backward(ctx, g):
+            pred, gt = ctx.saved_tensors
+            d = pred - gt
+            R = d.reshape(-1, 3).shape[0]
+            return g[0] * torch.sign(d) / R + (g[1] / R + g[2] / (3 * R)) * 2 * d, None
+
+    def depth_l1(pred, gt, mask):
+        m = mask if mask is not None else torch.ones_like(pred, dtype=torch.bool)
+        return ((pred - gt).abs() * m).sum() / m.sum().clamp_min(1)
+
+    def depth_inv(pred, gt, mask):
+        p, g_ = pred[mask], gt[mask]
+        n = lambda x: (x - x.median()) / (x - x.median()).abs().mean()
+        return ((n(p) - n(g_)) ** 2).mean()
+
+    _ops.RgbLoss = _Rgb
+    _ops.DepthL1 = type("L1", (), {"apply": staticmethod(depth_l1)})
+    _ops.DepthInvariant = type("Inv", (), {"apply": staticmethod(depth_inv)})
+    g = torch.Generator().manual_seed(11)
+    R = 61
+    pred0, gt0 = torch.rand(1, R, 3, generator=g), torch.rand(1, R, 3, generator=g)
+    dpred0, dgt0 = torch.rand(R, generator=g) + 0.5, torch.rand(R, generator=g) + 0.5
+    mask = torch.rand(R, generator=g) > 0.3
+    w = {k: 0.0 for k in syn.WEIGHT_NAMES}
+    w.update(rgb_weight=1.0, depth_weight=0.04)
+    for dlt in ("l1", "invariant"):
+        cfg = dict(syn.default_cfg()["training"], depth_loss_type=dlt)
+        one = losses.Loss(cfg)
+        a, b, c = pred0.clone().requires_grad_(True), dpred0.clone().requires_grad_(True), dgt0.clone().requires_grad_(True)
+        ld1 = one(a, gt0, b, c, weights=w, rgb_loss_type="l1", depth_mask=mask)
+        ld1["loss"].backward()
+        L = losses.Loss(cfg)
+        L.dp = dp
+        lo, hi = dp.shard(R)
+        pa, pb = pred0[:, lo:hi].clone().requires_grad_(True), dpred0[lo:hi].clone().requires_grad_(True)
+        gall = dgt0.clone().requires_grad_(True)
+        info = {"lo": lo, "hi": hi, "n_global": R, "mask_global": mask, "depth_gt_global": gall}
+        ld = L(pa, gt0[:, lo:hi], pb, gall[lo:hi], weights=w, rgb_loss_type="l1", depth_mask=mask[lo:hi], dp_info=info)
+        ld["loss"].backward()
+        # what Trainer does after the backward: ONE allreduce over [gradients | loss scalars]
+        gp = [torch.nn.Parameter(torch.zeros(1, R, 3)), torch.nn.Parameter(torch.zeros(R)), torch.nn.Parameter(torch.zeros(R))]
+        gp[0].grad = torch.zeros(1, R, 3)
+        gp[0].grad[:, lo:hi] = pa.grad
+        gp[1].grad = torch.zeros(R)
+        gp[1].grad[lo:hi] = pb.grad
+        gp[2].grad = gall.grad if gall.grad is not None else torch.zeros(R)
+        scal = [ld[k] for k in ("loss", "loss_rgb", "loss_depth", "l2_mean")]
+        dp.allreduce_grads(gp, extra=scal)
+        for k in ("loss", "loss_rgb", "loss_depth", "l2_mean"):
+            assert abs(float(ld[k]) - float(ld1[k])) <= 2e-6 * max(1.0, abs(float(ld1[k]))), (dlt, k, float(ld[k]), float(ld1[k]))
+        for got, want in ((gp[0].grad, a.grad), (gp[1].grad, b.grad), (gp[2].grad, c.grad)):
+            assert torch.allclose(got, want, rtol=1e-4, atol=1e-7), (dlt, float((got - want).abs().max()))
+
+
 def _gloo_worker(rank, world, port, out_dir):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     sys.path.insert(0, PKG)
@@ -201,6 +271,7 @@ def _gloo_worker(rank, world, port, out_dir):
     red /= world
     want = torch.cat([full.detach().reshape(1), Xf.grad.reshape(-1), Yf.grad.reshape(-1)])
     assert torch.allclose(red, want, rtol=1e-5, atol=1e-7), float((red - want).abs().max())
+    _dp_loss_forward_check(dp, world, rank, _ops, losses)
     open(os.path.join(out_dir, "ok%d" % rank), "w").write("ok")
     dist.destroy_process_group()
 
