@@ -439,6 +439,9 @@ class Trainer(object):
         n_global = ray_idx.numel()
         lo, hi = self.dp.shard(n_global)
         sharded = self.dp.world_size > 1
+        if hi <= lo:
+            raise ValueError("data parallelism over %d ranks needs at least that many rays per step (n_training_points = %d): rank %d "
+                             "would render an empty shard" % (self.dp.world_size, n_global, self.dp.rank))
         shard = (lo, hi) if sharded else None
 
         if (h_depth, w_depth) != (h, w):

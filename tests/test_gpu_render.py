@@ -173,7 +173,7 @@ def test_renderer_variants_vs_reference(golden, name, precision):
     """Non-default renderer branches through the drop-in Renderer against fixtures made by the
     reference's Renderer: NDC sampling + dist_alpha (configs/LLFF/fern.yaml), dist_alpha with uniform sampling, white
     background + relu density + use_ray_dir False.  fp32 path: 1e-3 relative end to end (2^9 positional-encoding gain);
-    bf16 tensor-core path: 1e-2 abs on rgb/alpha (north_star), gradients 0.25 relative L2."""
+    bf16 tensor-core path: 1e-2 abs on rgb/alpha (north_star), gradients 0.15 relative L2 at 48 rays (DESIGN.md sections 2 and 6)."""
     from util import build_models
     g = golden("render_variants")
     i, v = g["inputs"], g[name]
@@ -205,7 +205,7 @@ def test_renderer_variants_vs_reference(golden, name, precision):
         return float((a.detach().cpu() - b).norm() / b.norm().clamp_min(1e-20))
     # fp32: forward agrees to ~1e-7; the first layer's weight gradient is a cancelling sum over 6,144 samples of
     # 2^9-gain encodings, so fp32 summation order alone moves it by ~3e-3 relative L2 (measured 2.9e-3 on the NDC case)
-    tol = 5e-3 if precision == "fp32" else 0.25
+    tol = 5e-3 if precision == "fp32" else 0.15      # measured on B200 (48 rays): fp32 <= 2.9e-3, bf16 <= 0.10
     errs = {"world_mat": rel_l2(wm.grad, v["grad_world_mat"]), "camera_mat": rel_l2(cm.grad, v["grad_camera_mat"])}
     for k, gr in v["mlp_grads"].items():
         errs[k] = rel_l2(dict(nerf.named_parameters())[k].grad, gr)

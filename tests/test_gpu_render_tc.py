@@ -68,7 +68,7 @@ def test_tc_backward_vs_oracle(R):
     """Gradients of the bf16 tensor-core path.
     (1) Tight: against the bf16-emulating oracle (oracle/bf16_emulation.py: same rounding points, fp32 accumulate):
         relative L2 error <= 5e-2 per gradient tensor (measured 4e-3 .. 2.5e-2; the rest is a handful of mask flips from summation order) -- this is the kernel-correctness check.
-    (2) Loose: against the fp32 oracle: relative L2 <= 0.25 -- the documented bf16-vs-fp32 deviation, dominated by
+    (2) Loose: against the fp32 oracle: relative L2 <= 0.18 at these 33 / 64 rays (0.06 at 4,096 rays, tests/test_gpu_cfg2.py) -- the documented bf16-vs-fp32 deviation, dominated by
         ReLU masks flipping for pre-activations within bf16 rounding distance of zero."""
     from model import _cabi, _ops
     from oracle import nope_oracle as O
@@ -91,7 +91,9 @@ def test_tc_backward_vs_oracle(R):
     torch.cuda.synchronize()
     assert max_err(rgb2, ref32[0]) <= 1e-2
     print("tc R=%d forward vs bf16-emulation: rgb %.2e dist %.2e" % (R, max_err(rgb2, refbf[0]), max_err(dist2, refbf[1])))
-    for name, ref, tol in (("bf16-emulation", refbf, 5e-2), ("fp32 oracle", ref32, 0.25)):
+    # fp32 oracle: measured 0.090 (R = 64) and 0.128 (R = 33) on B200 -- a handful of rays, so single ReLU-mask flips weigh heavily;
+    # at 4,096 rays the same comparison gives 0.029 (tests/test_gpu_cfg2.py asserts 0.06)
+    for name, ref, tol in (("bf16-emulation", refbf, 5e-2), ("fp32 oracle", ref32, 0.18)):
         errs = {k: _rel_l2(p.grad, ref[2][k]) for k, p in zip(_cabi.PARAM_ORDER, params)}
         errs["d_origin"], errs["d_dirs"] = _rel_l2(od.grad, ref[3]), _rel_l2(dd.grad, ref[4])
         print("tc backward R=%d vs %s: worst rel-L2 %.3e" % (R, name, max(errs.values())))
