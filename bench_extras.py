@@ -321,8 +321,8 @@ def dp_parity(dev, scene, cfg, dp, rays_global=2048):
 # ---------------------------------------------------------------------------------------------------------------------
 # per-stage rooflines of the HBM-bound stages: algorithmic bytes per unit x units / CUDA-event time
 # ---------------------------------------------------------------------------------------------------------------------
-def stage_rooflines(dev, hbm_gbs, units=1048576):
-    """Each stage on `units` (>= 65,536; default 1 M) rays / points, timed as CUDA-graph replays (graph_ms: device time, no
+def stage_rooflines(dev, hbm_gbs, units=4194304):
+    """Each stage on `units` (>= 65,536; default 4 M rays, 2 M points) rays / points, timed as CUDA-graph replays (graph_ms: device time, no
     host launch gaps), so that the figure is bandwidth and not launch latency.  Bytes per unit are SURVEY.md 8d's algorithmic
     figures (inputs read once + outputs written once).  Between replays the inputs + outputs of a stage (tens to hundreds of
     MB) exceed or rival the 126 MB L2 only for the compositing stages; the smaller ones are L2-resident on replay, which the
@@ -330,10 +330,10 @@ def stage_rooflines(dev, hbm_gbs, units=1048576):
     from model import _ops
     g = torch.Generator().manual_seed(5)
     R = units
-    h, w = 1024, 2048                                   # source image of the gathers: 2 M pixels
+    h, w = 2048, 4096                                   # source image of the gathers: 8 M pixels
     img = torch.rand(3, h, w, generator=g).to(dev)
     depth_img = (torch.rand(h, w, generator=g) + 0.5).to(dev)
-    ray_idx = torch.randperm(h * w, generator=g)[:R].to(dev)
+    ray_idx = torch.randint(0, h * w, (R,), generator=g).to(dev)
     ss = torch.tensor([1.1, 0.02], device=dev)
     K = torch.diag(torch.tensor([1.17, -3.87, -1.0, 1.0])).unsqueeze(0).to(dev)
     c2w = syn.make_poses(3)[2].to(dev)
@@ -348,7 +348,7 @@ def stage_rooflines(dev, hbm_gbs, units=1048576):
         mb = bytes_per_unit * n_units / 1e6
         out.append({"kernel": name, "bound": "hbm", "ms": ms, "us": ms * 1e3, "units": n_units, "unit": "GB/s", "per": unit,
                     "bytes_per_unit": bytes_per_unit, "achieved": gbs, "peak": hbm_gbs, "frac": gbs / hbm_gbs,
-                    "note": note + ("; %.0f MB per launch%s" % (mb, " (fits the 126 MB L2 on replay)" if mb < 100 else ""))})
+                    "note": note + ("; %.0f MB per launch%s" % (mb, " (fits the 126 MB L2 on replay: an upper bound of what HBM gives)" if mb < 126 else ""))})
 
     with torch.no_grad():
         add("nnb_gather_rays_fwd (ray gather: pixels, rgb_gt, depth*scale+shift)", med_ms(lambda: _ops.GatherRays.apply(ray_idx, img, depth_img, ss, h, w)),
@@ -381,8 +381,8 @@ def stage_rooflines(dev, hbm_gbs, units=1048576):
     def bwd():     # the C-ABI call of Composite.backward without the autograd engine (it allocates per call)
         call("nnb_composite_bwd", ptr(a_), ptr(c_), ptr(z), ptr(wts.detach()), Rc, 128, 0, 0, ptr(g_rgb), ptr(g_dist), None, ptr(da), ptr(dc), stream())
     add("nnb_composite_bwd", med_ms(bwd), 4624, Rc, "ray", "SURVEY 8d: 4,624 B/ray")
-    # reference-frame branch: back-projection and reprojection at >= 65,536 points (h4 x w4 = 320 x 416 = 133,120)
-    h4, w4 = 320, 416
+    # reference-frame branch: back-projection and reprojection at 2 M points (h4 x w4 = 1024 x 2048)
+    h4, w4 = 1024, 2048
     dfull = (torch.rand(1, 1, 4 * h4, 4 * w4, generator=g) + 1.0).to(dev)
     Km = K
     with torch.no_grad():

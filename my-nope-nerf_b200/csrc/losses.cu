@@ -3,7 +3,7 @@
 
 static inline int red_grid(int n, int threads) {
   int g = nnb_cdiv(n, threads * 4);
-  const int cap = nnb_sm_count() * 4;
+  const int cap = nnb_sm_count() * 8;
   return g < 1 ? 1 : (g > cap ? cap : g);
 }
 
@@ -14,7 +14,18 @@ __global__ void rgb_loss_fwd_kernel(const float *__restrict__ pred, const float 
                                     float *__restrict__ out3) {
   __shared__ float red[32];
   float s1 = 0.f, s2 = 0.f;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n3; i += gridDim.x * blockDim.x) {
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x, nthr = gridDim.x * blockDim.x;
+  // 16-byte loads where both tensors allow it (two independent loads in flight per iteration), scalar tail
+  const bool vec = ((reinterpret_cast<uintptr_t>(pred) | reinterpret_cast<uintptr_t>(gt)) & 15) == 0;
+  const int n4 = vec ? n3 >> 2 : 0;
+  const float4 *p4 = reinterpret_cast<const float4 *>(pred), *g4 = reinterpret_cast<const float4 *>(gt);
+  for (int i = tid; i < n4; i += nthr) {
+    const float4 a = __ldg(p4 + i), b = __ldg(g4 + i);
+    const float d0 = a.x - b.x, d1 = a.y - b.y, d2 = a.z - b.z, d3 = a.w - b.w;
+    s1 += (fabsf(d0) + fabsf(d1)) + (fabsf(d2) + fabsf(d3));
+    s2 += (d0 * d0 + d1 * d1) + (d2 * d2 + d3 * d3);
+  }
+  for (int i = 4 * n4 + tid; i < n3; i += nthr) {
     const float d = pred[i] - gt[i];
     s1 += fabsf(d);
     s2 += d * d;
@@ -31,11 +42,16 @@ __global__ void rgb_loss_fwd_kernel(const float *__restrict__ pred, const float 
 __global__ void rgb_loss_bwd_kernel(const float *__restrict__ pred, const float *__restrict__ gt, int n3, float inv_r,
                                     const float *__restrict__ g3, float *__restrict__ d_pred) {
   const float g1 = g3[0] * inv_r, g2 = 2.f * inv_r * (g3[1] + g3[2] * (1.0f / 3.0f));
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n3; i += gridDim.x * blockDim.x) {
-    const float d = pred[i] - gt[i];
-    const float sg = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f);
-    d_pred[i] = g1 * sg + g2 * d;
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x, nthr = gridDim.x * blockDim.x;
+  auto grad = [&](float d) { return g1 * (d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f)) + g2 * d; };
+  const bool vec = ((reinterpret_cast<uintptr_t>(pred) | reinterpret_cast<uintptr_t>(gt) | reinterpret_cast<uintptr_t>(d_pred)) & 15) == 0;
+  const int n4 = vec ? n3 >> 2 : 0;
+  const float4 *p4 = reinterpret_cast<const float4 *>(pred), *g4 = reinterpret_cast<const float4 *>(gt);
+  for (int i = tid; i < n4; i += nthr) {
+    const float4 a = __ldg(p4 + i), b = __ldg(g4 + i);
+    reinterpret_cast<float4 *>(d_pred)[i] = make_float4(grad(a.x - b.x), grad(a.y - b.y), grad(a.z - b.z), grad(a.w - b.w));
   }
+  for (int i = 4 * n4 + tid; i < n3; i += nthr) d_pred[i] = grad(pred[i] - gt[i]);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -45,7 +61,18 @@ __global__ void depth_l1_fwd_kernel(const float *__restrict__ p, const float *__
                                     int n, float *__restrict__ out2) {
   __shared__ float red[32];
   float s = 0.f, c = 0.f;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x, nthr = gridDim.x * blockDim.x;
+  const bool vec = ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g)) & 15) == 0 && (!m || (reinterpret_cast<uintptr_t>(m) & 3) == 0);
+  const int n4 = vec ? n >> 2 : 0;
+  for (int i = tid; i < n4; i += nthr) {
+    const float4 a = __ldg(reinterpret_cast<const float4 *>(p) + i), b = __ldg(reinterpret_cast<const float4 *>(g) + i);
+    const uint32_t mm = m ? __ldg(reinterpret_cast<const uint32_t *>(m) + i) : 0x01010101u;   // four bool bytes
+    if (mm & 0x000000ffu) { s += fabsf(a.x - b.x); c += 1.f; }
+    if (mm & 0x0000ff00u) { s += fabsf(a.y - b.y); c += 1.f; }
+    if (mm & 0x00ff0000u) { s += fabsf(a.z - b.z); c += 1.f; }
+    if (mm & 0xff000000u) { s += fabsf(a.w - b.w); c += 1.f; }
+  }
+  for (int i = 4 * n4 + tid; i < n; i += nthr) {
     if (!m || m[i]) { s += fabsf(p[i] - g[i]); c += 1.f; }
   }
   s = block_sum(s, red);
