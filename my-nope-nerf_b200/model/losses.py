@@ -28,7 +28,23 @@ class Loss(nn.Module):
         # data-parallel context (set by Trainer): the Chamfer SOURCE points are sharded across ranks
         self.dp = None
         self._nan_pending, self._nan_step = None, 0
-        self._weight_vectors = {}   # (weights of the active terms, device) -> device vector, built once per schedule phase
+        # names of the active terms -> [device vector, values last written].  ONE persistent device tensor
+        # per active set: a captured graph bakes its address, the VALUES (the annealed weights change every epoch) are
+        # written before each replay, so annealing does not multiply graphs
+        self._weight_vectors = {}
+
+    def weight_vector(self, names, values, dev):
+        """Device vector of the active terms' weights.  Outside a capture the current values are (re)written when they changed
+        (one small H2D copy); during a capture the tensor is used as it is -- Trainer.train_step_graphed
+        writes the step's values through this same call before every replay."""
+        rec = self._weight_vectors.get((names, str(dev)))
+        vals = tuple(float(v) for v in values)
+        if rec is None:
+            rec = self._weight_vectors[(names, str(dev))] = [torch.tensor(vals, dtype=torch.float32, device=dev), vals]
+        elif rec[1] != vals and not (torch.device(dev).type == 'cuda' and torch.cuda.is_current_stream_capturing()):
+            rec[0].copy_(torch.tensor(vals, dtype=torch.float32))     # a few bytes, staged by the driver: stream-ordered before the next launch
+            rec[1] = vals
+        return rec[0]
 
     def raise_if_nan(self, loss_dict):
         """model/losses.py:213-214 (`if torch.isnan(loss): breakpoint()`) without a host synchronisation on the step just
@@ -184,13 +200,10 @@ class Loss(nn.Module):
         named = (('rgb_weight', rgb_full_loss), ('depth_weight', depth_loss), ('weight_dist_1st_loss', loss_dist_1st),
                  ('weight_dist_2nd_loss', loss_dist_2nd), ('pc_weight', pc_loss), ('rgb_s_weight', rgb_s_loss),
                  ('depth_consistency_weight', depth_consistency_loss), ('t_cycle_weight', t_cycle_loss))
-        active = [(float(weights[k]), v) for k, v in named if weights[k] != 0.0]
+        active = [(k, float(weights[k]), v) for k, v in named if weights[k] != 0.0]
         if active:
-            wkey = (tuple(w for w, _ in active), str(dev))
-            wvec = self._weight_vectors.get(wkey)
-            if wvec is None:
-                wvec = self._weight_vectors[wkey] = torch.tensor(wkey[0], dtype=torch.float32, device=dev)
-            loss = torch.dot(torch.stack([v.reshape(()) for _, v in active]), wvec)
+            wvec = self.weight_vector(tuple(k for k, _, _ in active), [w for _, w, _ in active], dev)
+            loss = torch.dot(torch.stack([v.reshape(()) for _, _, v in active]), wvec)
         else:
             loss = zero
         return {

@@ -20,6 +20,9 @@ logger_py = logging.getLogger(__name__)
 
 WEIGHT_NAMES = ['rgb_weight', 'depth_weight', 'pc_weight', 'rgb_s_weight', 'depth_consistency_weight',
                 'weight_dist_2nd_loss', 'weight_dist_1st_loss', 't_cycle_weight']
+# the order in which Loss.forward sums the terms (model/losses.py:204-208): the key of Loss.weight_vector
+WEIGHT_NAMES_IN_SUM = ['rgb_weight', 'depth_weight', 'weight_dist_1st_loss', 'weight_dist_2nd_loss', 'pc_weight', 'rgb_s_weight',
+                       'depth_consistency_weight', 't_cycle_weight']
 
 
 class Trainer(object):
@@ -31,6 +34,7 @@ class Trainer(object):
         self.fork_wgrad = True      # train_step_graphed: weight-gradient kernel on its own stream (joined before the optimiser)
         self.fork_geometry = True   # train_step_graphed: reference-frame branch as a parallel branch of the graph
         self._geom_stream = None    # set while train_step_graphed warms up and captures: forks the reference-frame branch
+        self._geom_forked = False
         self.optimizer_pose = optimizer_pose
         self.pose_param_net = pose_param_net
         self.focal_net = focal_net
@@ -64,6 +68,7 @@ class Trainer(object):
         # graph whenever the batch allows it (see _graph_ok); False: always launch kernel by kernel; True: always graph
         env = os.environ.get('NNB_GRAPH', 'auto')
         self.use_graph = {'0': False, '1': True}.get(env, 'auto')
+        self.max_graphs = int(os.environ.get('NNB_MAX_GRAPHS', '8'))   # captured step variants kept (least recently used evicted)
         # 'feistel' (nnb_ray_choice, no sort) or 'reference' (torch.randperm(h*w)[:n], the draw of model/training.py:277 with
         # the same consumption of the device generator); cfg key `ray_choice`, env NNB_RAY_CHOICE
         self.ray_choice = cfg.get('ray_choice', os.environ.get('NNB_RAY_CHOICE', 'feistel'))
@@ -135,14 +140,22 @@ class Trainer(object):
         n = self.pose_param_net.num_cams
         idx = int(data.get('img.idx'))
         ref = int(data.get('img.ref_idxs')) if data.get('img.ref_idxs') is not None else -1
-        wkey = tuple(self.anneal(getattr(self, w)[0], getattr(self, w)[1], scheduling_start, self.annealing_epochs, epoch)
-                     for w in WEIGHT_NAMES) + (epoch < self.annealing_epochs + scheduling_start,)
+        wvals = [self.anneal(getattr(self, w)[0], getattr(self, w)[1], scheduling_start, self.annealing_epochs, epoch) for w in WEIGHT_NAMES]
+        # WHICH terms are active selects the graph (zero-weight terms are skipped, model/losses.py:169-197); their VALUES -- the
+        # annealed weights change every epoch -- live in a device vector written below, before the replay
+        wkey = tuple(v != 0.0 for v in wvals) + (epoch < self.annealing_epochs + scheduling_start,)
         tensors = sorted(k for k, v in data.items() if torch.is_tensor(v) and k not in ('img.idx', 'img.ref_idxs'))
         key = (idx < n - 1, idx == n - 1, ref == n - 1, wkey, tuple((k, tuple(data[k].shape), data[k].dtype) for k in tensors))
-        slot = self._graphs.get(key)
+        slot = self._graphs.pop(key, None)
         if slot is None:
+            while len(self._graphs) >= self.max_graphs:       # each graph owns a saved-activation workspace (1.3 MB per ray)
+                self._graphs.pop(next(iter(self._graphs)))     # least recently used first (dicts keep insertion order)
             slot = self._capture_step(data, tensors, it, epoch, scheduling_start)
-            self._graphs[key] = slot
+        self._graphs[key] = slot                              # most recently used last
+        wnow = dict(zip(WEIGHT_NAMES, wvals))
+        active = tuple(w for w in WEIGHT_NAMES_IN_SUM if wnow[w] != 0.0)
+        if active:
+            self.loss.weight_vector(active, [wnow[w] for w in active], self.device)    # this step's weight values, before the replay
         static = slot['static']
         # batch staging: every device-resident tensor of the batch and the two frame indices in ONE launch (nnb_copy_many)
         pairs = []
@@ -233,7 +246,7 @@ class Trainer(object):
         def body():
             for p in params:
                 p.grad = None
-            self._geom_stream = geom
+            self._geom_stream, self._geom_forked = geom, False
             _ops.wgrad_stream, _ops.wgrad_forked = wgrad, False
             try:
                 if pack is not None:
@@ -243,7 +256,7 @@ class Trainer(object):
                 ld = self.compute_loss(static, it=it, epoch=epoch, scheduling_start=scheduling_start)
                 ld['loss'].backward()
                 renderer.join_pack()                                # no-op when the render consumed the pack
-                if geom is not None:
+                if geom is not None and self._geom_forked:          # (a step without reference-frame terms never forks it)
                     torch.cuda.current_stream().wait_stream(geom)   # nothing of the branch is left unjoined when capture ends
                 if wgrad is not None and _ops.wgrad_forked:
                     torch.cuda.current_stream().wait_stream(wgrad)  # parameter gradients complete before the optimiser reads them
@@ -364,6 +377,7 @@ class Trainer(object):
             main_stream = torch.cuda.current_stream() if geom is not None else None
             if geom is not None:
                 geom.wait_stream(main_stream)
+                self._geom_forked = True
             with (torch.cuda.stream(geom) if geom is not None else contextlib.nullcontext()):
                 ref_idx_i = int(ref_idx)
                 c2w_ref = self.pose_param_net(ref_idx_i, ref_idx_dev)

@@ -264,3 +264,44 @@ def test_nan_loss_raises_one_step_late():
     L.raise_if_nan(bad)          # examines the previous (finite) loss
     with pytest.raises(FloatingPointError):
         L.raise_if_nan(ok)       # now the NaN of the step before is seen
+
+
+def test_annealed_loss_weights_do_not_multiply_graphs():
+    """model/training.py:204-212 anneals the loss weights every epoch between scheduling_start and scheduling_start +
+    annealing_epochs.  The graph is keyed on WHICH terms are active; the weight VALUES live in a device vector written before each
+    replay -- so 40 epochs of annealing replay the same graphs, give the eager step's losses, and the cache stays bounded."""
+    cfg = syn.default_cfg()
+    scene = syn.make_scene("tiny")
+    n, R = scene["n"], 64
+    sched, ann = 5, 40
+    ray_idx, noise = syn.ray_choice(scene["h"], scene["w"], R).to(dev()), syn.jitter(R).to(dev())
+    runs = {}
+    for graphed in (False, True):
+        tr, nerf, pose, dist = _trainer(cfg, scene, "bf16", R, annealing_epochs=ann)
+        tr.fixed_ray_idx, tr.fixed_noise = ray_idx, noise
+        out = []
+        for epoch in (0, 5, 6, 15, 25, 44, 45, 60):      # before, during (weights change every time) and after annealing
+            for f in (0, n - 1):
+                b = _dev_batch(scene, f, f + 1 if f < n - 1 else f - 1)
+                ld = (tr.train_step_graphed if graphed else tr.train_step_eager)(b, it=epoch, epoch=epoch, scheduling_start=sched)
+                out.append([float(ld[k].detach()) for k in ("loss", "loss_rgb", "loss_depth", "loss_pc", "loss_rgb_s")])
+        runs[graphed] = torch.tensor(out)
+        if graphed:
+            # variants: {mid, last frame} x {all four terms active, (epoch >= 45) depth / pc / rgb_s switched off + L2 rgb}
+            assert len(tr._graphs) == 4, len(tr._graphs)
+    assert_close(runs[True], runs[False], 5e-3, 5e-4, "graphed vs eager losses under annealing")
+    w0 = runs[False][:, 0]
+    assert float((w0[2] - w0[4]).abs()) > 1e-4        # the total loss does follow the changing weights
+
+
+def test_graph_cache_is_bounded():
+    cfg = syn.default_cfg()
+    scene = syn.make_scene("tiny")
+    tr, *_ = _trainer(cfg, scene, "bf16", 64)
+    tr.max_graphs = 2
+    sched = cfg["training"]["scheduling_start"]
+    n = scene["n"]
+    for it, f in enumerate([0, n - 2, n - 1, 0, n - 1, n - 2]):     # three variants through a cache of two
+        tr.train_step_graphed(_dev_batch(scene, f, f + 1 if f < n - 1 else f - 1), it=it, epoch=0, scheduling_start=sched)
+        assert len(tr._graphs) <= 2
+    torch.cuda.synchronize()
