@@ -145,7 +145,9 @@ class Trainer(object):
         # annealed weights change every epoch -- live in a device vector written below, before the replay
         wkey = tuple(v != 0.0 for v in wvals) + (epoch < self.annealing_epochs + scheduling_start,)
         tensors = sorted(k for k, v in data.items() if torch.is_tensor(v) and k not in ('img.idx', 'img.ref_idxs'))
-        key = (idx < n - 1, idx == n - 1, ref == n - 1, wkey, tuple((k, tuple(data[k].shape), data[k].dtype) for k in tensors))
+        # injected draws (test hooks) are baked into a capture as device pointers: they select their own graphs
+        hooks = tuple(None if t is None else (t.data_ptr(), str(t.device)) for t in (self.fixed_ray_idx, self.fixed_noise))
+        key = (idx < n - 1, idx == n - 1, ref == n - 1, wkey, hooks, tuple((k, tuple(data[k].shape), data[k].dtype) for k in tensors))
         slot = self._graphs.pop(key, None)
         if slot is None:
             while len(self._graphs) >= self.max_graphs:       # each graph owns a saved-activation workspace (1.3 MB per ray)

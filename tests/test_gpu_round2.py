@@ -305,3 +305,72 @@ def test_graph_cache_is_bounded():
         tr.train_step_graphed(_dev_batch(scene, f, f + 1 if f < n - 1 else f - 1), it=it, epoch=0, scheduling_start=sched)
         assert len(tr._graphs) <= 2
     torch.cuda.synchronize()
+
+
+def test_training_loop_with_schedulers_reset_preview_and_checkpoint(tmp_path):
+    """What else train.py does around train_step, against the graph's persistent buffers: MultiStepLR on the three optimisers
+    (train.py:303-346), the in-place re-initialisation of every nn.Linear of `scheduling_mode: reset` (train.py:347-350), a preview
+    render between steps (train.py:239), and a checkpoint save / load (train.py:62,262).  After each of them the NEXT graphed step
+    must see the new weights: it is compared with an eager step from the same state."""
+    import copy
+    import model as mdl
+    cfg = syn.default_cfg()
+    scene = syn.make_scene("tiny")
+    n = scene["n"]
+    sched = cfg["training"]["scheduling_start"]
+    torch.manual_seed(1)
+    model = mdl.OfficialStaticNerf(cfg)
+    renderer = mdl.Renderer(model, cfg["rendering"], device=dev())
+    net = mdl.get_model(renderer, cfg, device=dev())
+    pose = mdl.LearnPose(n, True, True, cfg=cfg, init_c2w=scene["poses_gt"].clone()).to(dev())
+    dist = mdl.Learn_Distortion(n, True, True, cfg).to(dev())
+    opt = torch.optim.Adam(net.parameters(), lr=1e-3)
+    opt_p, opt_d = torch.optim.Adam(pose.parameters(), lr=5e-4), torch.optim.Adam(dist.parameters(), lr=5e-4)
+    scheds = [torch.optim.lr_scheduler.MultiStepLR(o, milestones=[1, 2], gamma=0.5) for o in (opt, opt_p, opt_d)]
+    tcfg = dict(cfg["training"], n_training_points=64)
+    tr = mdl.Trainer(net, opt, tcfg, device=dev(), optimizer_pose=opt_p, pose_param_net=pose, optimizer_distortion=opt_d, distortion_net=dist)
+    ckpt = mdl.CheckpointIO(str(tmp_path), model=net)           # modules only: restoring an optimiser would also restore its lr
+    ckpt_pose = mdl.CheckpointIO(str(tmp_path), model=pose)
+    ray_idx, noise = syn.ray_choice(scene["h"], scene["w"], 64).to(dev()), syn.jitter(64).to(dev())
+
+    def check_next_step_sees_current_weights(tag):
+        """graphed step vs an eager step of a deep copy taken at the same state, same injected draws"""
+        tr.fixed_ray_idx, tr.fixed_noise = ray_idx, noise
+        twin = copy.deepcopy(net)
+        tw_pose, tw_dist = copy.deepcopy(pose), copy.deepcopy(dist)
+        t2 = mdl.Trainer(twin, None, tcfg, device=dev(), pose_param_net=tw_pose, distortion_net=tw_dist)
+        t2.fixed_ray_idx, t2.fixed_noise = ray_idx, noise
+        b = syn.make_batch(scene, 1, 2)
+        want = t2.compute_loss(b, it=0, epoch=0, scheduling_start=sched)
+        got = tr.train_step_graphed({k: (v.to(dev()) if torch.is_tensor(v) and k not in ("img.idx", "img.ref_idxs") else v) for k, v in b.items()},
+                                    it=0, epoch=0, scheduling_start=sched)
+        for k in ("loss", "loss_rgb", "loss_depth", "loss_pc"):
+            a, c = float(got[k].detach()), float(want[k].detach())
+            assert abs(a - c) <= 2e-4 * max(1.0, abs(c)), (tag, k, a, c)
+        tr.fixed_ray_idx = tr.fixed_noise = None
+
+    it = 0
+    for epoch in range(3):
+        for f in range(n):
+            it += 1
+            ld = tr.train_step(syn.make_batch(scene, f, f + 1 if f < n - 1 else f - 1), it, epoch, sched, str(tmp_path))
+            assert ld["loss"].item() == ld["loss"].item()
+        for s_ in scheds:
+            s_.step()
+        assert opt.param_groups[0]["lr"] == pytest.approx(1e-3 * 0.5 ** min(epoch + 1, 2))
+        check_next_step_sees_current_weights("after epoch %d" % epoch)
+        if epoch == 0:
+            img = tr.render_visdata(syn.make_batch(scene, 0), (scene["h"], scene["w"]), it, str(tmp_path))
+            assert img.shape == (scene["h"], scene["w"], 3)
+            check_next_step_sees_current_weights("after the preview render")
+            ckpt.save("model.pt", epoch_it=epoch, it=it)
+            ckpt_pose.save("model_pose.pt")
+        if epoch == 1:
+            for m in net.modules():                      # train.py:347-350
+                if isinstance(m, torch.nn.Linear):
+                    m.reset_parameters()
+            check_next_step_sees_current_weights("after reset_parameters")
+            scal = ckpt.load("model.pt")
+            ckpt_pose.load("model_pose.pt")
+            assert scal["it"] == n and scal["epoch_it"] == 0
+            check_next_step_sees_current_weights("after loading the checkpoint")
