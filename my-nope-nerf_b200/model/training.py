@@ -93,6 +93,7 @@ class Trainer(object):
         return (dev is not None and dev.type == 'cuda' and self.pose_param_net is not None
                 and self.fixed_ray_idx is None and self.fixed_noise is None
                 and self.ray_choice != 'reference'        # the reference's generator sequence is an eager-mode property
+                and not self.optimizer_focal              # learned intrinsics (non-default): kernel-by-kernel step
                 and data.get('img.dpt') is not None       # sparse depth: the resample loop of model/training.py:279-284 reads the mask on the host
                 and _cabi.profile is None)                # per-entry-point timing (bench.py) needs eager launches
 
