@@ -1093,7 +1093,8 @@ constexpr int WG_GROUPS = 8;          // 8-sample row groups per stage (64 sampl
 constexpr uint32_t WG_RING_BYTES = 184320;   // a stage is P 16 KB + Q parts up to 44 KB
 constexpr uint32_t SW_RING = 0;
 constexpr uint32_t SW_BARS = WG_RING_BYTES;
-constexpr uint32_t SW_TOTAL = SW_BARS + 24 * 8 + 16;
+constexpr uint32_t SW_ONES = SW_BARS + 24 * 8 + 64;   // 256 B of bf16 1.0: a constant [16 samples x 8] operand (any layout of all-ones is all-ones)
+constexpr uint32_t SW_TOTAL = SW_ONES + 256;
 static_assert(SW_TOTAL <= 232448, "shared memory budget");
 
 struct WgPart { uint32_t slot_off, gs; uint16_t n, tm_col; uint8_t ws, pad[3]; };
@@ -1108,7 +1109,11 @@ struct WgJob {
   // (16 columns of per-sample head gradients); the MMA still has M = 128, rows past the image's width are never flushed.
   uint32_t p2_slot_off, p2_gs;
   uint16_t p2_n, p2_tm_col, p2_qcol0;
-  uint8_t p2_on, p2_ws, p2_q, pad2[3];
+  uint8_t p2_on, p2_ws, p2_q;
+  // bias gradient db[m] = sum_s P[s][m] as a product with a CONSTANT all-ones operand kept in shared memory (column ones_tm_col of
+  // TMEM): the 256-wide layers used to stream the 8 KB `aux` image of every ray just for its ones column (6 % of the kernel's reads)
+  uint8_t ones_on;
+  uint16_t ones_tm_col;
 };
 __constant__ WgJob c_wg_jobs[WG_MAX_JOBS];
 
@@ -1151,6 +1156,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(192, 1) tc_wgrad_ker
     mbar_init(bar_done, 1);
     mbar_fence_init();
   }
+  if (threadIdx.x < 64) reinterpret_cast<uint32_t *>(smem + SW_ONES)[threadIdx.x] = 0x3F803F80u;   // bf16 {1.0, 1.0}
+  fence_async_smem();   // generic-proxy stores -> visible to the tensor core's operand reads
   if (warp == 5 && active) tmem_alloc(smem_u32(tmem_slot), 512);
   tc_fence_before();
   __syncthreads();
@@ -1213,6 +1220,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(192, 1) tc_wgrad_ker
       const bool p2_on = J.p2_on != 0;
       const uint32_t p2_gs = J.p2_gs, p2_tm = tmem + J.p2_tm_col, p2_idesc = idesc_bf16(128, p2_on ? J.p2_n : 16, 1, 1);
       const uint32_t p2_b = p2_on ? q_off[J.p2_q] + (J.p2_qcol0 >> 3) * 128u : 0, p2_bgs = p2_on ? J.q[J.p2_q].gs : 0;
+      const bool ones_on = J.ones_on != 0;
+      const uint32_t ones_tm = tmem + J.ones_tm_col, ones_idesc = idesc_bf16(128, 8, 1, 1);
+      const uint64_t ones_desc = desc_mnmajor(sbase + SW_ONES, 128);   // 2 x 128 B: the two 8-sample groups of a k-step
       for (int t = t0; t < t1; ++t)
         for (int sub = 0; sub < WG_SUB; ++sub) {
           mbar_wait(bar_full + 8 * slot, phase);
@@ -1225,6 +1235,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(192, 1) tc_wgrad_ker
             for (int q = 0; q < 3; ++q)
               if (q < n_parts) umma(qtm[q], pd, desc_mnmajor(src + q_off[q] + ks * 2 * qgs[q], qgs[q]), qn_idesc[q], accum);
             if (p2_on) umma(p2_tm, desc_mnmajor(src + p2_off + ks * 2 * p2_gs, p2_gs), desc_mnmajor(src + p2_b + ks * 2 * p2_bgs, p2_bgs), p2_idesc, accum);
+            if (ones_on) umma(ones_tm, pd, ones_desc, ones_idesc, accum);
             accum = 1;
           }
           if (shared) umma_commit_mc(bar_empty + 8 * slot, mc_mask);   // the slot is free once BOTH consumers are done
@@ -1302,29 +1313,30 @@ WgPlan build_wg_plan() {
       WgJob J{};
       const int wp = P_L0 + 2 * L;
       J.p_ws = 1; J.p_slot_off = BW_DY + (uint32_t)L * 65536u + (uint32_t)h * 32768u; J.p_gs = 2048; J.p_col0 = 0;
+      // the bias gradient comes from the constant all-ones operand (ones_on), not from the `aux` image's ones column
       if (L == 0) {
-        J.n_parts = 2;
+        J.n_parts = 1;
         J.q[0] = part(0, FW_ENC, 1024, 64, 0);
-        J.q[1] = part(0, FW_AUX, 512, 32, 64);
+        J.ones_on = 1; J.ones_tm_col = 64;
         J.n_segs = 2;
         J.seg[0] = seg(wp, 128 * h * 63, 63, 1, 0, 63);
-        J.seg[1] = seg(wp + 1, 128 * h, 1, 1, 64 + 27, 1);
+        J.seg[1] = seg(wp + 1, 128 * h, 1, 1, 64, 1);
       } else if (L == 4) {
-        J.n_parts = 3;
+        J.n_parts = 2;
         J.q[0] = part(0, FW_H + 3 * 65536u, 4096, 256, 0);
         J.q[1] = part(0, FW_ENC, 1024, 64, 256);
-        J.q[2] = part(0, FW_AUX, 512, 32, 320);
+        J.ones_on = 1; J.ones_tm_col = 320;
         J.n_segs = 3;
         J.seg[0] = seg(wp, 128 * h * 319, 319, 1, 0, 256);
         J.seg[1] = seg(wp, 128 * h * 319 + 256, 319, 1, 256, 63);
-        J.seg[2] = seg(wp + 1, 128 * h, 1, 1, 320 + 27, 1);
+        J.seg[2] = seg(wp + 1, 128 * h, 1, 1, 320, 1);
       } else {
-        J.n_parts = 2;
+        J.n_parts = 1;
         J.q[0] = part(0, FW_H + (uint32_t)(L - 1) * 65536u, 4096, 256, 0);
-        J.q[1] = part(0, FW_AUX, 512, 32, 256);
+        J.ones_on = 1; J.ones_tm_col = 256;
         J.n_segs = 2;
         J.seg[0] = seg(wp, 128 * h * 256, 256, 1, 0, 256);
-        J.seg[1] = seg(wp + 1, 128 * h, 1, 1, 256 + 27, 1);
+        J.seg[1] = seg(wp + 1, 128 * h, 1, 1, 256, 1);
       }
       H[h] = J;
     }
@@ -1335,12 +1347,12 @@ WgPlan build_wg_plan() {
     for (int h = 0; h < 2; ++h) {
       WgJob J{};
       J.p_ws = 1; J.p_slot_off = BW_DYFEAT + (uint32_t)h * 32768u; J.p_gs = 2048; J.p_col0 = 0;
-      J.n_parts = 2;
+      J.n_parts = 1;
       J.q[0] = part(0, FW_H + 7 * 65536u, 4096, 256, 0);
-      J.q[1] = part(0, FW_AUX, 512, 32, 256);
+      J.ones_on = 1; J.ones_tm_col = 256;
       J.n_segs = 2;
       J.seg[0] = seg(P_FEAT, 128 * h * 256, 256, 1, 0, 256);
-      J.seg[1] = seg(P_FEAT + 1, 128 * h, 1, 1, 256 + 27, 1);
+      J.seg[1] = seg(P_FEAT + 1, 128 * h, 1, 1, 256, 1);
       // fc_density weight rides along: sum_s d_raw_den[s] * H7[s][128h + n] (row 3 of the 16-column head-gradient image)
       J.p2_on = 1; J.p2_ws = 1; J.p2_slot_off = BW_DSMALL; J.p2_gs = 256;
       J.p2_q = 0; J.p2_qcol0 = (uint16_t)(128 * h); J.p2_n = 128; J.p2_tm_col = 288;
