@@ -228,3 +228,41 @@ def test_precision_default_and_override(monkeypatch):
     assert mk(cfg["rendering"]).precision == "fp32"
     with pytest.raises(ValueError):
         mk(dict(cfg["rendering"], precision="fp16"))
+
+
+def test_objects_build_from_the_reference_yaml_like_train_py():
+    """train.py:50-158 builds the model stack from configs/default.yaml (+ a scene config).  Every key the drop-in reads must
+    exist in the reference's YAML, and nothing the YAML lacks (precision, ray_choice) may be required.  CPU: construction only."""
+    import yaml
+    ref = os.environ.get("NOPE_REFERENCE_ROOT", "/root/reference")
+    if not os.path.isdir(os.path.join(ref, "configs")):
+        pytest.skip("reference tree not mounted")
+    import model as mdl
+    cfg = yaml.safe_load(open(os.path.join(ref, "configs", "default.yaml")))
+    scene_cfg = yaml.safe_load(open(os.path.join(ref, "configs", "V_KITTI", "intersection_d5.yaml")))
+    for sec, kv in scene_cfg.items():          # dataloading.load_config: the scene file overrides the defaults section by section
+        if isinstance(kv, dict):
+            cfg.setdefault(sec, {}).update(kv)
+    n_views = 8
+    model = mdl.OfficialStaticNerf(cfg)
+    renderer = mdl.Renderer(model, cfg['rendering'], device="cpu")
+    nope_nerf = mdl.get_model(renderer, cfg, device="cpu")
+    opt = torch.optim.Adam(nope_nerf.parameters(), lr=cfg['training']['learning_rate'], weight_decay=cfg['training']['weight_decay'])
+    pose = mdl.LearnPose(n_views, cfg['pose']['learn_R'], cfg['pose']['learn_t'], cfg=cfg, init_c2w=None)
+    opt_pose = torch.optim.Adam(pose.parameters(), lr=cfg['training']['pose_lr'])
+    dist = mdl.Learn_Distortion(n_views, cfg['distortion']['learn_scale'], cfg['distortion']['learn_shift'], cfg)
+    opt_dist = torch.optim.Adam(dist.parameters(), lr=cfg['training']['distortion_lr'])
+    focal = mdl.LearnFocal(cfg['pose']['learn_focal'], cfg['pose']['fx_only'], order=cfg['pose']['focal_order'])
+    trainer = mdl.Trainer(nope_nerf, opt, cfg['training'], device="cpu", optimizer_pose=opt_pose, pose_param_net=pose,
+                          optimizer_focal=None, focal_net=None, optimizer_distortion=opt_dist, distortion_net=dist, cfg_all=cfg)
+    assert renderer.precision in ("bf16", "fp32") and trainer.ray_choice == "feistel" and trainer.use_graph == "auto"
+    assert trainer.n_training_points == cfg['training']['n_training_points']
+    ex = mdl.Extract_Images(renderer, cfg, use_learnt_poses=cfg['pose']['learn_pose'], use_learnt_focal=cfg['pose']['learn_focal'],
+                            device="cpu", render_type=cfg['rendering']['type'])
+    assert list(ex.resolution) == list(cfg['extract_images']['resolution'])
+    ck = mdl.CheckpointIO("/tmp/nnb_ckpt_probe", model=nope_nerf, optimizer=opt)
+    assert focal is not None and ck is not None
+    # the annealing schedule of train.py / model/training.py:204-212 on the YAML's own weights
+    w = trainer.anneal(cfg['training']['pc_weight'][0], cfg['training']['pc_weight'][1], cfg['training']['scheduling_start'],
+                       cfg['training']['annealing_epochs'], cfg['training']['scheduling_start'] + cfg['training']['annealing_epochs'] // 2)
+    assert min(cfg['training']['pc_weight']) <= w <= max(cfg['training']['pc_weight'])
