@@ -1,8 +1,9 @@
 """Loss / Loss_Eval -- drop-in for the reference's model/losses.py.
 
 forward() keeps the reference's signature, zero-weight skipping and its 10 return keys.  Every active term is a
-kernel launch (rgb, depth l1 / invariant, Chamfer, reprojection photometric); the terms whose weights are [0,0] in
-every shipped config (pose smoothness, depth consistency, t-cycle, SSIM) stay plain PyTorch.
+kernel launch (rgb, depth l1 / invariant, Chamfer, reprojection photometric); the terms whose weights are [0,0] / False in
+every shipped config (pose smoothness, depth consistency, t-cycle, the with_ssim mix of the photometric term) stay plain
+PyTorch and are compared with the reference's own methods in tests/test_cpu_dropin.py.
 Differences kept on purpose: tensors follow the inputs' device (no hard-coded .cuda()), and a NaN loss raises
 FloatingPointError (Loss.raise_if_nan, called by the Trainer after every step, one step late so that the read never
 stalls the launch queue) instead of dropping into a debugger (model/losses.py:213-214).
@@ -118,7 +119,10 @@ class Loss(nn.Module):
 
     def get_rgb_s_loss(self, rgb1, rgb2, valid_points):
         if self.cfg['with_ssim']:
-            raise NotImplementedError("with_ssim is False in every shipped config ('next' row)")
+            # False in every shipped config: plain PyTorch, model/losses.py:152-159 with the SSIM branch
+            diff = 0.15 * (rgb1 - rgb2).abs().clamp(0, 1) + 0.85 * compute_ssim_loss(rgb1, rgb2)
+            mask = valid_points.expand_as(diff)
+            return (diff * mask).sum() / mask.sum().clamp_min(1)      # 0 for an empty mask, without a host read
         return _ops.Photometric.apply(rgb1, rgb2, valid_points)
 
     # zero-weight terms: plain PyTorch, same formulas as model/losses.py:105-128,161-162
@@ -211,3 +215,21 @@ class Loss(nn.Module):
             'loss_dist_1st': loss_dist_1st, 'loss_dist_2nd': loss_dist_2nd, 'loss_pc': pc_loss,
             'loss_rgb_s': rgb_s_loss, 'loss_depth_consistency': depth_consistency_loss, 'loss_t_cycle': t_cycle_loss,
         }
+
+
+class SSIM(nn.Module):
+    """model/losses.py:232-261: (1 - SSIM) / 2 on 3 x 3 box windows after a one-pixel reflection pad, clamped to [0, 1].  The
+    reference feeds it the (B, h, w, 3) reprojection tensors as they are, i.e. pooled over its last two axes; so does this."""
+    C1, C2 = 0.01 ** 2, 0.03 ** 2
+
+    def forward(self, x, y):
+        x, y = F.pad(x, (1, 1, 1, 1), mode='reflect'), F.pad(y, (1, 1, 1, 1), mode='reflect')
+        box = lambda t: F.avg_pool2d(t, 3, 1)
+        mx, my = box(x), box(y)
+        vx, vy, cxy = box(x * x) - mx * mx, box(y * y) - my * my, box(x * y) - mx * my
+        num = (2 * mx * my + self.C1) * (2 * cxy + self.C2)
+        den = (mx * mx + my * my + self.C1) * (vx + vy + self.C2)
+        return ((1 - num / den) / 2).clamp(0, 1)
+
+
+compute_ssim_loss = SSIM()

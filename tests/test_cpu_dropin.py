@@ -142,6 +142,19 @@ xy, valid = C.project_to_cam(pc, cm, torch.device("cpu"))
 res["proj"] = {"pc": pc.tolist(), "xy": xy.tolist(), "valid": valid.tolist()}
 v = torch.tensor([0.3, -1.2, 2.0])
 res["skew"] = C.vec2skew(v).tolist()
+# the loss terms the drop-in keeps as plain PyTorch (zero weight / False in every shipped config), model/losses.py:105-162,232-263
+L = ref_harness.load_reference().losses
+lo = L.Loss({"depth_loss_type": "l1", "with_ssim": True, "match_method": "dense"})
+a = torch.rand(1, 9, 11, 3, generator=g); b = (a + 0.2 * torch.randn(1, 9, 11, 3, generator=g)).clamp(0, 1)
+vm = torch.rand(1, 9, 11, 1, generator=g) > 0.3
+tl = torch.randn(6, 3, generator=g)
+d1, d2 = torch.rand(1, 40, generator=g), torch.rand(1, 40, generator=g)
+rt, rtg = P[1:2], P[2:3]
+w1, w2 = lo.get_weight_dist_loss(tl)
+res["terms"] = {"a": a.tolist(), "b": b.tolist(), "vm": vm.tolist(), "tl": tl.tolist(), "d1": d1.tolist(), "d2": d2.tolist(),
+                "ssim_map": L.compute_ssim_loss(a, b).tolist(), "rgb_s": float(lo.get_rgb_s_loss(a, b, vm)),
+                "dist": [float(w1), float(w2)], "dc": [float(lo.get_depth_consistency_loss(d1, d2)), float(lo.get_depth_consistency_loss(d1, d2, d2 * 0.9, d1 * 1.1))],
+                "tc": float(lo.get_t_cycle_loss(rt, rtg))}
 print(json.dumps(res))
 '''
 
@@ -180,6 +193,20 @@ def test_host_helpers_match_the_reference(capsys):
     close(xy, ref["proj"]["xy"])
     assert valid.tolist() == ref["proj"]["valid"]
     close(C.vec2skew(torch.tensor([0.3, -1.2, 2.0])), ref["skew"])
+    # plain-PyTorch loss terms (with_ssim photometric term, pose smoothness, depth consistency, t-cycle)
+    from model import losses as ML
+    t = ref["terms"]
+    lo = ML.Loss({"depth_loss_type": "l1", "with_ssim": True, "match_method": "dense"})
+    a, b, vm = T(t["a"]), T(t["b"]), torch.tensor(t["vm"])
+    close(ML.compute_ssim_loss(a, b), t["ssim_map"])
+    assert abs(float(lo.get_rgb_s_loss(a, b, vm)) - t["rgb_s"]) < 1e-6
+    assert float(lo.get_rgb_s_loss(a, b, torch.zeros_like(vm))) == 0.0
+    w1, w2 = lo.get_weight_dist_loss(T(t["tl"]))
+    assert abs(float(w1) - t["dist"][0]) < 1e-6 and abs(float(w2) - t["dist"][1]) < 1e-6
+    d1, d2 = T(t["d1"]), T(t["d2"])
+    assert abs(float(lo.get_depth_consistency_loss(d1, d2)) - t["dc"][0]) < 1e-5
+    assert abs(float(lo.get_depth_consistency_loss(d1, d2, d2 * 0.9, d1 * 1.1)) - t["dc"][1]) < 1e-5
+    assert abs(float(lo.get_t_cycle_loss(P[1:2], P[2:3])) - t["tc"]) < 1e-5
 
 
 def test_backup_copies_config_and_sources(tmp_path, monkeypatch):
