@@ -429,11 +429,12 @@ class Trainer(object):
                     else:
                         kwargs['rt_12_gt'] = world_mat_gt @ torch.inverse(ref_Rt_gt)
                 if geom is not None:
-                    # the two losses of this branch are evaluated here, on its stream (model/losses.py:111-112)
-                    if weights['pc_weight'] != 0.0:
-                        kwargs['pc_loss_pre'] = self.loss.get_pc_loss(kwargs['X'], kwargs['Y'])
+                    # the two losses of this branch are evaluated here, on its stream (model/losses.py:111-112); the photometric
+                    # term first: the main stream waits for the END of this branch, which then is the Chamfer search's own tail
                     if weights['rgb_s_weight'] != 0.0:
                         kwargs['rgb_s_loss_pre'] = self.loss.get_rgb_s_loss(kwargs['rgb_pc1'], kwargs['rgb_pc1_proj'], kwargs['valid_points'])
+                    if weights['pc_weight'] != 0.0:
+                        kwargs['pc_loss_pre'] = self.loss.get_pc_loss(kwargs['X'], kwargs['Y'])
 
         # Ray choice (model/training.py:277); ranks draw the SAME global batch.  'reference': the reference's own call,
         # torch.randperm(h*w, device)[:n] on the device generator, followed by its torch.rand(1, R, S) (model/rendering.py:190):
