@@ -299,3 +299,71 @@ def get_ndc_rays_fxfy(fxfy, near, rays_o, rays_d):
     d0 = -1. / (1 / fxfy[0]) * (rays_d[..., 0] / rays_d[..., 2] - ox)
     d1 = -1. / (1 / fxfy[1]) * (rays_d[..., 1] / rays_d[..., 2] - oy)
     return (torch.stack([-1. / (1 / fxfy[0]) * ox, -1. / (1 / fxfy[1]) * oy, o2], -1), torch.stack([d0, d1, 1 - o2], -1))
+
+
+# -- helpers the reference's own modules call internally; kept for callers that reach for them by name ---------------------
+def skew_symmetric(w):
+    """(...,3) -> (...,3,3) cross-product matrices (model/common.py:459-465)."""
+    x, y, z = w.unbind(dim=-1)
+    o = torch.zeros_like(x)
+    return torch.stack([o, -z, y, z, o, -x, -y, x, o], dim=-1).reshape(w.shape[:-1] + (3, 3))
+
+
+def _alternating_series(x, first, nth):
+    """sum_i (-1)^i x^(2i) / d_i with d_0 = first and d_i = d_{i-1} (2i + k)(2i + k + 1), k fixed by `first`
+    (1 -> sin x / x, 2 -> (1 - cos x) / x^2, 6 -> (x - sin x) / x^3): model/common.py:467-490."""
+    k = {1.0: 0, 2.0: 1, 6.0: 2}[float(first)]
+    total, denom, x2 = torch.zeros_like(x), float(first), x * x
+    power = torch.ones_like(x)
+    for i in range(nth + 1):
+        if i > 0:
+            denom *= (2 * i + k) * (2 * i + k + 1)
+            power = power * x2
+        total = total + (-1) ** i * power / denom
+    return total
+
+
+def taylor_A(x, nth=10):
+    return _alternating_series(x, 1.0, nth)
+
+
+def taylor_B(x, nth=10):
+    return _alternating_series(x, 2.0, nth)
+
+
+def taylor_C(x, nth=10):
+    return _alternating_series(x, 6.0, nth)
+
+
+def check_weights(params):
+    """Warn about NaNs in a state dict (model/common.py:240-248)."""
+    import logging
+    for name, value in params.items():
+        if torch.isnan(value).any():
+            logging.getLogger(__name__).warning('NaN Values detected in model weight %s.' % name)
+
+
+def check_tensor(tensor, tensorname='', input_tensor=None):
+    """Warn about NaNs in a tensor (model/common.py:251-262)."""
+    import logging
+    if torch.isnan(tensor).any():
+        log = logging.getLogger(__name__)
+        log.warning('Tensor %s contains nan values.' % tensorname)
+        if input_tensor is not None:
+            log.warning('Input was: %s' % (input_tensor,))
+
+
+def reprojection(pixels, depth, Rt_ref, world_mat, camera_mat):
+    """Pixels (B,N,2) with depths of one view -> their image coordinates in a reference view, plus the inside-the-image mask
+    (model/common.py:405-435): K Rt_ref W^-1 K^-1 [x d, y d, d, 1]^T, then the perspective divide."""
+    assert pixels.shape[-1] == 2
+    pixels, was_numpy = to_pytorch(pixels, True)
+    depth, camera_mat, Rt_ref = to_pytorch(depth), to_pytorch(camera_mat), to_pytorch(Rt_ref)
+    d = depth.reshape(1, -1, 1)
+    ones = torch.ones_like(pixels)
+    homog = torch.cat([pixels * d, d.expand(pixels.shape[0], -1, 1), ones[..., :1]], dim=-1).transpose(1, 2)   # (B,4,N)
+    chain = camera_mat @ Rt_ref @ torch.inverse(world_mat) @ torch.inverse(camera_mat)
+    cam = (chain @ homog)[:, :3].transpose(1, 2)
+    xy = cam[..., :2] / cam[..., 2:]
+    valid = (xy.abs().amax(dim=-1) <= 1).unsqueeze(-1).float()
+    return (xy.numpy() if was_numpy else xy), valid

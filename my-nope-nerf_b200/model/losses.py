@@ -117,12 +117,16 @@ class Loss(nn.Module):
         X, Y = Xt[0], Yt[0]  # (P,3) row-major: the layout the kernels want (the reference permutes to (3,P))
         return self._point_point_error_rows(X, Y) + self._point_point_error_rows(Y, X)
 
+    def mean_on_mask(self, diff, valid_mask):
+        """model/losses.py:79-87: mean of `diff` over the masked elements, 0 for an empty mask -- without the host read."""
+        mask = valid_mask.expand_as(diff)
+        return (diff * mask).sum() / mask.sum().clamp_min(1)
+
     def get_rgb_s_loss(self, rgb1, rgb2, valid_points):
         if self.cfg['with_ssim']:
             # False in every shipped config: plain PyTorch (SURVEY.md 8f), model/losses.py:152-159 with the SSIM branch
             diff = 0.15 * (rgb1 - rgb2).abs().clamp(0, 1) + 0.85 * compute_ssim_loss(rgb1, rgb2)
-            mask = valid_points.expand_as(diff)
-            return (diff * mask).sum() / mask.sum().clamp_min(1)      # 0 for an empty mask, without a host read
+            return self.mean_on_mask(diff, valid_points)
         return _ops.Photometric.apply(rgb1, rgb2, valid_points)
 
     # zero-weight terms: plain PyTorch, same formulas as model/losses.py:105-128,161-162

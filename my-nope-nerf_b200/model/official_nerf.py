@@ -78,3 +78,14 @@ class OfficialStaticNerf(nn.Module):
         with torch.no_grad():
             g = _ops.mlp_points_density_grad(self.param_list(), p.reshape(-1, 3))
         return g.unsqueeze(1)
+
+
+def encode_position(input, levels, inc_input):
+    """model/official_nerf.py:99-119 as a stand-alone function: (...,C) -> (..., C * (2 * levels + inc_input)), column order
+    [x, sin(2^0 x), cos(2^0 x), sin(2^1 x), ...].  The render kernels compute the same columns in their prologue
+    (csrc/mlp_tc.cu write_encodings); this one is for callers that want the encoding itself."""
+    freqs = 2.0 ** torch.arange(levels, dtype=input.dtype, device=input.device)
+    ang = input.unsqueeze(-2) * freqs.view(-1, 1)                           # (..., levels, C)
+    waves = torch.stack([ang.sin(), ang.cos()], dim=-2)                     # (..., levels, 2, C)
+    waves = waves.reshape(input.shape[:-1] + (-1,))
+    return torch.cat([input, waves], dim=-1) if inc_input else waves

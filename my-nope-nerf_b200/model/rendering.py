@@ -63,6 +63,43 @@ class Renderer(nn.Module):
                                      n_secant_steps=n_secant_steps, depth_range=depth_range, max_points=max_points,
                                      rad=rad, renderer=self if model is self.model else None).unsqueeze(0)
 
+    def secant(self, f_low, f_high, d_low, d_high, n_secant_steps, ray0_masked, ray_direction_masked, tau, it=0):
+        """Reference signature (model/rendering.py:389-419); the field evaluations are C-ABI kernels (geometry.secant)."""
+        return geometry.secant(self.model, f_low, f_high, d_low, d_high, n_secant_steps, ray0_masked, ray_direction_masked, tau)
+
+    def transform_to_homogenous(self, p):
+        """(B,N,3) -> (B,N,4): [p, 1] / |p| (model/rendering.py:421-426)."""
+        return torch.cat([p, torch.ones_like(p[..., :1])], dim=2) / p.norm(dim=2, keepdim=True)
+
+    # The two sampling routines of the reference (model/rendering.py:169-198) as stand-alone methods.  `nope_nerf` does NOT call
+    # them: sampling is the prologue of the fused render kernels (csrc/mlp_tc.cu z_sample, csrc/render.cu); these exist for callers
+    # that want the sample positions themselves, and tests/test_gpu_edges.py checks the kernels' z values against them.
+    def _sample_points(self, origins, directions, view_dirs, z_val):
+        steps = z_val.shape[-1]
+        pts = (origins.unsqueeze(-2) + directions.unsqueeze(-2) * z_val.unsqueeze(-1)).reshape(-1, 3)
+        view = -view_dirs.unsqueeze(-2).expand(-1, -1, steps, -1).reshape(-1, 3)
+        return z_val.reshape(-1, steps, 1), pts, view
+
+    def sample_uniform(self, camera_world, ray_vector, z_val, add_noise, depth_range, noise=None):
+        """z_val (B,R,S) in [0,1] -> depths in depth_range, jittered inside their strata when add_noise (`noise`: the uniform
+        draws to use instead of torch.rand); returns z (B*R,S,1), points (B*R*S,3), negated view directions (B*R*S,3)."""
+        z_val = depth_range[0] * (1. - z_val) + depth_range[1] * z_val
+        if add_noise:
+            mid = .5 * (z_val[..., 1:] + z_val[..., :-1])
+            lower, upper = torch.cat([z_val[..., :1], mid], dim=-1), torch.cat([mid, z_val[..., -1:]], dim=-1)
+            if noise is None:
+                noise = torch.rand(z_val.shape, device=z_val.device)
+            z_val = lower + (upper - lower) * noise
+        return self._sample_points(camera_world, ray_vector, ray_vector, z_val)
+
+    def sample_ndc(self, camera_mat, camera_world, ray_vector, z_val, depth_range=[0., 1.]):
+        """The LLFF branch: origins and directions warped to NDC (common.get_ndc_rays_fxfy), no jitter."""
+        from .common import get_ndc_rays_fxfy
+        focal = torch.cat([camera_mat[:, 0, 0], camera_mat[:, 1, 1]])
+        o_ndc, d_ndc = get_ndc_rays_fxfy(focal, 1.0, rays_o=camera_world, rays_d=ray_vector)
+        z_val = depth_range[0] * (1. - z_val) + depth_range[1] * z_val
+        return self._sample_points(o_ndc, d_ndc, ray_vector, z_val)
+
     def to(self, device):
         new = super().to(device)
         new._device = device

@@ -155,6 +155,30 @@ res["terms"] = {"a": a.tolist(), "b": b.tolist(), "vm": vm.tolist(), "tl": tl.to
                 "ssim_map": L.compute_ssim_loss(a, b).tolist(), "rgb_s": float(lo.get_rgb_s_loss(a, b, vm)),
                 "dist": [float(w1), float(w2)], "dc": [float(lo.get_depth_consistency_loss(d1, d2)), float(lo.get_depth_consistency_loss(d1, d2, d2 * 0.9, d1 * 1.1))],
                 "tc": float(lo.get_t_cycle_loss(rt, rtg))}
+# helpers the reference's modules call internally (sampling routines, positional encoding, SE(3) series, reprojection)
+REF = ref_harness.load_reference()
+rcfg = {"depth_range": [0.01, 10.0], "n_max_network_queries": 64000, "white_background": False}
+rr = REF.rendering.Renderer(torch.nn.Identity(), rcfg, device=torch.device("cpu"))
+zv = torch.linspace(0., 1., 16).view(1, 1, 16).repeat(1, 5, 1)
+cw = torch.randn(1, 5, 3, generator=g) * 0.1; rv = torch.nn.functional.normalize(torch.randn(1, 5, 3, generator=g), dim=-1)
+rv[..., 2] = -rv[..., 2].abs() - 0.2; cw[..., 2] -= 2.0
+torch.manual_seed(11)
+su = rr.sample_uniform(cw, rv, zv.clone(), True, [0.01, 10.0])
+su0 = rr.sample_uniform(cw, rv, zv.clone(), False, [0.01, 10.0])
+cmat = torch.diag(torch.tensor([1.17, -3.87, -1., 1.])).unsqueeze(0)
+sn = rr.sample_ndc(cmat, cw, rv, zv.clone(), depth_range=[0., 1.])
+x = torch.randn(6, 3, generator=g)
+sm = torch.randn(7, generator=g) * 0.5
+px = torch.rand(1, 12, 2, generator=g) * 1.6 - 0.8
+dd = torch.rand(1, 12, 1, generator=g) + 1.0
+rp, rpv = C.reprojection(px, dd, torch.inverse(P[3]).unsqueeze(0), torch.inverse(P[2]).unsqueeze(0), cm)
+res["internal"] = {"zv": zv.tolist(), "cw": cw.tolist(), "rv": rv.tolist(),
+    "su": [t.tolist() for t in su], "su0": [t.tolist() for t in su0], "sn": [t.tolist() for t in sn],
+    "x": x.tolist(), "enc10": REF.official_nerf.encode_position(x, 10, True).tolist(), "enc4n": REF.official_nerf.encode_position(x, 4, False).tolist(),
+    "homo": rr.transform_to_homogenous(pw).tolist(), "skew": C.skew_symmetric(x).tolist(), "sm": sm.tolist(),
+    "tA": C.taylor_A(sm).tolist(), "tB": C.taylor_B(sm).tolist(), "tC": C.taylor_C(sm).tolist(),
+    "px": px.tolist(), "dd": dd.tolist(), "rp": rp.tolist(), "rpv": rpv.tolist(),
+    "mom": float(lo.mean_on_mask((a - b).abs(), vm))}
 print(json.dumps(res))
 '''
 
@@ -207,6 +231,31 @@ def test_host_helpers_match_the_reference(capsys):
     assert abs(float(lo.get_depth_consistency_loss(d1, d2)) - t["dc"][0]) < 1e-5
     assert abs(float(lo.get_depth_consistency_loss(d1, d2, d2 * 0.9, d1 * 1.1)) - t["dc"][1]) < 1e-5
     assert abs(float(lo.get_t_cycle_loss(P[1:2], P[2:3])) - t["tc"]) < 1e-5
+    # helpers the reference's modules call internally
+    from model import rendering as MR, official_nerf as MN
+    q = ref["internal"]
+    rcfg = {"depth_range": [0.01, 10.0], "n_max_network_queries": 64000, "white_background": False, "num_points": 16, "outside_steps": 0}
+    rr = MR.Renderer(torch.nn.Identity(), rcfg, device=torch.device("cpu"))
+    zv, cw, rv = T(q["zv"]), T(q["cw"]), T(q["rv"])
+    torch.manual_seed(11)
+    for got, want in zip(rr.sample_uniform(cw, rv, zv.clone(), True, [0.01, 10.0]), q["su"]):
+        close(got, want)
+    for got, want in zip(rr.sample_uniform(cw, rv, zv.clone(), False, [0.01, 10.0]), q["su0"]):
+        close(got, want)
+    cmat = torch.diag(torch.tensor([1.17, -3.87, -1., 1.])).unsqueeze(0)
+    for got, want in zip(rr.sample_ndc(cmat, cw, rv, zv.clone(), depth_range=[0., 1.]), q["sn"]):
+        close(got, want)
+    x = T(q["x"])
+    torch.testing.assert_close(MN.encode_position(x, 10, True), T(q["enc10"]), rtol=0, atol=0)
+    torch.testing.assert_close(MN.encode_position(x, 4, False), T(q["enc4n"]), rtol=0, atol=0)
+    close(rr.transform_to_homogenous(T(ref["cam"]["pw"])), q["homo"])
+    close(C.skew_symmetric(x), q["skew"])
+    sm = T(q["sm"])
+    close(C.taylor_A(sm), q["tA"]); close(C.taylor_B(sm), q["tB"]); close(C.taylor_C(sm), q["tC"])
+    rp, rpv = C.reprojection(T(q["px"]), T(q["dd"]), torch.inverse(P[3]).unsqueeze(0), torch.inverse(P[2]).unsqueeze(0), cm)
+    torch.testing.assert_close(rp, T(q["rp"]), rtol=1e-5, atol=1e-5)
+    assert rpv.tolist() == q["rpv"]
+    assert abs(float(lo.mean_on_mask((a - b).abs(), vm)) - q["mom"]) < 1e-6
 
 
 def test_backup_copies_config_and_sources(tmp_path, monkeypatch):

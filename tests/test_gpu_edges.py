@@ -38,6 +38,13 @@ def test_render_forward_backward_at_tiny_and_odd_ray_counts(R, precision):
     ((rgb2 * p_rgb.to(dev())).sum() + (dist2 * p_dist.to(dev())).sum()).backward()
     torch.cuda.synchronize()
     assert torch.equal(z2.cpu(), z), "sample depths must be bit-exact"
+    # ... and equal to what the reference-named stand-alone routine returns for the same draws (model/rendering.py:183-198)
+    import model as mdl
+    rcfg = {"depth_range": [0.01, 10.0], "n_max_network_queries": 64000, "white_background": False, "num_points": 128, "outside_steps": 0}
+    z_ref, pts_ref, view_ref = mdl.Renderer(torch.nn.Identity(), rcfg, device=torch.device("cpu"), precision="fp32").sample_uniform(
+        origin.view(1, 1, 3).expand(1, R, 3), dirs.view(1, R, 3), torch.linspace(0., 1., 128).view(1, 1, 128).repeat(1, R, 1), True, [0.01, 10.0],
+        noise=noise.view(1, R, 128))
+    assert torch.equal(z_ref.view(R, 128), z2.cpu()) and torch.equal(pts_ref, pts.reshape(-1, 3)) and torch.equal(view_ref, (-dirs).view(R, 1, 3).expand(R, 128, 3).reshape(-1, 3))
     ftol = 1e-5 if precision == "fp32" else 1e-3
     assert max_err(rgb2, rgb) <= ftol and max_err(dist2, dist) <= 10 * ftol and max_err(w2, w) <= ftol
     gtol = 2e-4 if precision == "fp32" else 0.3      # a handful of rays: single ReLU-mask flips dominate the bf16 gradient
