@@ -9,22 +9,22 @@ import torch
 
 
 class CheckpointIO(object):
-    def __init__(self, checkpoint_dir='./chkpts', **modules):
+    def __init__(self, checkpoint_dir='./chkpts', **kwargs):
         self.checkpoint_dir = checkpoint_dir
-        self.module_dict = modules
+        self.module_dict = kwargs          # name -> module (or optimiser): everything with a state_dict
         os.makedirs(checkpoint_dir, exist_ok=True)
 
     def _path(self, filename):
         """Relative names live in the checkpoint directory (model/checkpoints.py:30-31,56-57)."""
         return filename if os.path.isabs(filename) else os.path.join(self.checkpoint_dir, filename)
 
-    def register_modules(self, **modules):
-        self.module_dict.update(modules)
+    def register_modules(self, **kwargs):
+        self.module_dict.update(kwargs)
 
-    def save(self, filename, **scalars):
+    def save(self, filename, **kwargs):
         """model/checkpoints.py:29-41: the scalars (epoch_it, it, loss_val_best, ...) next to one state_dict per module."""
         payload = {name: module.state_dict() for name, module in self.module_dict.items()}
-        torch.save({**scalars, **payload}, self._path(filename))
+        torch.save({**kwargs, **payload}, self._path(filename))
 
     def backup_model_best(self, filename, **kwargs):
         """model/checkpoints.py:43-53: a COPY under a timestamp name; model_best.pt itself stays in place."""
