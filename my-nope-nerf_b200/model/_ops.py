@@ -72,17 +72,26 @@ class Distortion(torch.autograd.Function):
         call("nnb_distortion_fwd", ptr(scales), ptr(shifts), int(cam_id), n, int(bool(fix_scaleN)), ptr(out), stream())
         ctx.save_for_backward(scales)
         ctx.args = (int(cam_id), n, int(bool(fix_scaleN)))
+        ctx.set_materialize_grads(False)
         return out
 
     @staticmethod
     def backward(ctx, g):
+        """WHICH parameters receive a gradient follows the reference (torch.optim.Adam skips a parameter whose .grad is None and
+        keeps moving one whose gradient is zero): the pinned scale of the last camera is a constant there (model/distortions.py:
+        23-24), so `global_scales` gets NO gradient from this call, not a zero one.  (The 0.01 clamp of :21-22 is decided on the
+        device here, without the reference's host read: a clamped scale yields a zero row instead of no gradient.)"""
+        if g is None:
+            return None, None, None, None
         (scales,) = ctx.saved_tensors
         cam, n, fix = ctx.args
-        ds, dsh = torch.zeros_like(scales), torch.zeros_like(scales)
+        pinned = bool(fix) and cam == n - 1
+        ds, dsh = (None if pinned else torch.zeros_like(scales)), torch.zeros_like(scales)
         row = _new(scales, 2)
         call("nnb_distortion_bwd", ptr(scales), cam, n, fix, ptr(f32(g)), C.c_void_p(row.data_ptr()),
              C.c_void_p(row.data_ptr() + 4), stream())
-        ds[cam, 0] = row[0]
+        if ds is not None:
+            ds[cam, 0] = row[0]
         dsh[cam, 0] = row[1]
         return ds, dsh, None, None
 
@@ -159,6 +168,7 @@ class GatherRays(torch.autograd.Function):
              ptr(depth), stream())
         ctx.save_for_backward(ray_idx, depth_img if depth_img is not None else torch.empty(0, device=ray_idx.device))
         ctx.has_ss = ss is not None
+        ctx.set_materialize_grads(False)
         ctx.mark_non_differentiable(pixels)
         if rgb is not None:
             ctx.mark_non_differentiable(rgb)
@@ -193,13 +203,16 @@ class RayGen(torch.autograd.Function):
         ctx.has_depth, ctx.normalise = depth is not None, int(bool(normalise))
         ctx.shapes = (camera_mat.shape, world_mat.shape, scale_mat.shape, None)
         ctx.mark_non_differentiable(mask, nrm)
+        ctx.set_materialize_grads(False)   # an unused output arrives as None, not as zeros
         return origin, dirs, nrm, dgt, mask
 
     @staticmethod
     def backward(ctx, g_origin, g_dirs, g_nrm, g_dgt, g_mask):
         pixels, depth, Km, Wm, Sm, A = ctx.saved_tensors
         n = pixels.shape[0]
-        d_depth = _new(pixels, n) if ctx.has_depth else None
+        # the depth input reaches only the ground-truth ray distance (model/rendering.py:65-70): when no loss reads that output
+        # the depth -- and the distortion parameters behind it -- get NO gradient, as in the reference, rather than zeros
+        d_depth = _new(pixels, n) if (ctx.has_depth and g_dgt is not None) else None
         dK, dW, dS = _new(pixels, 4, 4), _new(pixels, 4, 4), _new(pixels, 4, 4)
         scratch = _new(pixels, 16)
         call("nnb_raygen_bwd", ptr(pixels), ptr(depth) if ctx.has_depth else None, ptr(Km), ptr(Wm), ptr(Sm), ptr(A), n, ctx.normalise,

@@ -12,6 +12,7 @@ class DataParallelContext(object):
         self.rank, self.world_size, self.group = rank, world_size, group
         self.timing = None
         self.bytes_per_allreduce = 0
+        self.check_symmetry = os.environ.get('NNB_DP_CHECK', '0') == '1'
 
     @classmethod
     def from_env(cls):
@@ -25,7 +26,7 @@ class DataParallelContext(object):
 
     def allreduce_grads(self, params, extra=()):
         """Average the gradients of `params` across ranks with ONE collective over a flat fp32 buffer.  Parameters whose grad
-        is None on this rank contribute zeros (every rank must pass the same list).  `extra`: scalar tensors (the loss terms of
+        is None occupy a zero slot (so every rank's buffer has the same layout) and stay without gradient afterwards.  `extra`: scalar tensors (the loss terms of
         the step) averaged in place by the same collective.  `self.timing` = [] collects CUDA-event pairs around the call."""
         if self.world_size == 1:
             return
@@ -37,6 +38,15 @@ class DataParallelContext(object):
             ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
             ev[0].record()
         extra = [e for e in extra if torch.is_tensor(e)]
+        if self.check_symmetry:
+            # debugging aid (env NNB_DP_CHECK=1; one extra collective and a host read): every rank must reach the same parameters
+            have = torch.tensor([float(p.grad is not None) for p in params], device=params[0].device)
+            lo, hi = have.clone(), have.clone()
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=self.group)
+            dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=self.group)
+            if not torch.equal(lo, hi):
+                raise RuntimeError("data-parallel ranks disagree on which parameters received a gradient: %s"
+                                   % [i for i, (a, b) in enumerate(zip(lo.tolist(), hi.tolist())) if a != b])
         flat = flatten_grads(params, extra)
         if dist.get_backend(self.group) == 'nccl':
             dist.all_reduce(flat, op=dist.ReduceOp.AVG, group=self.group)     # the average is taken inside the collective
@@ -76,15 +86,16 @@ def flatten_grads(params, extra=()):
 
 
 def unflatten_grads(flat, params, extra=()):
-    views, o = [], 0
+    """Inverse of flatten_grads.  A parameter without a gradient keeps none: which parameters a step reaches is a property of
+    the step (frame pairing, active loss terms), the same on every rank, and the optimisers treat "no gradient" (skipped)
+    differently from a zero one (moments still move) -- as torch.optim.Adam does under the reference."""
+    views, dst, o = [], [], 0
     for p in params:
         n = p.numel()
-        views.append(flat[o:o + n].view_as(p))
+        if p.grad is not None:
+            views.append(flat[o:o + n].view_as(p))
+            dst.append(p.grad)
         o += n
-    missing = [i for i, p in enumerate(params) if p.grad is None]
-    for i in missing:
-        params[i].grad = torch.empty_like(params[i])
-    dst = [p.grad for p in params]
     for e in extra:
         n = e.numel()
         views.append(flat[o:o + n].view_as(e))

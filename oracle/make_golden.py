@@ -428,8 +428,71 @@ def cfg5_vectors(ref, cfg):
     return out
 
 
+TRAJ_STEPS = 12
+TRAJ_SMALL = ("fc_density.weight", "fc_density.bias", "fc_rgb.weight", "fc_rgb.bias", "layers0.0.bias", "layers1.6.bias", "rgb_layers.0.bias")
+
+
+def trajectory_frames(n, t):
+    """(frame, reference frame) of step t: cycles through the frames, the last one pairing with its predecessor."""
+    idx = t % n
+    return idx, (idx + 1 if idx < n - 1 else idx - 1)
+
+
+def trajectory_vectors(ref, cfg):
+    """TRAJ_STEPS consecutive calls of the UNMODIFIED reference's Trainer.train_step (model/training.py:68-100) with three
+    torch.optim.Adam optimisers (train.py:59,100,118) on the tiny scene; ray choice and jitter of every step injected and
+    recorded.  Steps 0-7 run at epoch 0 (l1 colour term, start weights), steps 8-9 in the middle of the annealing window
+    (interpolated weights), steps 10-11 after it (l2 colour term, end weights).  Recorded: every loss term of every step and the parameters after the last one."""
+    scene = syn.make_scene("tiny")
+    n, h, w, R = scene["n"], scene["h"], scene["w"], syn.SHAPES["tiny"][3]
+    sd = syn.init_mlp_state(42)
+    r0, t0 = syn.init_pose_params(n)
+    tcfg = dict(cfg["training"], n_training_points=R)
+    nerf, renderer, net = build_ref_model(ref, cfg, sd)
+    pose_net = ref.model.LearnPose(n, True, True, cfg, init_c2w=scene["poses_gt"].clone())
+    dist_net = ref.model.Learn_Distortion(n, True, True, cfg)
+    scales = 1.0 + 0.05 * torch.arange(n, dtype=torch.float32).view(n, 1)
+    shifts = 0.01 * torch.arange(n, dtype=torch.float32).view(n, 1)
+    with torch.no_grad():
+        pose_net.r.copy_(r0)
+        pose_net.t.copy_(t0)
+        dist_net.global_scales.copy_(scales)
+        dist_net.global_shifts.copy_(shifts)
+    lrs = {"model": tcfg["learning_rate"], "pose": tcfg["pose_lr"], "distortion": tcfg["distortion_lr"]}
+    trainer = ref.model.Trainer(net, torch.optim.Adam(net.parameters(), lr=lrs["model"]), tcfg, device=torch.device("cpu"),
+                                optimizer_pose=torch.optim.Adam(pose_net.parameters(), lr=lrs["pose"]), pose_param_net=pose_net,
+                                optimizer_distortion=torch.optim.Adam(dist_net.parameters(), lr=lrs["distortion"]), distortion_net=dist_net)
+    g = torch.Generator().manual_seed(77)
+    sched = tcfg["scheduling_start"]
+    steps = []
+    for t in range(TRAJ_STEPS):
+        idx, ref_idx = trajectory_frames(n, t)
+        epoch = 0 if t < 8 else (sched + tcfg["annealing_epochs"] // 2 if t < 10 else sched + tcfg["annealing_epochs"] + 1)
+        perm = torch.randperm(h * w, generator=g)
+        noise = torch.rand(1, R, 128, generator=g)
+        with injected_draws(noise=noise, perm=perm):
+            ld = trainer.train_step(syn.make_batch(scene, idx, ref_idx), it=t, epoch=epoch, scheduling_start=sched, render_path="/tmp")
+        steps.append({"idx": idx, "ref": ref_idx, "epoch": epoch, "ray_idx": perm[:R].clone(), "noise": noise.reshape(R, 128).clone(),
+                      "loss_dict": {k: v.detach().clone().reshape(-1) for k, v in ld.items()},
+                      # parameters AFTER this step's optimiser updates (small tensors only)
+                      "after": {"r": pose_net.r.detach().clone(), "t": pose_net.t.detach().clone(),
+                                "scales": dist_net.global_scales.detach().clone(), "shifts": dist_net.global_shifts.detach().clone(),
+                                **{k: v.detach().clone() for k, v in nerf.named_parameters() if k in TRAJ_SMALL}}})
+        print("trajectory step", t, idx, ref_idx, epoch, {k: round(float(v.reshape(-1)[0]), 6) for k, v in ld.items()}, flush=True)
+    return {"steps": steps, "lrs": lrs, "setup": {"scales": scales, "shifts": shifts, "r": r0, "t": t0},
+            "final": {"r": pose_net.r.detach().clone(), "t": pose_net.t.detach().clone(),
+                      "scales": dist_net.global_scales.detach().clone(), "shifts": dist_net.global_shifts.detach().clone(),
+                      "mlp_stats": {k: flat_stats(v.detach()) for k, v in nerf.named_parameters()},
+                      "mlp_small": {k: v.detach().clone() for k, v in nerf.named_parameters() if k in TRAJ_SMALL}}}
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
+    if "--trajectory" in sys.argv:
+        ref = ref_harness.load_reference()
+        torch.set_num_threads(max(1, os.cpu_count() or 1))
+        torch.save(trajectory_vectors(ref, syn.default_cfg()), os.path.join(OUT, "trajectory.pt"))
+        return
     if "--cfg2" in sys.argv or "--cfg5" in sys.argv:
         ref = ref_harness.load_reference()
         torch.set_num_threads(max(1, os.cpu_count() or 1))

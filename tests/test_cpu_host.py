@@ -225,18 +225,28 @@ def _gloo_worker(rank, world, port, out_dir):
     lo, hi = dp.shard(idx.numel())
     got = dp.gather_rows(idx[lo:hi].reshape(-1, 1).float(), idx.numel()).reshape(-1).long()
     assert torch.equal(got, idx)
-    # gradient averaging over one flat buffer; a param without grad on one rank contributes zeros
+    # gradient averaging over one flat buffer; a parameter the step did not reach (no gradient on any rank) keeps none, so
+    # that the optimiser skips it as torch.optim.Adam does under the reference (tests/test_gpu_trajectory.py)
     torch.manual_seed(0)
     ps = [torch.nn.Parameter(torch.randn(3, 5)), torch.nn.Parameter(torch.randn(7)), torch.nn.Parameter(torch.randn(2))]
     ps[0].grad = torch.full((3, 5), float(rank + 1))
     ps[1].grad = torch.arange(7.0) * (rank + 1)
-    if rank == 0:
-        ps[2].grad = torch.ones(2)
+    dp.check_symmetry = True
     dp.allreduce_grads(ps)
     mean = sum(r + 1 for r in range(world)) / world
     assert torch.allclose(ps[0].grad, torch.full((3, 5), mean))
     assert torch.allclose(ps[1].grad, torch.arange(7.0) * mean)
-    assert torch.allclose(ps[2].grad, torch.ones(2) / world)
+    assert ps[2].grad is None
+    # ranks that disagree on which parameters have a gradient are a bug upstream: the check names the parameter
+    if rank == 0:
+        ps[2].grad = torch.ones(2)
+    try:
+        dp.allreduce_grads(ps)
+        raise AssertionError("asymmetric gradients not reported")
+    except RuntimeError as e:
+        assert "[2]" in str(e)
+    ps[2].grad = None
+    dp.check_symmetry = False
     # Chamfer with the SOURCE points sharded by rank: averaging the ranks' terms and gradients must give the
     # one-rank loss and gradient.  The two kernels are replaced by torch stand-ins: this checks the host-side sharding.
     from model import _ops, losses

@@ -61,8 +61,11 @@ def _compare(tag, rec, ld, nerf, pose, dist, loss_tol, grad_tol, mlp_tol, stat_t
         print("%s %-12s got %.8f  reference %.8f  rel %.2e" % (tag, k, got, want, errs["loss/" + k]))
         assert errs["loss/" + k] <= loss_tol, (tag, k, got, want)
     pairs = [("grad_r", pose.r.grad, rec["grad_r"]), ("grad_t", pose.t.grad, rec["grad_t"])]
-    if rec["grad_scales"] is not None:
-        pairs += [("grad_scales", dist.global_scales.grad, rec["grad_scales"]), ("grad_shifts", dist.global_shifts.grad, rec["grad_shifts"])]
+    for gname, p, want in (("grad_scales", dist.global_scales, rec["grad_scales"]), ("grad_shifts", dist.global_shifts, rec["grad_shifts"])):
+        if want is None:   # e.g. the pinned scale of the last frame: no gradient, so torch.optim.Adam skips the parameter
+            assert p.grad is None, "%s: the reference leaves %s without gradient" % (tag, gname)
+        else:
+            pairs.append((gname, p.grad, want))
     for name, got, want in pairs:
         e = _rel(got, want)
         print("%s %-12s scale-relative err %.2e" % (tag, name, e))
