@@ -486,12 +486,52 @@ def trajectory_vectors(ref, cfg):
                       "mlp_small": {k: v.detach().clone() for k, v in nerf.named_parameters() if k in TRAJ_SMALL}}}
 
 
+POSEFIT_STEPS = 8
+
+
+def posefit_vectors(ref, cfg):
+    """POSEFIT_STEPS calls of the UNMODIFIED reference's Trainer_pose.train_step (model/eval_pose_one_epoch.py:25-98: the test-time
+    pose fit of evaluation/eval.py:122-137 -- MLP in eval mode, colour MSE, one Adam on the poses) on the tiny scene, poses
+    started away from the truth; the ray choice of every step injected and recorded."""
+    scene = syn.make_scene("tiny")
+    n, h, w, R = scene["n"], scene["h"], scene["w"], syn.SHAPES["tiny"][3]
+    sd = syn.init_mlp_state(42)
+    r0, t0 = syn.init_pose_params(n)
+    nerf, renderer, net = build_ref_model(ref, cfg, sd)
+    pose_net = ref.model.LearnPose(n, True, True, cfg, init_c2w=scene["poses_gt"].clone())
+    with torch.no_grad():
+        pose_net.r.copy_(r0)
+        pose_net.t.copy_(t0)
+    lr = 1e-3
+    trainer = ref.model.Trainer_pose(net, {"n_points": R, "type": "nope_nerf"}, device=torch.device("cpu"),
+                                     optimizer_pose=torch.optim.Adam(pose_net.parameters(), lr=lr), pose_param_net=pose_net)
+    g = torch.Generator().manual_seed(78)
+    steps = []
+    for t in range(POSEFIT_STEPS):
+        idx = t % n
+        batch = syn.make_batch(scene, idx, (idx + 1) % n)
+        data = {"img": batch["img"], "img.idx": batch["img.idx"], "img.camera_mat": batch["img.camera_mat"], "img.scale_mat": batch["img.scale_mat"]}
+        if t >= POSEFIT_STEPS // 2:
+            data["img.depth"] = batch["img.dpt"]        # optional key (model/eval_pose_one_epoch.py:56): both forms
+        perm = torch.randperm(h * w, generator=g)
+        with injected_draws(perm=perm):
+            ld = trainer.train_step(data)
+        steps.append({"idx": idx, "ray_idx": perm[:R].clone(), "with_depth": "img.depth" in data, "loss": ld["loss"].detach().clone().reshape(-1),
+                      "r": pose_net.r.detach().clone(), "t": pose_net.t.detach().clone()})
+        print("posefit step", t, idx, float(ld["loss"]), flush=True)
+    grads = {k: (v.grad is not None) for k, v in nerf.named_parameters()}
+    return {"steps": steps, "lr": lr, "setup": {"r": r0, "t": t0}, "mlp_has_grad": grads}
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
-    if "--trajectory" in sys.argv:
+    if "--trajectory" in sys.argv or "--posefit" in sys.argv:
         ref = ref_harness.load_reference()
         torch.set_num_threads(max(1, os.cpu_count() or 1))
-        torch.save(trajectory_vectors(ref, syn.default_cfg()), os.path.join(OUT, "trajectory.pt"))
+        if "--trajectory" in sys.argv:
+            torch.save(trajectory_vectors(ref, syn.default_cfg()), os.path.join(OUT, "trajectory.pt"))
+        if "--posefit" in sys.argv:
+            torch.save(posefit_vectors(ref, syn.default_cfg()), os.path.join(OUT, "posefit.pt"))
         return
     if "--cfg2" in sys.argv or "--cfg5" in sys.argv:
         ref = ref_harness.load_reference()

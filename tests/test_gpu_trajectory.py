@@ -125,3 +125,42 @@ def test_bf16_graphed_steps_track_the_reference_trajectory(golden):
         err, moved = float((got.detach().cpu() - want).abs().max()), _moved(want, start)
         print("  %-6s moved %.3e, differs from the reference by %.3e" % (name, moved, err))
         assert err <= 0.25 * moved, name
+
+
+@pytest.mark.parametrize("precision,loss_tol,pose_tol", [("fp32", 5e-6, 5e-3), ("bf16", 2e-3, 0.25)])
+def test_pose_fit_steps_stay_on_the_reference_trajectory(golden, precision, loss_tol, pose_tol):
+    """The test-time pose fit (evaluation/eval.py:122-137 -> model/eval_pose_one_epoch.py): eight steps of the unmodified
+    reference's Trainer_pose.train_step (tests/golden/posefit.pt), with and without the optional `img.depth` key.
+    Measured on B200: fp32 loss 1.1e-7, r 8e-7 / t 4.5e-6 of a 4.7e-3 displacement; bf16 loss 4.5e-5, r 1.2e-4 / t 3.3e-4."""
+    import model as mdl
+    g = golden("posefit")
+    cfg = syn.default_cfg()
+    scene = syn.make_scene("tiny")
+    n, R = scene["n"], syn.SHAPES["tiny"][3]
+    s = g["setup"]
+    nerf, renderer, net, pose, dist = build_models(cfg, n, scene, precision=precision, r0=s["r"], t0=s["t"])
+    tr = mdl.Trainer_pose(net, {"n_points": R, "type": "nope_nerf"}, device=dev(),
+                          optimizer_pose=torch.optim.Adam(pose.parameters(), lr=g["lr"]), pose_param_net=pose)
+    real_randperm = torch.randperm
+    worst = 0.0
+    try:
+        for t, rec in enumerate(g["steps"]):
+            batch = syn.make_batch(scene, rec["idx"], (rec["idx"] + 1) % n)
+            data = {"img": batch["img"], "img.idx": batch["img.idx"], "img.camera_mat": batch["img.camera_mat"], "img.scale_mat": batch["img.scale_mat"]}
+            if rec["with_depth"]:
+                data["img.depth"] = batch["img.dpt"]
+            head = rec["ray_idx"]
+            torch.randperm = lambda m, device=None, **kw: torch.cat([head, torch.zeros(m - head.numel(), dtype=torch.long)]).to(device)   # this step's recorded choice
+            ld = tr.train_step(data)
+            got, want = float(ld["loss"].detach()), float(rec["loss"])
+            worst = max(worst, abs(got - want) / want)
+            assert abs(got - want) <= loss_tol * want, (t, got, want)
+            moved = float((rec["r"] - s["r"]).abs().max())
+            for name, p in (("r", pose.r), ("t", pose.t)):
+                err = float((p.detach().cpu() - rec[name]).abs().max())
+                assert err <= pose_tol * moved + 1e-7, (t, name, err, moved)
+    finally:
+        torch.randperm = real_randperm
+    print("%s pose fit: worst relative loss error %.2e; r differs by %.2e, t by %.2e after %d steps (moved %.2e)" % (
+        precision, worst, float((pose.r.detach().cpu() - g["steps"][-1]["r"]).abs().max()),
+        float((pose.t.detach().cpu() - g["steps"][-1]["t"]).abs().max()), len(g["steps"]), moved))
