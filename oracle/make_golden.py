@@ -523,11 +523,54 @@ def posefit_vectors(ref, cfg):
     return {"steps": steps, "lr": lr, "setup": {"r": r0, "t": t0}, "mlp_has_grad": grads}
 
 
+def extract_vectors(ref, cfg):
+    """The UNMODIFIED reference's Extract_Images.generate_images (model/extracting_images.py:39-131, the body of the loop in
+    vis/render.py:104-109) on two frames of the tiny scene: the returned img / depth / disp arrays, the raw depth it saves as
+    .npy, and the relative paths of everything it writes (imageio.imwrite and np.save are recorded instead of touching disk)."""
+    import importlib
+    import tempfile
+    import numpy as np
+    written = []
+    sys.modules["imageio"].imwrite = lambda path, arr: written.append((path, np.array(arr)))
+    ref_ex = importlib.import_module("model.extracting_images")
+    scene = syn.make_scene("tiny")
+    n, h, w = scene["n"], scene["h"], scene["w"]
+    nerf, renderer, net = build_ref_model(ref, cfg, syn.init_mlp_state(42))
+    r0, t0 = syn.init_pose_params(n)
+    pose_net = ref.model.LearnPose(n, True, True, cfg, init_c2w=scene["poses_gt"].clone())
+    with torch.no_grad():
+        pose_net.r.copy_(r0)
+        pose_net.t.copy_(t0)
+        c2ws = torch.stack([pose_net(i) for i in range(n)])
+    ex = ref_ex.Extract_Images(renderer, {"extract_images": {"resolution": [h, w]}}, use_learnt_poses=True, use_learnt_focal=False,
+                               device=torch.device("cpu"), render_type="nope_nerf")
+    out = {"c2ws": c2ws, "frames": {}}
+    o_save = np.save
+    with tempfile.TemporaryDirectory() as tmp:
+        for i in (0, 2):
+            del written[:]
+            saved = []
+            np.save = lambda path, arr: saved.append((path, np.array(arr)))
+            try:
+                data = {"img.camera_mat": scene["camera_mat"], "img.scale_mat": scene["scale_mat"], "img.idx": torch.tensor([i])}
+                d = ex.generate_images(data, tmp, c2ws, None, 1000, False)
+            finally:
+                np.save = o_save
+            out["frames"][i] = {"img": torch.from_numpy(np.ascontiguousarray(d["img"])), "depth": torch.from_numpy(np.ascontiguousarray(d["depth"])),
+                                "disp": torch.from_numpy(np.ascontiguousarray(d["disp"])), "geo_is_none": d["geo"] is None,
+                                "depth_raw": torch.from_numpy(saved[0][1]),
+                                "paths": sorted(os.path.relpath(p, tmp) for p, _ in written + saved)}
+            print("extract frame", i, out["frames"][i]["paths"], float(saved[0][1].mean()), flush=True)
+    return out
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
-    if "--trajectory" in sys.argv or "--posefit" in sys.argv:
+    if "--trajectory" in sys.argv or "--posefit" in sys.argv or "--extract" in sys.argv:
         ref = ref_harness.load_reference()
         torch.set_num_threads(max(1, os.cpu_count() or 1))
+        if "--extract" in sys.argv:
+            torch.save(extract_vectors(ref, syn.default_cfg()), os.path.join(OUT, "extract.pt"))
         if "--trajectory" in sys.argv:
             torch.save(trajectory_vectors(ref, syn.default_cfg()), os.path.join(OUT, "trajectory.pt"))
         if "--posefit" in sys.argv:

@@ -164,3 +164,40 @@ def test_pose_fit_steps_stay_on_the_reference_trajectory(golden, precision, loss
     print("%s pose fit: worst relative loss error %.2e; r differs by %.2e, t by %.2e after %d steps (moved %.2e)" % (
         precision, worst, float((pose.r.detach().cpu() - g["steps"][-1]["r"]).abs().max()),
         float((pose.t.detach().cpu() - g["steps"][-1]["t"]).abs().max()), len(g["steps"]), moved))
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_generate_images_matches_the_reference_frames_and_files(golden, tmp_path, precision):
+    """vis/render.py:104-109 -> Extract_Images.generate_images: the img / depth / disp arrays, the raw depth .npy and the file
+    names against what the UNMODIFIED reference returns and writes for two frames (tests/golden/extract.pt)."""
+    import os
+    import numpy as np
+    import model as mdl
+    g = golden("extract")
+    cfg = syn.default_cfg()
+    scene = syn.make_scene("tiny")
+    h, w = scene["h"], scene["w"]
+    nerf, renderer, net, pose, dist = build_models(cfg, scene["n"], scene, precision=precision)
+    ex = mdl.Extract_Images(renderer, {"extract_images": {"resolution": [h, w]}}, use_learnt_poses=True, use_learnt_focal=False,
+                            device=dev(), render_type="nope_nerf")
+    for i, want in g["frames"].items():
+        data = {"img.camera_mat": scene["camera_mat"], "img.scale_mat": scene["scale_mat"], "img.idx": torch.tensor([i])}
+        out_dir = tmp_path / ("frame%d" % i)
+        got = ex.generate_images(data, str(out_dir), g["c2ws"].to(dev()), None, 1000, False)
+        paths = sorted(os.path.relpath(os.path.join(r, f), out_dir) for r, _, fs in os.walk(out_dir) for f in fs)
+        assert paths == want["paths"], (paths, want["paths"])
+        raw = np.load(out_dir / "depth_out" / ("%d.npy" % i))
+        rel = float(np.abs(raw - want["depth_raw"].numpy()).max() / np.abs(want["depth_raw"].numpy()).max())
+        d_img = np.abs(got["img"].astype(np.int32) - want["img"].numpy().astype(np.int32))
+        d_dep = np.abs(got["depth"].astype(np.int32) - want["depth"].numpy().astype(np.int32))
+        d_disp = np.abs(got["disp"].astype(np.int32) - want["disp"].numpy().astype(np.int32))
+        print("%s frame %d: raw depth rel %.2e; uint8 img max diff %d (%.2f %% of values differ), depth %d, disp %d" % (
+            precision, i, rel, d_img.max(), 100.0 * (d_img > 0).mean(), d_dep.max(), d_disp.max()))
+        assert got["geo"] is None and want["geo_is_none"]
+        assert got["img"].dtype == np.uint8 and got["img"].shape == (h, w, 3) and got["depth"].shape == (h, w) and got["disp"].shape == (h, w, 3)
+        if precision == "fp32":
+            # a value within 1e-6 of a quantisation step may land on the other side: at most one level, on few pixels
+            assert rel <= 1e-5 and d_img.max() <= 1 and (d_img > 0).mean() <= 0.01 and d_dep.max() <= 1
+            assert d_disp.max() <= 12          # one step of the 256-entry inferno table moves a channel by up to ~10
+        else:
+            assert rel <= 5e-3 and d_img.max() <= 3 and d_dep.max() <= 4
