@@ -11,9 +11,11 @@ import contextlib
 import logging
 import os
 
+import numpy as np
 import torch
 
 from . import _cabi, _ops, parallel
+from .extracting_images import _imwrite
 from .losses import Loss
 
 logger_py = logging.getLogger(__name__)
@@ -513,20 +515,31 @@ class Trainer(object):
         return loss_dict
 
     def render_visdata(self, data, resolution, it, out_render_path):
-        """Full-frame preview render (model/training.py:103-165) -> uint8 (h,w,3) image; file output is left to the caller."""
+        """Full-frame preview (model/training.py:103-165, called by train.py:239 every `visualize_every` iterations): renders frame
+        `img.idx` at `resolution`, writes `<idx>_depth.png` (min-max normalised), `<idx>_img.png` and -- with `vis_geo`, the
+        default -- `<idx>_geo.png` (phong-shaded sphere-traced surface) into `out_render_path`, and returns the last image
+        written as uint8 (h,w,3), like the reference."""
         (img, depth_input, camera_mat, scale_mat, img_idx, *other) = self.process_data_dict(data)
         h, w = resolution
-        c2w = self.pose_param_net(int(img_idx))
+        idx = int(img_idx)
+        c2w = self.pose_param_net(idx)
         world_mat = _ops.Mat4Inverse.apply(c2w.detach()).unsqueeze(0)
         _, pixels = _ops.pixel_grid(h, w, self.device)
         with torch.no_grad():
             out = self.model.renderer(pixels.unsqueeze(0), torch.ones(1, h * w, 1, device=self.device), camera_mat, world_mat,
                                       scale_mat, self.rendering_technique, add_noise=False, eval_=True, it=it)
-        rgb = out['rgb'].view(h, w, 3)
+        img_out = (out['rgb'].view(h, w, 3) * 255).to(torch.uint8).cpu().numpy()
+        depth = out['depth_pred'].view(h, w).cpu().numpy()
+        depth_u8 = np.clip(255.0 / depth.max() * (depth - depth.min()), 0, 255).astype(np.uint8)
+        dp_rank = self.dp.rank if self.dp is not None else 0
+        if out_render_path is not None and dp_rank == 0:
+            _imwrite(os.path.join(out_render_path, '%04d_depth.png' % idx), depth_u8)
+            _imwrite(os.path.join(out_render_path, '%04d_img.png' % idx), img_out)
         if self.vis_geo:
-            # model/training.py:146-163: the phong-shaded geometry image is what the reference returns when vis_geo is on
             with torch.no_grad():
                 geo = self.model(pixels.unsqueeze(0), None, camera_mat, world_mat, scale_mat, 'phong_renderer', add_noise=False,
                                  eval_mode=True, it=it, depth_img=depth_input, img_size=(h, w))['rgb']
-            rgb = geo.view(h, w, 3)
-        return (rgb * 255).to(torch.uint8).cpu().numpy()
+            img_out = (geo.view(h, w, 3) * 255).to(torch.uint8).cpu().numpy()
+            if out_render_path is not None and dp_rank == 0:
+                _imwrite(os.path.join(out_render_path, '%04d_geo.png' % idx), img_out)
+        return img_out

@@ -561,6 +561,21 @@ def extract_vectors(ref, cfg):
                                 "depth_raw": torch.from_numpy(saved[0][1]),
                                 "paths": sorted(os.path.relpath(p, tmp) for p, _ in written + saved)}
             print("extract frame", i, out["frames"][i]["paths"], float(saved[0][1].mean()), flush=True)
+    # Trainer.render_visdata (model/training.py:103-165; train.py:239): the preview of one frame with vis_geo on (the default)
+    from PIL import Image
+    tcfg = dict(cfg["training"], vis_geo=True)
+    _, _, net_geo = build_ref_model(ref, cfg, geometry_state(syn.init_mlp_state(42)))     # a field WITH surfaces
+    pose_vis = ref.model.LearnPose(n, True, True, cfg, init_c2w=scene["poses_gt"].clone())   # r = t = 0: the cameras of geometry.pt, which see surfaces
+    trainer = ref.model.Trainer(net_geo, None, tcfg, device=torch.device("cpu"), pose_param_net=pose_vis)
+    res = [12, 16]
+    with tempfile.TemporaryDirectory() as tmp:
+        del written[:]
+        ret = trainer.render_visdata(syn.make_batch(scene, 1, 2), res, 1000, tmp)
+        files = {f: torch.from_numpy(np.array(Image.open(os.path.join(tmp, f)))) for f in sorted(os.listdir(tmp))}
+        for path, arr in written:
+            files[os.path.relpath(path, tmp)] = torch.from_numpy(arr)
+    out["visdata"] = {"resolution": res, "idx": 1, "returned": torch.from_numpy(np.ascontiguousarray(ret)), "files": files}
+    print("visdata", {k: tuple(v.shape) for k, v in files.items()}, ret.shape, float(ret.mean()), flush=True)
     return out
 
 

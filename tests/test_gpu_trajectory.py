@@ -201,3 +201,40 @@ def test_generate_images_matches_the_reference_frames_and_files(golden, tmp_path
             assert d_disp.max() <= 12          # one step of the 256-entry inferno table moves a channel by up to ~10
         else:
             assert rel <= 5e-3 and d_img.max() <= 3 and d_dep.max() <= 4
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_render_visdata_writes_and_returns_what_the_reference_does(golden, tmp_path, precision):
+    """train.py:239 -> Trainer.render_visdata with vis_geo on (configs/default.yaml:116): the three PNGs and the returned image
+    against the unmodified reference's (tests/golden/extract.pt 'visdata'; a field with surfaces, see oracle geometry_state)."""
+    import os
+    import numpy as np
+    import model as mdl
+    from PIL import Image
+    g = golden("extract")["visdata"]
+    cfg = syn.default_cfg()
+    scene = syn.make_scene("tiny")
+    sd = syn.init_mlp_state(42)
+    sd["fc_density.weight"] = sd["fc_density.weight"] * 200.0     # oracle/make_golden.py::geometry_state
+    sd["fc_density.bias"] = torch.tensor([0.86])
+    nerf, renderer, net, pose, dist = build_models(cfg, scene["n"], scene, precision=precision, state=sd)    # poses: r = t = 0 on the true ones
+    tr = mdl.Trainer(net, None, dict(cfg["training"], vis_geo=True), device=dev(), pose_param_net=pose)
+    ret = tr.render_visdata(syn.make_batch(scene, g["idx"], 2), g["resolution"], 1000, str(tmp_path))
+    assert sorted(os.listdir(tmp_path)) == sorted(g["files"].keys())
+    assert ret.dtype == np.uint8 and ret.shape == tuple(g["returned"].shape)
+    diffs = {"returned": np.abs(ret.astype(np.int32) - g["returned"].numpy().astype(np.int32))}
+    for f, want in g["files"].items():
+        got = np.array(Image.open(tmp_path / f))
+        assert got.shape == tuple(want.shape), f
+        diffs[f] = np.abs(got.astype(np.int32) - want.numpy().astype(np.int32))
+    print(precision, {k: (int(v.max()), "%.1f %%" % (100.0 * (v > 0).mean())) for k, v in diffs.items()},
+          "surface pixels in the reference's geo image: %d of %d" % (int((g["returned"].float().mean(-1) < 254.5).sum()), ret.shape[0] * ret.shape[1]))
+    assert np.array_equal(diffs["returned"], diffs["%04d_geo.png" % g["idx"]])     # the geo image is what is returned
+    if precision == "fp32":
+        assert diffs["%04d_img.png" % g["idx"]].max() <= 1 and diffs["%04d_depth.png" % g["idx"]].max() <= 1
+        # shading of a sphere-traced surface: the secant root is found to ~1e-6 on both sides, normals from the density gradient
+        assert diffs["returned"].max() <= 2
+    else:
+        assert diffs["%04d_img.png" % g["idx"]].max() <= 3 and diffs["%04d_depth.png" % g["idx"]].max() <= 4
+        # bf16 proposals may bracket a neighbouring crossing on a few rays (DESIGN.md 7): the bulk of the image must agree
+        assert (diffs["returned"] > 8).mean() <= 0.1
