@@ -179,6 +179,17 @@ res["internal"] = {"zv": zv.tolist(), "cw": cw.tolist(), "rv": rv.tolist(),
     "tA": C.taylor_A(sm).tolist(), "tB": C.taylor_B(sm).tolist(), "tC": C.taylor_C(sm).tolist(),
     "px": px.tolist(), "dd": dd.tolist(), "rp": rp.tolist(), "rpv": rpv.tolist(),
     "mom": float(lo.mean_on_mask((a - b).abs(), vm))}
+# LearnFocal parametrisations (model/intrinsics.py)
+import importlib
+FI = importlib.import_module("model.intrinsics")
+FOCAL_CASES = [(True, False, 2, [1.3, 2.1]), (True, False, 1, [1.3, 2.1]), (True, True, 2, 1.7), (False, True, 1, 1.7), (True, False, 2, None), (True, True, 1, None), (True, False, 2, 0.9)]
+res["focal"] = []
+for rq, fxo, order, init in FOCAL_CASES:
+    m = FI.LearnFocal(rq, fxo, order=order, init_focal=init)
+    out = m(0)
+    (out * torch.tensor([2.0, 3.0])).sum().backward() if rq else None
+    res["focal"].append({"out": out.tolist(), "keys": sorted(m.state_dict().keys()), "req": [p.requires_grad for p in m.parameters()],
+                         "grads": [None if p.grad is None else p.grad.tolist() for p in m.parameters()]})
 print(json.dumps(res))
 '''
 
@@ -256,6 +267,20 @@ def test_host_helpers_match_the_reference(capsys):
     torch.testing.assert_close(rp, T(q["rp"]), rtol=1e-5, atol=1e-5)
     assert rpv.tolist() == q["rpv"]
     assert abs(float(lo.mean_on_mask((a - b).abs(), vm)) - q["mom"]) < 1e-6
+    # LearnFocal: every parametrisation (order 1 / 2, fx only, list / scalar / no initial focal)
+    import model as mdl
+    cases = [(True, False, 2, [1.3, 2.1]), (True, False, 1, [1.3, 2.1]), (True, True, 2, 1.7), (False, True, 1, 1.7), (True, False, 2, None), (True, True, 1, None), (True, False, 2, 0.9)]
+    for (rq, fxo, order, init), want in zip(cases, ref["focal"]):
+        m = mdl.LearnFocal(rq, fxo, order=order, init_focal=init)
+        out = m(0)
+        if rq:
+            (out * torch.tensor([2.0, 3.0])).sum().backward()
+        close(out.detach(), want["out"])
+        assert sorted(m.state_dict().keys()) == want["keys"] and [p.requires_grad for p in m.parameters()] == want["req"]
+        for p, gw in zip(m.parameters(), want["grads"]):
+            assert (p.grad is None) == (gw is None)
+            if gw is not None:
+                close(p.grad, gw)
 
 
 def test_backup_copies_config_and_sources(tmp_path, monkeypatch):
