@@ -579,8 +579,62 @@ def extract_vectors(ref, cfg):
     return out
 
 
+def eval_lpips_stand_in(a, b, normalize=True):
+    """Stands in for the LPIPS network evaluation/eval.py:163 builds (lpips is not installed): any callable with its signature."""
+    return ((a - b).abs().mean() * (2.0 if normalize else 1.0)).reshape(1)
+
+
+def eval_vectors(ref, cfg):
+    """The UNMODIFIED reference's Eval_Images.eval_images (model/eval_images.py:47-219, the loop body of evaluation/eval.py:178-188)
+    on two frames of the tiny scene: ground-truth depth at another resolution than the render (exercises the nearest-exact resize),
+    sc = 0.5, a depth range that cuts both maps.  Returned dict and every file it writes are recorded."""
+    import importlib
+    import tempfile
+    import numpy as np
+    import cv2
+    from oracle.ref_harness import REFERENCE_ROOT
+    ref_harness._stub("skimage").metrics = None
+    written = []
+    sys.modules["imageio"].imwrite = lambda path, arr: written.append((path, np.array(arr)))
+    sys.path.insert(0, REFERENCE_ROOT)
+    try:
+        ref_ev = importlib.import_module("model.eval_images")
+    finally:
+        sys.path.remove(REFERENCE_ROOT)
+    scene = syn.make_scene("tiny")
+    n, h, w = scene["n"], scene["h"], scene["w"]
+    nerf, renderer, net = build_ref_model(ref, cfg, syn.init_mlp_state(42))
+    c2ws = scene["poses_gt"].clone()
+    ev = ref_ev.Eval_Images(renderer, {"extract_images": {"resolution": [h, w]}}, use_learnt_poses=True, use_learnt_focal=False,
+                            device=torch.device("cpu"), render_type="nope_nerf", c2ws=c2ws, img_list=None)
+    out = {"c2ws": c2ws, "frames": {}, "sc": 0.5, "min_depth": 0.03, "max_depth": 0.036}
+    g = torch.Generator().manual_seed(5)
+    for i in (1, 3):
+        batch = syn.make_batch(scene, i, (i + 1) % n)
+        gt_depth = 0.03 + 0.01 * torch.rand(1, h // 2, w // 2, generator=g)          # (1, 12, 16): half the render resolution
+        data = {"img": batch["img"], "img.idx": batch["img.idx"], "img.camera_mat": batch["img.camera_mat"], "img.scale_mat": batch["img.scale_mat"],
+                "img.gt_depths": gt_depth}
+        with tempfile.TemporaryDirectory() as tmp:
+            del written[:]
+            d = ev.eval_images(data, tmp, None, eval_lpips_stand_in, logger=None, min_depth=out["min_depth"], max_depth=out["max_depth"], sc=out["sc"],
+                               show_errors=False)
+            files = {os.path.relpath(p, tmp): torch.from_numpy(a) for p, a in written}
+            for r, _, fs in os.walk(tmp):
+                for f in fs:
+                    files[os.path.relpath(os.path.join(r, f), tmp)] = torch.from_numpy(cv2.imread(os.path.join(r, f), cv2.IMREAD_UNCHANGED))
+        out["frames"][i] = {"gt_depth": gt_depth, "files": files,
+                            "ret": {k: (torch.from_numpy(np.ascontiguousarray(v)) if isinstance(v, np.ndarray) else float(v)) for k, v in d.items()}}
+        print("eval frame", i, {k: (tuple(v.shape) if isinstance(v, np.ndarray) else round(float(v), 5)) for k, v in d.items()}, sorted(files), flush=True)
+    return out
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
+    if "--evalimg" in sys.argv:
+        ref = ref_harness.load_reference()
+        torch.set_num_threads(max(1, os.cpu_count() or 1))
+        torch.save(eval_vectors(ref, syn.default_cfg()), os.path.join(OUT, "evalimg.pt"))
+        return
     if "--trajectory" in sys.argv or "--posefit" in sys.argv or "--extract" in sys.argv:
         ref = ref_harness.load_reference()
         torch.set_num_threads(max(1, os.cpu_count() or 1))

@@ -15,14 +15,14 @@ import torch
 from util import ROOT, PKG
 
 # `from model... import ...` / `import model ...` statements of the callers, as they stand in the reference:
-# train.py:15,17   vis/render.py:11-14   evaluation/eval.py:12-13,15,21   evaluation/eval_poses.py:13   vis/vis_poses.py:7
+# train.py:15,17   vis/render.py:11-14   evaluation/eval.py:12-15,21   evaluation/eval_poses.py:13   vis/vis_poses.py:7
 CALLER_IMPORTS = {
     "train.py": ["import model as mdl", "from model.common import backup,  mse2psnr"],
     "vis/render.py": ["from model.checkpoints import CheckpointIO",
                       "from model.common import convert3x4_4x4,  interp_poses, interp_poses_bspline, generate_spiral_nerf",
                       "from model.extracting_images import Extract_Images", "import model as mdl"],
     "evaluation/eval.py": ["from model.checkpoints import CheckpointIO", "from model.common import compute_errors",
-                           "import model as mdl", "from model.common import mse2psnr"],
+                           "from model.eval_images import Eval_Images", "import model as mdl", "from model.common import mse2psnr"],
     "evaluation/eval_poses.py": ["import model as mdl"],
     "vis/vis_poses.py": ["import model as mdl"],
 }
@@ -54,13 +54,12 @@ def test_caller_import_blocks_resolve_in_the_dropin():
 
 
 def test_recorded_import_blocks_are_the_callers_own():
-    """Only where the reference is mounted: the recorded lines above still cover what the scripts import from `model`
-    (evaluation/eval.py also imports model.eval_images, the SSIM/LPIPS evaluation loop, which is out of scope: SURVEY.md 2)."""
+    """Only where the reference is mounted: the recorded lines above still cover what the scripts import from `model`."""
     ref = os.environ.get("NOPE_REFERENCE_ROOT", "/root/reference")
     if not os.path.isdir(os.path.join(ref, "model")):
         pytest.skip("reference tree not mounted")
     for script, lines in CALLER_IMPORTS.items():
-        found = [l for l in _model_imports_of(os.path.join(ref, script)) if "eval_images" not in l]
+        found = _model_imports_of(os.path.join(ref, script))
         ns = {}
         for l in found:
             exec(l, ns)
@@ -190,6 +189,13 @@ for rq, fxo, order, init in FOCAL_CASES:
     (out * torch.tensor([2.0, 3.0])).sum().backward() if rq else None
     res["focal"].append({"out": out.tolist(), "keys": sorted(m.state_dict().keys()), "req": [p.requires_grad for p in m.parameters()],
                          "grads": [None if p.grad is None else p.grad.tolist() for p in m.parameters()]})
+# the SSIM evaluation/eval.py reports (third_party/pytorch_ssim, outside the model package)
+sys.path.insert(0, ref_harness.REFERENCE_ROOT)
+from third_party import pytorch_ssim
+sys.path.remove(ref_harness.REFERENCE_ROOT)
+i1 = torch.rand(1, 3, 24, 32, generator=g); i2 = (i1 + 0.1 * torch.randn(1, 3, 24, 32, generator=g)).clamp(0, 1)
+res["ssim_eval"] = {"i1": i1.tolist(), "i2": i2.tolist(), "v": float(pytorch_ssim.ssim(i1, i2)), "vn": float(pytorch_ssim.ssim(i1, i2, use_padding=False)),
+                    "per": pytorch_ssim.ssim(torch.cat([i1, i2]), torch.cat([i2, i2]), size_average=False).tolist()}
 print(json.dumps(res))
 '''
 
@@ -267,6 +273,12 @@ def test_host_helpers_match_the_reference(capsys):
     torch.testing.assert_close(rp, T(q["rp"]), rtol=1e-5, atol=1e-5)
     assert rpv.tolist() == q["rpv"]
     assert abs(float(lo.mean_on_mask((a - b).abs(), vm)) - q["mom"]) < 1e-6
+    # the SSIM of the evaluation loop
+    from model import eval_images as ME
+    e = ref["ssim_eval"]
+    i1, i2 = T(e["i1"]), T(e["i2"])
+    assert abs(float(ME.ssim(i1, i2)) - e["v"]) < 1e-6 and abs(float(ME.ssim(i1, i2, use_padding=False)) - e["vn"]) < 1e-6
+    close(ME.ssim(torch.cat([i1, i2]), torch.cat([i2, i2]), size_average=False), e["per"])
     # LearnFocal: every parametrisation (order 1 / 2, fx only, list / scalar / no initial focal)
     import model as mdl
     cases = [(True, False, 2, [1.3, 2.1]), (True, False, 1, [1.3, 2.1]), (True, True, 2, 1.7), (False, True, 1, 1.7), (True, False, 2, None), (True, True, 1, None), (True, False, 2, 0.9)]

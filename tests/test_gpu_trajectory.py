@@ -238,3 +238,56 @@ def test_render_visdata_writes_and_returns_what_the_reference_does(golden, tmp_p
         assert diffs["%04d_img.png" % g["idx"]].max() <= 3 and diffs["%04d_depth.png" % g["idx"]].max() <= 4
         # bf16 proposals may bracket a neighbouring crossing on a few rays: the bulk of the image must agree
         assert (diffs["returned"] > 8).mean() <= 0.1
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_eval_images_matches_the_reference_metrics_and_files(golden, tmp_path, precision):
+    """evaluation/eval.py:178-188 -> Eval_Images.eval_images: the returned metrics / arrays and all eleven PNGs per frame against the
+    UNMODIFIED reference's (tests/golden/evalimg.pt; LPIPS network replaced by the same stand-in callable on both sides)."""
+    import os
+    import cv2
+    import numpy as np
+    from model.eval_images import Eval_Images
+    from oracle.make_golden import eval_lpips_stand_in
+    g = golden("evalimg")
+    cfg = syn.default_cfg()
+    scene = syn.make_scene("tiny")
+    n, h, w = scene["n"], scene["h"], scene["w"]
+    nerf, renderer, net, pose, dist = build_models(cfg, n, scene, precision=precision)
+    ev = Eval_Images(renderer, {"extract_images": {"resolution": [h, w]}}, use_learnt_poses=True, use_learnt_focal=False, device=dev(),
+                     render_type="nope_nerf", c2ws=g["c2ws"].to(dev()), img_list=None)
+    tol = 1e-5 if precision == "fp32" else 2e-3
+    for i, want in g["frames"].items():
+        batch = syn.make_batch(scene, i, (i + 1) % n)
+        data = {"img": batch["img"], "img.idx": batch["img.idx"], "img.camera_mat": batch["img.camera_mat"], "img.scale_mat": batch["img.scale_mat"],
+                "img.gt_depths": want["gt_depth"]}
+        out_dir = tmp_path / ("frame%d" % i)
+        os.makedirs(out_dir)
+        got = ev.eval_images(data, str(out_dir), None, eval_lpips_stand_in, logger=None, min_depth=g["min_depth"], max_depth=g["max_depth"],
+                             sc=g["sc"], show_errors=False)
+        assert sorted(got.keys()) == sorted(want["ret"].keys())
+        for k in ("mse", "psnr", "ssim", "lpips"):
+            assert abs(got[k] - want["ret"][k]) <= tol * abs(want["ret"][k]), (k, got[k], want["ret"][k])
+        d_img = np.abs(got["img"].astype(np.int32) - want["ret"]["img"].numpy().astype(np.int32))
+        files = sorted(os.path.relpath(os.path.join(r, f), out_dir) for r, _, fs in os.walk(out_dir) for f in fs)
+        assert files == sorted(want["files"].keys())
+        worst_file = 0
+        for f in files:
+            mine = cv2.imread(str(out_dir / f), cv2.IMREAD_UNCHANGED)
+            ref = want["files"][f].numpy()
+            if ref.ndim == 3 and not f.startswith(("disp_out", "disp_gt_out")):
+                ref = ref[:, :, ::-1]          # recorded as handed to imageio (RGB); OpenCV reads BGR
+            assert mine.shape == ref.shape, f
+            worst_file = max(worst_file, int(np.abs(mine.astype(np.int32) - ref.astype(np.int32)).max()))
+        same_mask = got["depth_pred"].shape == tuple(want["ret"]["depth_pred"].shape)
+        print("%s frame %d: psnr %.5f (reference %.5f) ssim %.6f (%.6f); uint8 image max diff %d, worst file diff %d, %d evaluated depth pixels%s" % (
+            precision, i, got["psnr"], want["ret"]["psnr"], got["ssim"], want["ret"]["ssim"], d_img.max(), worst_file, got["depth_pred"].size,
+            "" if same_mask else " (reference %d)" % want["ret"]["depth_pred"].numel()))
+        if precision == "fp32":
+            assert d_img.max() <= 1 and worst_file <= 1 and same_mask
+            np.testing.assert_allclose(got["depth_pred"], want["ret"]["depth_pred"].numpy(), rtol=1e-5)
+            np.testing.assert_array_equal(got["depth_gt"], want["ret"]["depth_gt"].numpy())
+            np.testing.assert_array_equal(got["conf_mat"], want["ret"]["conf_mat"].numpy())
+        else:
+            assert d_img.max() <= 3
+            assert np.abs(got["conf_mat"] - want["ret"]["conf_mat"].numpy()).max() <= 0.03      # a depth at the range edge may change side
