@@ -47,25 +47,36 @@ class Loss(nn.Module):
             rec[1] = vals
         return rec[0]
 
-    def raise_if_nan(self, loss_dict):
+    def raise_if_nan(self, loss_dict, no_valid_depth=None):
         """model/losses.py:213-214 (`if torch.isnan(loss): breakpoint()`) without a host synchronisation on the step just
-        issued: the loss is copied to pinned host memory asynchronously and examined when the NEXT step has been queued."""
+        issued: the loss is copied to pinned host memory asynchronously and examined when the NEXT step has been queued.
+        `no_valid_depth` (optional device scalar, Trainer's graphed step with sparse depth): non-zero when neither of the step's
+        two ray draws contained a pixel with a valid depth -- the case the reference's loop resamples until it is gone
+        (model/training.py:279-284); reported the same way, one step late."""
         loss = loss_dict['loss']
         if not loss.is_cuda:
             if bool(torch.isnan(loss)):
                 raise FloatingPointError("NaN loss")
             return
         prev = self._nan_pending
-        host = prev[1] if prev is not None else torch.zeros(2, dtype=torch.float32).pin_memory()
+        host = prev[1] if prev is not None else torch.zeros(2, 2, dtype=torch.float32).pin_memory()
         slot = 0
         if prev is not None:
             ev, _, slot, step = prev
             ev.synchronize()
-            if bool(torch.isnan(host[slot])):
+            if bool(torch.isnan(host[slot, 0])):
                 self._nan_pending = None
                 raise FloatingPointError("NaN loss at step %d (model/losses.py:213)" % step)
+            if float(host[slot, 1]) != 0.0:
+                self._nan_pending = None
+                raise RuntimeError("step %d: no ray with a valid depth in two consecutive draws (model/training.py:279-284 resamples "
+                                   "until there is one); run this batch kernel by kernel (Trainer.use_graph = False)" % step)
             slot ^= 1
-        host[slot:slot + 1].copy_(loss.detach().reshape(1), non_blocking=True)
+        host[slot, 0:1].copy_(loss.detach().reshape(1), non_blocking=True)
+        if no_valid_depth is not None:
+            host[slot, 1:2].copy_(no_valid_depth.detach().reshape(1).float(), non_blocking=True)
+        else:
+            host[slot, 1] = 0.0
         ev = torch.cuda.Event()
         ev.record()
         self._nan_pending = (ev, host, slot, self._nan_step)

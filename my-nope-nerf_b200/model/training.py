@@ -37,6 +37,8 @@ class Trainer(object):
         self.fork_geometry = True   # train_step_graphed: reference-frame branch as a parallel branch of the graph
         self._geom_stream = None    # set while train_step_graphed warms up and captures: forks the reference-frame branch
         self._geom_forked = False
+        self._graph_body = False    # True while train_step_graphed warms up and captures (graph-safe forms of host-side decisions)
+        self._no_valid_depth = None
         self.optimizer_pose = optimizer_pose
         self.pose_param_net = pose_param_net
         self.focal_net = focal_net
@@ -96,7 +98,6 @@ class Trainer(object):
                 and self.fixed_ray_idx is None and self.fixed_noise is None
                 and self.ray_choice != 'reference'        # the reference's generator sequence is an eager-mode property
                 and not self.optimizer_focal              # learned intrinsics (non-default): kernel-by-kernel step
-                and data.get('img.dpt') is not None       # sparse depth: the resample loop of model/training.py:279-284 reads the mask on the host
                 and _cabi.profile is None)                # per-entry-point timing (bench.py) needs eager launches
 
     def train_step_eager(self, data, it=None, epoch=None, scheduling_start=None, render_path=None):
@@ -176,6 +177,7 @@ class Trainer(object):
         _ops.copy_many(pairs, scalars)
         static['img.idx'], static['img.ref_idxs'] = data.get('img.idx'), data.get('img.ref_idxs')
         slot['graph'].replay()
+        self._last_draw = slot['last_draw']      # this variant's ray choice / jitter tensors (parity tests read them)
         self.graphed_launches = getattr(self, 'graphed_launches', 0) + slot['n_launches']
         for p in slot['no_grad']:
             p.grad = None       # a parameter this graph variant gives no gradient must not carry one from another variant
@@ -183,7 +185,7 @@ class Trainer(object):
             p.grad = g
         self._optimizer_tail(slot['loss_dict'])
         if self.loss.check_nan:
-            self.loss.raise_if_nan(slot['loss_dict'])
+            self.loss.raise_if_nan(slot['loss_dict'], slot['no_valid_depth'])
         return slot['loss_dict']
 
     # keys of the batch schema the training step reads (process_data_dict / process_data_reference); the DataLoader also yields
@@ -252,6 +254,7 @@ class Trainer(object):
             for p in params:
                 p.grad = None
             self._geom_stream, self._geom_forked = geom, False
+            self._graph_body, self._no_valid_depth = True, None
             _ops.wgrad_stream, _ops.wgrad_forked = wgrad, False
             try:
                 if pack is not None:
@@ -267,6 +270,7 @@ class Trainer(object):
                     torch.cuda.current_stream().wait_stream(wgrad)  # parameter gradients complete before the optimiser reads them
             finally:
                 self._geom_stream = None
+                self._graph_body = False
                 _ops.wgrad_stream = None
             return ld
 
@@ -291,6 +295,7 @@ class Trainer(object):
         with torch.cuda.graph(graph):
             loss_dict = body()
         return {'graph': graph, 'static': static, 'loss_dict': loss_dict, 'n_launches': _cabi.kernel_launches() - l0,
+                'no_valid_depth': self._no_valid_depth, 'last_draw': getattr(self, '_last_draw', None),
                 'grads': [(p, p.grad) for p in params if p.grad is not None],
                 'no_grad': [p for p in params if p.grad is None]}
 
@@ -452,10 +457,21 @@ class Trainer(object):
         else:
             ray_idx = draw()
             if data.get('img.dpt') is None:
+                # sparse depth maps (dataloading `with_depth` + `sparsify_depth`, the V_KITTI configs): the reference draws again
+                # until at least one chosen pixel has a depth (model/training.py:279-284), reading the mask on the host
                 depth_mask_flat = torch.flatten(depth_mask)
-                while not depth_mask_flat[ray_idx].any():
-                    print('No valid depths found, resampling...')
-                    ray_idx = draw()
+                if self._graph_body:
+                    # graph-safe form: a second draw, selected on the device when the first holds no valid pixel (probability
+                    # (1 - valid fraction)^n_rays: 1e-22 for 4,096 rays on a 1-in-81 pattern); both empty -> flag, checked
+                    # one step late with the NaN check (Loss.raise_if_nan)
+                    alt = draw()
+                    ok = depth_mask_flat[ray_idx].any()
+                    self._no_valid_depth = (~(ok | depth_mask_flat[alt].any())).float()
+                    ray_idx = torch.where(ok, ray_idx, alt)
+                else:
+                    while not depth_mask_flat[ray_idx].any():
+                        print('No valid depths found, resampling...')
+                        ray_idx = draw()
         n_global = ray_idx.numel()
         lo, hi = self.dp.shard(n_global)
         sharded = self.dp.world_size > 1

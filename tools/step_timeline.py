@@ -15,7 +15,9 @@ batches = []
 for i in range(4):
     b = syn.make_batch(scene, i, i + 1)
     batches.append({k: (v.to(dev) if torch.is_tensor(v) and k not in ("img.idx", "img.ref_idxs") else v) for k, v in b.items()})
-step = tr.train_step if '--no-graph' in sys.argv else tr.train_step_graphed
+if '--no-graph' in sys.argv:
+    tr.use_graph = False          # kernel by kernel (what a batch that does not qualify for the graph gets)
+step = tr.train_step
 for it in range(5):
     step(batches[it % 4], it=it, epoch=0, scheduling_start=sched)
 torch.cuda.synchronize()
