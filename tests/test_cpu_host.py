@@ -99,8 +99,16 @@ for n in names:
 out["get_model"] = list(inspect.signature(ref.get_model).parameters)
 import yaml
 cfg = yaml.safe_load(open(ref_harness.REFERENCE_ROOT + "/configs/default.yaml"))
+import torch
+torch.manual_seed(42)          # train.py:24, then the construction order of train.py:47-56,97,110
 net = ref.get_model(ref.Renderer(ref.OfficialStaticNerf(cfg), cfg["rendering"], device="cpu"), cfg, device="cpu")
+pose = ref.LearnPose(5, True, True, cfg, init_c2w=None)
+dist = ref.Learn_Distortion(5, True, True, cfg)
+after = float(torch.rand(1))
 out["state"] = {k: list(v.shape) for k, v in net.state_dict().items()}
+out["seeded"] = {"net": {k: [float(v.double().sum()), float(v.double().abs().sum())] for k, v in net.state_dict().items()},
+                 "pose": {k: float(v.double().abs().sum()) for k, v in pose.state_dict().items()},
+                 "dist": {k: float(v.double().sum()) for k, v in dist.state_dict().items()}, "next_draw": after}
 print(json.dumps(out))
 ''' % ROOT
     import json
@@ -109,7 +117,7 @@ print(json.dumps(out))
     ref = json.loads(res.stdout.strip().splitlines()[-1])
     import model as mdl
     for n, methods in ref.items():
-        if n in ("get_model", "state"):
+        if n in ("get_model", "state", "seeded"):
             continue
         c = getattr(mdl, n)
         for m, params in methods.items():
@@ -119,6 +127,17 @@ print(json.dumps(out))
     cfg = syn.default_cfg()
     net = mdl.get_model(mdl.Renderer(mdl.OfficialStaticNerf(cfg), cfg["rendering"], device="cpu"), cfg, device="cpu")
     assert {k: list(v.shape) for k, v in net.state_dict().items()} == ref["state"]
+    # the same seed gives the same initial weights AND leaves the generator where the reference leaves it: a run of the unchanged
+    # train.py (torch.manual_seed(42), train.py:24) starts from the reference's own initialisation
+    torch.manual_seed(42)
+    net = mdl.get_model(mdl.Renderer(mdl.OfficialStaticNerf(cfg), cfg["rendering"], device="cpu"), cfg, device="cpu")
+    pose = mdl.LearnPose(5, True, True, cfg, init_c2w=None)
+    dist = mdl.Learn_Distortion(5, True, True, cfg)
+    after = float(torch.rand(1))
+    sd = ref["seeded"]
+    assert {k: [float(v.double().sum()), float(v.double().abs().sum())] for k, v in net.state_dict().items()} == sd["net"]
+    assert {k: float(v.double().abs().sum()) for k, v in pose.state_dict().items()} == sd["pose"]
+    assert {k: float(v.double().sum()) for k, v in dist.state_dict().items()} == sd["dist"] and after == sd["next_draw"]
 
 
 def test_anneal_and_weights_match_oracle():
