@@ -334,6 +334,7 @@ def run_b200(args):
                          ("allreduce", lambda: X.allreduce_alone(dev, dp, n)),
                          ("dp_parity", lambda: X.dp_parity(dev, scene, cfg, dp)),
                          ("dropin", lambda: X.dropin_path(dev, scene, cfg, host_batches, "auto", dp)),
+                         ("fork_config", (lambda: X.fork_config(dev, cfg)) if world == 1 else (lambda: None)),
                          ("torch_eager_gpu", (lambda: X.torch_eager_gpu(dev, scene, cfg)) if world == 1 else (lambda: None))):
             try:
                 r = fn()
@@ -506,11 +507,12 @@ def _cpu_sample_text(cores, rays_sample, nn_slice, t, Pn, step_s):
 
 
 def cpu_baseline(max_seconds=25.0):
-    """Bounded (10-30 s) sample inside the GPU arm's run: 1,024 rays, 1,024 Chamfer sources."""
+    """Bounded (10-30 s: ~15 s on 16 cores) sample inside the GPU arm's run: 2,048 of the 4,096 rays, 3,072 Chamfer sources per
+    direction."""
     cores = os.cpu_count() or 1
-    step_s, t, Pn = cpu_step_sample(rays_sample=1024, nn_slice=1024, threads=cores)
+    step_s, t, Pn = cpu_step_sample(rays_sample=2048, nn_slice=3072, threads=cores)
     return {"value": RAYS_PER_GPU / step_s, "unit": "rays/s", "cores": cores, "kind": "port",
-            "sample": _cpu_sample_text(cores, 1024, 1024, t, Pn, step_s), "step_seconds_extrapolated": step_s,
+            "sample": _cpu_sample_text(cores, 2048, 3072, t, Pn, step_s), "step_seconds_extrapolated": step_s,
             "extrapolated_fraction": t["extrapolated_fraction"], "measured_seconds": t["measured_s"]}
 
 
