@@ -167,6 +167,29 @@ def torch_eager_gpu(dev, scene, cfg, steps=3):
 # ---------------------------------------------------------------------------------------------------------------------
 # cfg3: the 65,536-ray GLOBAL batch sharded over the N ranks (strong scaling: 65,536 / N rays per GPU)
 # ---------------------------------------------------------------------------------------------------------------------
+def fork_scene(n=20, h=188, w=621):
+    scene = syn.make_scene("cfg2", frames=n, h=h, w=w, sparse_depth=True)
+    host = []
+    for i in range(n):
+        b = syn.make_batch(scene, i, i + 1 if i < n - 1 else i - 1, dpt=False)
+        host.append({k: (v.pin_memory() if torch.is_tensor(v) else v) for k, v in b.items()})
+    return scene, host
+
+
+def fork_trainer(dev, cfg, scene, rays):
+    import model as mdl
+    n = scene["n"]
+    nerf = mdl.OfficialStaticNerf(cfg)
+    nerf.load_state_dict(syn.init_mlp_state(42))
+    net = mdl.get_model(mdl.Renderer(nerf, cfg["rendering"], device=dev), cfg, device=dev).to(dev)
+    pose = mdl.LearnPose(n, False, False, cfg, init_c2w=scene["poses_gt"].clone()).to(dev)
+    dist = mdl.Learn_Distortion(n, False, False, cfg).to(dev)
+    tcfg = dict(cfg["training"], n_training_points=rays)
+    return mdl.Trainer(net, torch.optim.Adam(net.parameters(), lr=tcfg["learning_rate"]), tcfg, device=dev,
+                       optimizer_pose=torch.optim.Adam(pose.parameters(), lr=tcfg["pose_lr"]), pose_param_net=pose,
+                       optimizer_distortion=torch.optim.Adam(dist.parameters(), lr=tcfg["distortion_lr"]), distortion_net=dist)
+
+
 def fork_config(dev, cfg, steps=60):
     """The fork's OWN training configuration (configs/V_KITTI/*.yaml over configs/default.yaml) rather than BASELINE's cfg2: frames at
     half resolution (`resize_factor: 2` -> 188 x 621), 1,024 rays per step (`n_training_points` default), sparse ground-truth depth
@@ -174,26 +197,13 @@ def fork_config(dev, cfg, steps=60):
     values (`learn_R` / `learn_t` / `learn_scale` / `learn_shift: false`), three torch.optim.Adam, pinned host batches through
     `Trainer.train_step` with the three `.item()` reads of train.py:216-218.  Timed twice: as `train_step` routes it (CUDA graph;
     sparse-depth batches qualify since the in-graph re-draw) and kernel by kernel (`use_graph = False`)."""
-    import model as mdl
-    n, h, w, R = 20, 188, 621, 1024
-    scene = syn.make_scene("cfg2", frames=n, h=h, w=w, sparse_depth=True)
-    host = []
-    for i in range(n):
-        b = syn.make_batch(scene, i, i + 1 if i < n - 1 else i - 1, dpt=False)
-        host.append({k: (v.pin_memory() if torch.is_tensor(v) else v) for k, v in b.items()})
+    n, R = 20, 1024
+    scene, host = fork_scene(n)
     sched = cfg["training"]["scheduling_start"]
     out = {"what": "188 x 621 frames, 1,024 rays x 128 samples, sparse img.depth (1 pixel in 100 valid), poses / distortion frozen, full loss "
                    "set, 3 x torch.optim.Adam, host batches through Trainer.train_step + 3 .item() per step"}
     for mode in ("graph", "kernel_by_kernel"):
-        nerf = mdl.OfficialStaticNerf(cfg)
-        nerf.load_state_dict(syn.init_mlp_state(42))
-        net = mdl.get_model(mdl.Renderer(nerf, cfg["rendering"], device=dev), cfg, device=dev).to(dev)
-        pose = mdl.LearnPose(n, False, False, cfg, init_c2w=scene["poses_gt"].clone()).to(dev)
-        dist = mdl.Learn_Distortion(n, False, False, cfg).to(dev)
-        tcfg = dict(cfg["training"], n_training_points=R)
-        tr = mdl.Trainer(net, torch.optim.Adam(net.parameters(), lr=tcfg["learning_rate"]), tcfg, device=dev,
-                         optimizer_pose=torch.optim.Adam(pose.parameters(), lr=tcfg["pose_lr"]), pose_param_net=pose,
-                         optimizer_distortion=torch.optim.Adam(dist.parameters(), lr=tcfg["distortion_lr"]), distortion_net=dist)
+        tr = fork_trainer(dev, cfg, scene, R)
         if mode == "kernel_by_kernel":
             tr.use_graph = False
         for it in list(range(n)) + [0, 1]:

@@ -27,12 +27,39 @@ WEIGHT_NAMES_IN_SUM = ['rgb_weight', 'depth_weight', 'weight_dist_1st_loss', 'we
                        'depth_consistency_weight', 't_cycle_weight']
 
 
+def _prefer_fused_adam(opt):
+    """train.py:59,100,118,141 build plain `torch.optim.Adam(params, lr=...)`: torch then steps with its multi-tensor `foreach` path,
+    seven launches per optimiser (160 us for the 24 MLP tensors: a tenth of a 1,024-ray step).  The same class has a one-launch
+    `fused` implementation of the same update; it is selected here, on the caller's optimiser, when nothing the caller chose
+    stands against it (CUDA fp32 parameters, `foreach` / `fused` left at their defaults, none of amsgrad / maximize / capturable /
+    differentiable).  Step counters already restored from a checkpoint move to the parameters' device, as the fused path needs.
+    NNB_FUSED_TORCH_ADAM=0 leaves the optimisers untouched."""
+    if type(opt) is not torch.optim.Adam or os.environ.get('NNB_FUSED_TORCH_ADAM', '1') == '0':
+        return
+    for g in opt.param_groups:
+        if g.get('fused', 0) is not None or g.get('foreach') is not None:
+            return                                   # option missing in this torch, or set by the caller
+        if g.get('amsgrad') or g.get('maximize') or g.get('capturable') or g.get('differentiable'):
+            return
+        if not all(p.is_cuda and p.dtype == torch.float32 for p in g['params']):
+            return
+    for g in opt.param_groups:
+        g['fused'] = True
+        for p in g['params']:
+            st = opt.state.get(p)
+            if st and torch.is_tensor(st.get('step')):
+                st['step'] = st['step'].to(device=p.device, dtype=torch.float32)
+
+
 class Trainer(object):
     def __init__(self, model, optimizer, cfg, device=None, optimizer_pose=None, pose_param_net=None,
                  optimizer_focal=None, focal_net=None, optimizer_distortion=None, distortion_net=None, **kwargs):
         self.model = model
         self.optimizer = optimizer
         self.device = device
+        for opt in (optimizer, optimizer_pose, optimizer_focal, optimizer_distortion):
+            if opt is not None:
+                _prefer_fused_adam(opt)
         self.fork_wgrad = True      # train_step_graphed: weight-gradient kernel on its own stream (joined before the optimiser)
         self.fork_geometry = True   # train_step_graphed: reference-frame branch as a parallel branch of the graph
         self._geom_stream = None    # set while train_step_graphed warms up and captures: forks the reference-frame branch
@@ -148,7 +175,8 @@ class Trainer(object):
         # WHICH terms are active selects the graph (zero-weight terms are skipped, model/losses.py:169-197); their VALUES -- the
         # annealed weights change every epoch -- live in a device vector written below, before the replay
         wkey = tuple(v != 0.0 for v in wvals) + (epoch < self.annealing_epochs + scheduling_start,)
-        tensors = sorted(k for k, v in data.items() if torch.is_tensor(v) and k not in ('img.idx', 'img.ref_idxs'))
+        # the tensors the step reads (the DataLoader also yields img.gt_depths, evaluation only: not staged)
+        tensors = sorted(k for k, v in data.items() if torch.is_tensor(v) and k in self.STEP_KEYS and k not in ('img.idx', 'img.ref_idxs'))
         # injected draws (test hooks) are baked into a capture as device pointers: they select their own graphs
         hooks = tuple(None if t is None else (t.data_ptr(), str(t.device)) for t in (self.fixed_ray_idx, self.fixed_noise))
         key = (idx < n - 1, idx == n - 1, ref == n - 1, wkey, hooks, tuple((k, tuple(data[k].shape), data[k].dtype) for k in tensors))

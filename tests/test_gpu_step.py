@@ -374,3 +374,47 @@ def test_wgrad_on_its_own_stream_gives_the_same_step(golden):
             # the same computation in both runs (learning rates are zero): only the order of the weight-gradient atomics differs
             assert rel <= 1e-4, (step, k, rel)
     print("forked wgrad: worst scale-relative gradient difference, first step %.2e, later steps %.2e" % tuple(worst))
+
+
+def test_callers_torch_adam_is_stepped_by_its_fused_kernel():
+    """train.py builds plain torch.optim.Adam optimisers; the Trainer selects that class's own one-launch `fused` update when the
+    caller left `foreach` / `fused` at their defaults -- same parameters afterwards as the default multi-tensor path, also when the
+    step counters came from a checkpoint written by the default path."""
+    import model as mdl
+    from model.training import _prefer_fused_adam
+    g = torch.Generator().manual_seed(4)
+    shapes = [(256, 63), (256,), (3, 128), (1,)]
+    w0 = [torch.randn(s, generator=g) for s in shapes]
+    grads = [[torch.randn(s, generator=g) for s in shapes] for _ in range(5)]
+
+    def run(fused, resume_at=None):
+        ps = [torch.nn.Parameter(w.clone().to(dev())) for w in w0]
+        opt = torch.optim.Adam(ps, lr=1e-3)
+        if fused:
+            _prefer_fused_adam(opt)
+            assert opt.param_groups[0]["fused"] is True
+        for i, gs in enumerate(grads):
+            if resume_at == i:          # checkpoint written by the default path, loaded before the Trainer exists (train.py:62-66,158)
+                sd = opt.state_dict()
+                opt = torch.optim.Adam(ps, lr=1e-3)
+                opt.load_state_dict(sd)
+                _prefer_fused_adam(opt)
+                assert all(st["step"].is_cuda for st in opt.state.values())
+            for p, gg in zip(ps, gs):
+                p.grad = gg.to(dev()) if not (i == 2 and p.numel() == 1) else None      # one step without a gradient for one tensor
+            opt.step()
+        return [p.detach().cpu() for p in ps], opt
+
+    base, _ = run(False)
+    for got, _ in (run(True), run(False, resume_at=3)):
+        for a, b in zip(got, base):
+            assert float((a - b).abs().max()) <= 1e-6 * float(b.abs().max())      # a few fp32 ulps between the two implementations
+    # options the caller chose are left alone
+    for kw in ({"foreach": True}, {"fused": False}, {"amsgrad": True}):
+        opt = torch.optim.Adam([torch.nn.Parameter(torch.zeros(3, device=dev()))], lr=1e-3, **kw)
+        before = dict(opt.param_groups[0])
+        _prefer_fused_adam(opt)
+        assert {k: v for k, v in opt.param_groups[0].items() if k != "params"} == {k: v for k, v in before.items() if k != "params"}
+    cpu_opt = torch.optim.Adam([torch.nn.Parameter(torch.zeros(3))], lr=1e-3)
+    _prefer_fused_adam(cpu_opt)
+    assert cpu_opt.param_groups[0]["fused"] is None

@@ -8,13 +8,21 @@ import bench, synthetic_scene as syn
 from model import parallel
 dev = torch.device("cuda:0")
 dp = parallel.DataParallelContext(0, 1)
-cfg, scene, tr = bench.build_trainer(dev, 20, 4096, "bf16", dp)
+if '--fork-config' in sys.argv:
+    # the fork's own settings (bench_extras.fork_config): 188 x 621, 1,024 rays, sparse depth, frozen poses, host batches, torch Adam
+    import bench_extras as X
+    cfg = syn.default_cfg()
+    scene, batches = X.fork_scene(20)
+    batches = batches[:4]
+    tr = X.fork_trainer(dev, cfg, scene, 1024)
+else:
+    cfg, scene, tr = bench.build_trainer(dev, 20, 4096, "bf16", dp)
+    batches = []
+    for i in range(4):
+        b = syn.make_batch(scene, i, i + 1)
+        batches.append({k: (v.to(dev) if torch.is_tensor(v) and k not in ("img.idx", "img.ref_idxs") else v) for k, v in b.items()})
 n = scene["n"]
 sched = cfg["training"]["scheduling_start"]
-batches = []
-for i in range(4):
-    b = syn.make_batch(scene, i, i + 1)
-    batches.append({k: (v.to(dev) if torch.is_tensor(v) and k not in ("img.idx", "img.ref_idxs") else v) for k, v in b.items()})
 if '--no-graph' in sys.argv:
     tr.use_graph = False          # kernel by kernel (what a batch that does not qualify for the graph gets)
 step = tr.train_step
