@@ -287,7 +287,7 @@ extern "C" {
 size_t nnb_chamfer_workspace_bytes(int n_src, int n_dst) {
   if (n_src < 0) n_src = 0;
   if (n_dst < 0) n_dst = 0;
-  return (((size_t)n_src + 8) * sizeof(unsigned int) + 255) / 256 * 256 + nnb_chamfer_tc_workspace_bytes(n_src, n_dst);
+  return (((size_t)n_src + 16) * sizeof(unsigned int) + 255) / 256 * 256 + nnb_chamfer_tc_workspace_bytes(n_src, n_dst);
 }
 
 static int g_chamfer_pass1_cuda_cores = 0;
@@ -306,7 +306,7 @@ int nnb_chamfer_nn(const float *src, int n_src, const float *dst, int n_dst, int
   cudaStream_t s = nnb_stream(stream);
   unsigned long long *best = reinterpret_cast<unsigned long long *>(idx);
   unsigned int *bound = static_cast<unsigned int *>(workspace), *qqmax = bound + n_src, *tc_stats = qqmax + 1;
-  uint8_t *tc_ws = static_cast<uint8_t *>(workspace) + (((size_t)n_src + 8) * sizeof(unsigned int) + 255) / 256 * 256;
+  uint8_t *tc_ws = static_cast<uint8_t *>(workspace) + (((size_t)n_src + 16) * sizeof(unsigned int) + 255) / 256 * 256;
   const float *tc_norm2 = reinterpret_cast<const float *>(tc_ws + nnb_chamfer_tc_norm2_offset(n_src, n_dst));
   if (g_chamfer_pass1_cuda_cores == 1) {
     NNB_CUDA(cudaMemsetAsync(bound, 0x7f, (size_t)n_src * sizeof(unsigned int), s));

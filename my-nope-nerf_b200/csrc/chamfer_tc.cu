@@ -105,15 +105,24 @@ __global__ void chamfer_tc_prep_kernel(const float *__restrict__ src, int n_src,
 }
 
 // ---- fp16 two-way split (production screen): one K = 16 MMA per stage ------------------------------------------------
-// Both clouds are centred on dst[0] and multiplied by a power of two (exact) that brings the largest |coordinate| of
-// either cloud into [16, 32): fp16's range (nn' < 3,072, |-2 s'| < 64) and its normal range for the low halves.
+// Both clouds are centred on the centroid of the destinations (chamfer_tc_centre_kernel; the first destination -- a corner pixel
+// of a depth cloud -- made every scaled norm, and with it every error margin, several times larger) and multiplied by a power
+// of two (exact) that brings the largest |coordinate| of either cloud into [16, 32): fp16's range (nn' < 3,072, |-2 s'| < 64)
+// and its normal range for the low halves.
 // x = h + m (fp16 each, 22 bits).  Per coordinate all four cross terms ride in the K slots: source [h, h, m, m] against
 // destination [h, m, h, m]; |q'|^2 split three ways against ones in slots 12..14: K = 15 of 16.
 // Error of a' = |q'|^2 - 2 s'.q' against exact arithmetic on the scaled points:
 //   representation  <= 2^-21 (|s'|^2 + |q'|^2)     (2^-22 relative per factor)
 //   fp16 subnormals <= 2^-25 per low half -> <= 8.5e-6 absolute
 //   fp32 accumulation of 15 exact products <= 2^-20 (|s'|^2 + 2 |q'|^2)
-// The exact sweep's margin is 8e-6 (|s'|^2 + 2 max|q'|^2 + bound) + 2e-5: more than twice that.
+// i.e. err(s, j) <= 1.5e-6 |s'|^2 + 2.4e-6 |q_j'|^2 + 8.5e-6.  The sixteenth K slot carries the destination's own share of the margin,
+// e_j = 8e-6 |q_j'|^2 (fp16, rounded up): the screening sweeps run with +1 in the source's slot 15 and minimise a_j + e_j, the exact
+// sweep runs with -1 (a second source image) and tests a_j - e_j < min_k (a_k + e_k) + 8e-6 (|s'|^2 + bound) + 2e-5.  The true
+// nearest neighbour j* passes: a*_j <= a*_k for all k (exact values), so a_j* - e_j* <= a_k + e_k + [err(s,j*) - e_j*] + [err(s,k) - e_k]
+// and each bracket is below half the source's margin.  A destination near the centre is thus tested against ITS error scale, not
+// the cloud's: with max |q'|^2 in the threshold (as before) a cloud whose bulk sits in a small cap around the centre while a few
+// points set the extent -- sparse depth maps back-projected with the nearest_limit clamp -- sent hundreds of pairs per source to
+// the exact re-evaluation.
 __device__ __forceinline__ uint32_t pack2h(__half a, __half b) {
   return (uint32_t)__half_as_ushort(a) | ((uint32_t)__half_as_ushort(b) << 16);
 }
@@ -122,12 +131,38 @@ __device__ __forceinline__ void split2h(float x, __half &h, __half &m) {
   m = __float2half_rn(x - __half2float(h));
 }
 
-// stats[2] = float bits of max |p - dst[0]|_inf over both clouds
+// stats[6..8] += sum of the finite destinations, stats[9] += their number (float): the centre of the scaled frame.  The sums are
+// atomic (order-dependent in the last bits): the centre only shapes the screen, the exact sweep decides indices and distances.
+__global__ void chamfer_tc_centre_kernel(const float *__restrict__ dst, int n_dst, unsigned int *__restrict__ stats) {
+  float a[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_dst; i += gridDim.x * blockDim.x) {
+    const float x = dst[3 * (size_t)i], y = dst[3 * (size_t)i + 1], z = dst[3 * (size_t)i + 2];
+    if (isfinite(x) && isfinite(y) && isfinite(z)) { a[0] += x; a[1] += y; a[2] += z; a[3] += 1.f; }
+  }
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) a[c] += __shfl_xor_sync(0xffffffffu, a[c], o);
+  }
+  if ((threadIdx.x & 31) == 0 && a[3] > 0.f) {
+#pragma unroll
+    for (int c = 0; c < 4; ++c) atomicAdd(reinterpret_cast<float *>(stats + 6 + c), a[c]);
+  }
+}
+__device__ __forceinline__ void tc_centre(const unsigned int *__restrict__ stats, const float *__restrict__ dst, float (&c)[3]) {
+  const float n = __uint_as_float(stats[9]);
+#pragma unroll
+  for (int k = 0; k < 3; ++k) c[k] = n > 0.f ? __uint_as_float(stats[6 + k]) / n : dst[k];
+}
+
+// stats[2] = float bits of max |p - centre|_inf over both clouds
 __global__ void chamfer_tc_extent_kernel(const float *__restrict__ src, int n_src, const float *__restrict__ dst, int n_dst,
                                          unsigned int *__restrict__ stats) {
   __shared__ float red[32];
   float m = 0.f;
-  const float cx = dst[0], cy = dst[1], cz = dst[2];
+  float ctr[3];
+  tc_centre(stats, dst, ctr);
+  const float cx = ctr[0], cy = ctr[1], cz = ctr[2];
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_src + n_dst; i += gridDim.x * blockDim.x) {
     const float *p = i < n_src ? src + 3 * (size_t)i : dst + 3 * (size_t)(i - n_src);
     m = fmaxf(m, fmaxf(fabsf(p[0] - cx), fmaxf(fabsf(p[1] - cy), fabsf(p[2] - cz))));
@@ -156,8 +191,8 @@ __device__ __forceinline__ float extent_scale(unsigned int bits) {
 // Threads [ns_pad + nd_pad, + nsub_pad) build a THIRD set of images, every CT_SUB-th destination: the screening sweep runs
 // over those only (1/CT_SUB of the pairs); its minimum is an upper bound of the true one, which is all the exact sweep needs.
 __global__ void chamfer_tc_prep16_kernel(const float *__restrict__ src, int n_src, int ns_pad, const float *__restrict__ dst, int n_dst,
-                                         int nd_pad, int nsub_pad, int sub, uint8_t *__restrict__ a_img, uint8_t *__restrict__ b_img,
-                                         uint8_t *__restrict__ sub_img, float *__restrict__ norm2,
+                                         int nd_pad, int nsub_pad, int sub, uint8_t *__restrict__ a_img, uint8_t *__restrict__ a_img_x,
+                                         uint8_t *__restrict__ b_img, uint8_t *__restrict__ sub_img, float *__restrict__ norm2,
                                          unsigned int *__restrict__ stats, unsigned int *__restrict__ bound,
                                          unsigned long long *__restrict__ best) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -173,6 +208,8 @@ __global__ void chamfer_tc_prep16_kernel(const float *__restrict__ src, int n_sr
   const int r = i % rows;
   const size_t pi = is_sub ? (size_t)i * sub : (size_t)i;   // point index
   const float scale = extent_scale(stats[2]);
+  float ctr[3];
+  tc_centre(stats, dst, ctr);
   __half e[16];
   const __half zero = __float2half_rn(0.f), one = __float2half_rn(1.f);
 #pragma unroll
@@ -182,7 +219,7 @@ __global__ void chamfer_tc_prep16_kernel(const float *__restrict__ src, int n_sr
     float p[3];
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
-      p[c] = (pts[3 * pi + c] - dst[c]) * scale;   // centre = first destination point; power-of-two scale: exact
+      p[c] = (pts[3 * pi + c] - ctr[c]) * scale;   // centre = centroid of the destinations; power-of-two scale: exact
       nn += p[c] * p[c];
     }
 #pragma unroll
@@ -192,12 +229,13 @@ __global__ void chamfer_tc_prep16_kernel(const float *__restrict__ src, int n_sr
       if (is_src) { e[4 * c] = h; e[4 * c + 1] = h; e[4 * c + 2] = m; e[4 * c + 3] = m; }
       else        { e[4 * c] = h; e[4 * c + 1] = m; e[4 * c + 2] = h; e[4 * c + 3] = m; }
     }
-    if (is_src) { e[12] = one; e[13] = one; e[14] = one; }
+    if (is_src) { e[12] = one; e[13] = one; e[14] = one; e[15] = one; }
     else {
       e[12] = __float2half_rn(nn);
       const float r1 = nn - __half2float(e[12]);
       e[13] = __float2half_rn(r1);
       e[14] = __float2half_rn(r1 - __half2float(e[13]));
+      e[15] = __float2half_ru(8e-6f * nn);     // this destination's share of the error margin (see above)
     }
   } else if (!is_src) {
     e[12] = __float2half_rn(60000.f);   // padding destinations never win (real a' < 10^4)
@@ -210,6 +248,10 @@ __global__ void chamfer_tc_prep16_kernel(const float *__restrict__ src, int n_sr
     v.x = pack2h(e[8 * g], e[8 * g + 1]); v.y = pack2h(e[8 * g + 2], e[8 * g + 3]);
     v.z = pack2h(e[8 * g + 4], e[8 * g + 5]); v.w = pack2h(e[8 * g + 6], e[8 * g + 7]);
     *reinterpret_cast<uint4 *>(base + img_off(r, 8 * g, 16)) = v;
+    if (is_src) {   // the exact sweep's source image: slot 15 negated
+      if (g == 1) v.w = pack2h(e[14], __hneg(e[15]));
+      *reinterpret_cast<uint4 *>(a_img_x + (size_t)(i / rows) * (rows * 32) + img_off(r, 8 * g, 16)) = v;
+    }
   }
   if (is_src) {
     if (i < n) {
@@ -368,8 +410,8 @@ struct CtArgs {
 };
 
 // EXACT = false: bound[s] = min_j a(s, j) + |s - c|^2.
-// EXACT = true : same sweep (bit-identical a values: same operands, same MMA shape); every pair with
-//                a < (bound - |s - c|^2) + margin is re-evaluated with the reference's arithmetic (direct differences,
+// EXACT = true : same sweep (same MMA shape; F16: the source image with slot 15 negated, see the error model above); every pair
+//                with a < (bound - |s - c|^2) + margin is re-evaluated with the reference's arithmetic (direct differences,
 //                each op rounded, sqrt_rn) and merged with atomicMin on (bits(dist) << 32 | j): first index of the minimum.
 // F16: the fp16 two-way-split images above (one K = 16 MMA per 128 x 256 stage, 8 KB stages); else the bf16 three-way split
 // (two MMAs, 16 KB stages).
@@ -477,7 +519,8 @@ __global__ void __launch_bounds__(320, 1) chamfer_tc_kernel(const CtArgs A) {
       unsigned int jbest = 0xffffffffu;
       if (EXACT && s_row < A.n_src) {
         const float b = __uint_as_float(A.bound[s_row]), nn = A.norm2[s_row];
-        thr = (b - nn) + 8e-6f * (nn + 2.f * __uint_as_float(A.stats[0]) + b) + (F16 ? 2e-5f : 0.f);
+        thr = (b - nn) + (F16 ? 8e-6f * (nn + b) + 2e-5f                                  // destinations carry their own share (slot 15)
+                              : 8e-6f * (nn + 2.f * __uint_as_float(A.stats[0]) + b));
         sx = A.src[3 * s_row]; sy = A.src[3 * s_row + 1]; sz = A.src[3 * s_row + 2];
       }
       // one 64-column chunk: running minimum (screen) or threshold test + exact re-evaluation of the few survivors
@@ -574,8 +617,8 @@ size_t nnb_chamfer_tc_norm2_offset(int n_src, int n_dst) {
   return (size_t)nnb_cdiv(n_src, 128) * 8192 + (size_t)nnb_cdiv(n_dst, 256) * CT_STAGE;
 }
 
-// bound (n_src uint32 = float bits, pre-filled with a large value) <- min over destinations; stats[0] = max |q-c|^2,
-// stats[1] = max |q|^2 (float bits).  workspace: nnb_chamfer_tc_workspace_bytes.
+// bound (n_src uint32 = float bits, pre-filled with a large value) <- min over destinations; stats (10 x uint32): [0] = max |q-c|^2,
+// [1] = max |q|^2 (float bits), [2] extent, [3] list gate, [5] counter, [6..9] centre sums.  workspace: nnb_chamfer_tc_workspace_bytes.
 // Resets bound[] and best_init[] (to ~0) itself.  best != nullptr: also run the exact sweep, best[s] = (bits(dist) << 32 | first argmin j).
 int nnb_chamfer_tc_bound(const float *src, int n_src, const float *dst, int n_dst, unsigned int *bound, unsigned int *stats, void *workspace,
                          unsigned long long *best_init, unsigned long long *best, int use_f16, cudaStream_t s) {
@@ -590,8 +633,10 @@ int nnb_chamfer_tc_bound(const float *src, int n_src, const float *dst, int n_ds
   const int n_sblocks = nnb_cdiv(n_src, 128), n_stages = nnb_cdiv(n_dst, 256);
   uint8_t *a_img = static_cast<uint8_t *>(workspace);
   uint8_t *b_img = a_img + (size_t)n_sblocks * 8192;
+  // the fp16 source images take 4 KB per block of the 8 KB the bf16 ones need: the exact sweep's copy lives in the other half
+  uint8_t *a_img_x = a_img + (size_t)n_sblocks * 4096;
   float *norm2 = reinterpret_cast<float *>(b_img + (size_t)n_stages * CT_STAGE);
-  NNB_CUDA(cudaMemsetAsync(stats, 0, 6 * sizeof(unsigned int), s));
+  NNB_CUDA(cudaMemsetAsync(stats, 0, 10 * sizeof(unsigned int), s));
   const int ns_pad = n_sblocks * 128, nd_pad = n_stages * 256;
   // stage lists pay off when there are enough stages to skip; small problems run the two plain sweeps
   const bool lists = use_f16 && n_stages >= 16;
@@ -602,12 +647,16 @@ int nnb_chamfer_tc_bound(const float *src, int n_src, const float *dst, int n_ds
   int *list = reinterpret_cast<int *>(box + (size_t)n_stages * 8);
   int *list_cnt = list + (size_t)n_sblocks * n_stages;
   if (use_f16) {
+    int cg = nnb_cdiv(n_dst, 256 * 8);
+    if (cg > nnb_sm_count()) cg = nnb_sm_count();
+    chamfer_tc_centre_kernel<<<cg, 256, 0, s>>>(dst, n_dst, stats);
+    NNB_CHECK_LAUNCH();
     int eg = nnb_cdiv(n_src + n_dst, 256 * 8);
     if (eg > nnb_sm_count()) eg = nnb_sm_count();
     chamfer_tc_extent_kernel<<<eg, 256, 0, s>>>(src, n_src, dst, n_dst, stats);
     NNB_CHECK_LAUNCH();
     chamfer_tc_prep16_kernel<<<nnb_cdiv(ns_pad + nd_pad + nsub_pad, 128), 128, 0, s>>>(src, n_src, ns_pad, dst, n_dst, nd_pad, nsub_pad, sub, a_img,
-                                                                                     b_img, sub_img, norm2, stats, bound, best_init);
+                                                                                     a_img_x, b_img, sub_img, norm2, stats, bound, best_init);
     if (lists) {
       NNB_CHECK_LAUNCH();
       chamfer_tc_boxes_kernel<<<nnb_cdiv(n_stages, 4), 128, 0, s>>>(dst, n_dst, n_stages, box, stats);
@@ -648,8 +697,10 @@ int nnb_chamfer_tc_bound(const float *src, int n_src, const float *dst, int n_ds
   else chamfer_tc_kernel<false, false><<<grid, 320, CS_TOTAL, s>>>(A);
   NNB_CHECK_LAUNCH();
   if (best) {
-    if (use_f16) chamfer_tc_kernel<true, true><<<grid, 320, CS_TOTAL, s>>>(A);
-    else chamfer_tc_kernel<true, false><<<grid, 320, CS_TOTAL, s>>>(A);
+    if (use_f16) {
+      A.a_img = a_img_x;
+      chamfer_tc_kernel<true, true><<<grid, 320, CS_TOTAL, s>>>(A);
+    } else chamfer_tc_kernel<true, false><<<grid, 320, CS_TOTAL, s>>>(A);
     NNB_CHECK_LAUNCH();
   }
   return 0;

@@ -199,6 +199,46 @@ def test_chamfer_indices_far_from_origin(chamfer_pass1):
     assert torch.equal(idx.cpu(), want)
 
 
+@pytest.mark.parametrize("layout", ["raster", "shuffled", "far_centre"])
+def test_chamfer_indices_on_clouds_that_collapse_near_the_camera(layout, chamfer_pass1):
+    """Sparse depth maps (the fork's V_KITTI configs) back-project to clouds whose bulk sits in a cap of radius ~0.01 around the
+    camera (zero depths clamped to nearest_limit) while one point in six sets the extent: the tensor-core screen's margin carries
+    a per-destination share (K slot 15) so that the cap is tested against its own error scale.  Indices must stay bit-exact --
+    checked on every source -- for pixel-ordered clouds (stage lists), shuffled ones (plain sweeps), and with the first
+    destination (the screen's centre) far from the cap, where the cap points have the LARGEST scaled norms."""
+    from model import _ops
+    from oracle import nope_oracle as O
+    g = torch.Generator().manual_seed(21)
+    h, w = 47, 155
+    v, u = torch.meshgrid(torch.linspace(-0.3, 0.3, h), torch.linspace(-1, 1, w), indexing="ij")
+    dirs = torch.stack([u, v, -torch.ones_like(u)], -1).reshape(-1, 3)
+
+    def cloud(seed, shift):
+        gg = torch.Generator().manual_seed(seed)
+        far = torch.rand(h * w, generator=gg) < 0.16
+        depth = torch.where(far, 0.08 + 0.06 * torch.rand(h * w, generator=gg), torch.full((h * w,), 0.01))
+        return dirs * depth.unsqueeze(-1) + shift
+    a = cloud(1, torch.tensor([0.012, -0.004, 0.006]))
+    b = cloud(2, torch.zeros(3))
+    if layout == "shuffled":
+        a, b = a[torch.randperm(a.shape[0], generator=g)], b[torch.randperm(b.shape[0], generator=g)]
+    if layout == "far_centre":
+        b = torch.cat([torch.tensor([[0.9, -0.2, -0.15]]), b])      # dst[0] is the centre of the scaled frame
+    from model import _cabi as K
+    for src, dst in ((a, b), (b, a)):
+        idx, dist = _ops.chamfer_nn(src.to(dev()), dst.to(dev()), want_dist=True)
+        old = K.lib().nnb_debug_chamfer_pass1(1)          # every source against the CUDA-core sweeps ...
+        try:
+            idx_cc, dist_cc = _ops.chamfer_nn(src.to(dev()), dst.to(dev()), want_dist=True)
+        finally:
+            K.lib().nnb_debug_chamfer_pass1(old)
+        assert torch.equal(idx, idx_cc) and torch.equal(dist, dist_cc), "%d of %d indices differ" % (int((idx != idx_cc).sum()), idx.numel())
+        sub = torch.arange(0, src.shape[0], 7)            # ... and every seventh against the brute-force oracle on the CPU
+        want = O.nearest_idx(src[sub].t().contiguous(), dst.t().contiguous(), slice_len=256)
+        assert torch.equal(idx.cpu()[sub], want)
+        assert_close(dist[sub.to(dev())], torch.linalg.norm(src[sub] - dst[want], dim=1), 1e-6, 1e-8, "nn distance")
+
+
 def test_backproject_and_reproject_vs_oracle():
     from model import _ops
     from oracle import nope_oracle as O
