@@ -3,7 +3,6 @@ several repeats, each on >= 65,536 units where the stage allows it so that the f
 
 Nothing here is on the product path.  `torch_eager_gpu` executes oracle/ (the plain-PyTorch restatement of the reference) as a
 COMPARATOR on the same GPU -- SURVEY.md section 0 names stock PyTorch eager on the same device "the comparison target"."""
-import os
 import time
 
 import torch

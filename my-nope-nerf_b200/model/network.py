@@ -1,6 +1,5 @@
 """nope_nerf -- drop-in for the reference's model/network.py (the module `get_model` builds; its parameters are what
 train.py hands to Adam and what model.pt stores under `renderer.model.*`)."""
-import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
